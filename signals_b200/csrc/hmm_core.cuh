@@ -1,0 +1,276 @@
+// hmm_core.cuh -- per-sequence arithmetic of the HSCN / ASCN HMM, written once as
+// host+device inline functions.  The CUDA kernels (hmm_kernels.cu) call these per lane;
+// tests/hostemu compiles the very same functions with g++ so the control flow can be
+// checked against the oracle on a machine without a GPU.  There is no CPU execution
+// path in the product: nothing in signals_b200/ calls these functions on the host.
+//
+// Reference behaviour implemented here (all citations into /root/reference):
+//   emission probabilities and masks      R/callHSCN.R:48-80 (HaplotypeHMM), R/callASCN.R:50-81 (alleleHMM)
+//   transition matrix                     R/callHSCN.R:82-97, R/callASCN.R:83-96
+//   forward max-plus recursion + decode   src/code.cpp:20-42 (viterbi)
+//   logspace_add                          src/code.cpp:5-8
+// Third-party densities (stats::dbinom, VGAM::dbetabinom) are restated in lgamma form; the
+// exact operation order below is the contract shared with oracle/oracle.c (det flavour).
+#pragma once
+#include "sgb_math.h"
+
+#define SGB_MODEL_HSCN 0
+#define SGB_MODEL_ASCN 1
+#define SGB_LIK_BINOMIAL 0
+#define SGB_LIK_BETABINOMIAL 1
+#define SGB_DECODE_REFERENCE 0
+#define SGB_DECODE_CHAINED 1
+
+#define SGB_MAX_STATES 32      // S = maxCN+1 supported by the fused kernels
+#define SGB_CN_TABLE 16        // total-CN values 0..15 have their per-state constants tabulated
+#define SGB_COUNT_BITS 28      // read counts must be < 2^28 (packed record n:28 | x:28 | cn:8)
+
+// kind of a (total CN, state) pair
+#define SGB_KIND_NORMAL 0      // 0 < p < 1, use the density formula
+#define SGB_KIND_NAN 1         // p outside [0,1] or NaN -> dbinom returns NaN -> -Inf after the NA mask
+#define SGB_KIND_P0 2          // p == 0 : point mass at k == 0
+#define SGB_KIND_P1 3          // p == 1 : point mass at k == n
+#define SGB_KIND_BB_AS_BINOM 4 // beta-binomial with both shapes > exp(20): VGAM falls back to dbinom
+
+struct SgbStateConst {
+    double lp;    // log(p)
+    double lq;    // log1p(-p)
+    double a;     // beta-binomial shape1 = p (1-rho)/rho
+    double b;     // beta-binomial shape2 = (1-p)(1-rho)/rho
+    double l0;    // lgamma(a) + lgamma(b) - lgamma(a+b)
+    int kind;
+};
+
+// scalar parameters derived once per call (device set-up kernel / oracle computes the same values)
+struct SgbScalars {
+    double log_eps;     // log(eps)           (used when eps > 0)
+    double log_abias;   // log(Abias)         (used when Abias > 0, HSCN only)
+    double tr_self;     // log transition, from == to
+    double tr_off;      // log transition, from != to
+    double init;        // -log(S)            (src/code.cpp:20)
+    double bb_s;        // (1-rho)/rho
+    int use_eps;
+    int use_abias;
+};
+
+// total CN as the model sees it: HaplotypeHMM remaps 0 -> 1 (R/callHSCN.R:49), alleleHMM does not
+SGB_HD int sgb_cprime(int model, int c) { return (model == SGB_MODEL_HSCN && c == 0) ? 1 : c; }
+
+// number of leading states that are not masked to -Inf:
+//   HSCN  l[m > c'] = -Inf      (R/callHSCN.R:80)  -> states 0..min(c',S-1)
+//   ASCN  l[m > c/2] = -Inf     (R/callASCN.R:81)  -> states 0..min(floor(c/2),S-1)
+SGB_HD int sgb_live_states(int model, int cprime, int S)
+{
+    int top = (model == SGB_MODEL_HSCN) ? cprime : (cprime >> 1);
+    return (top < S - 1 ? top : S - 1) + 1;
+}
+
+// per-(total CN, state) constants; p follows R/callHSCN.R:53-59 / R/callASCN.R:53-59
+SGB_HD SgbStateConst sgb_state_const(int cprime, int m, double loherror, int lik, double rho, double bb_s,
+                                     const double* __restrict__ LT)
+{
+    SgbStateConst sc;
+    double p = sgb_div((double)m, (double)cprime);          // 0/0 = NaN, m/0 = Inf (ASCN, CN 0)
+    if (2 * m < cprime) p = sgb_add(p, loherror);
+    if (2 * m > cprime) p = sgb_sub(p, loherror);
+    sc.lp = 0.0; sc.lq = 0.0; sc.a = 0.0; sc.b = 0.0; sc.l0 = 0.0;
+    if (p != p || p < 0.0 || p > 1.0) { sc.kind = SGB_KIND_NAN; return sc; }
+    if (p == 0.0) { sc.kind = SGB_KIND_P0; return sc; }
+    if (p == 1.0) { sc.kind = SGB_KIND_P1; return sc; }
+    sc.kind = SGB_KIND_NORMAL;
+    sc.lp = sgb_log(p, LT);
+    sc.lq = sgb_log1p(-p, LT);
+    if (lik == SGB_LIK_BETABINOMIAL && rho > 0.0) {
+        sc.a = sgb_mul(p, bb_s);
+        sc.b = sgb_mul(sgb_sub(1.0, p), bb_s);
+        const double big = 485165195.40979028;              // exp(20), VGAM's Inf.shape
+        if (sc.a > big && sc.b > big) sc.kind = SGB_KIND_BB_AS_BINOM;
+        else sc.l0 = sgb_sub(sgb_add(sgb_lgamma(sc.a, LT), sgb_lgamma(sc.b, LT)), sgb_lgamma(sgb_add(sc.a, sc.b), LT));
+    }
+    return sc;
+}
+
+SGB_HD SgbScalars sgb_scalars(int S, double eps, double Abias, double stp, double rho, const double* __restrict__ LT)
+{
+    SgbScalars s;
+    s.use_eps = eps > 0.0;
+    s.use_abias = Abias > 0.0;
+    s.log_eps = s.use_eps ? sgb_log(eps, LT) : 0.0;
+    s.log_abias = s.use_abias ? sgb_log(Abias, LT) : 0.0;
+    if (stp == 0.0) {
+        s.tr_self = s.tr_off = sgb_log(sgb_div(1.0, (double)S), LT);
+    } else {
+        s.tr_self = sgb_log(stp, LT);
+        s.tr_off = sgb_log(sgb_div(sgb_sub(1.0, stp), (double)(S - 1)), LT);
+    }
+    s.init = -sgb_log((double)S, LT);
+    s.bb_s = (rho > 0.0) ? sgb_div(sgb_sub(1.0, rho), rho) : 0.0;
+    return s;
+}
+
+// quantities shared by every state of one bin
+struct SgbBin {
+    int n, x, cprime;
+    double kd, nkd;     // (double)x, (double)(n-x)
+    double lc_x;        // log choose(n, x)      = (LF(n) - LF(x)) - LF(n-x)
+    double lc_y;        // log choose(n, n-x)    = (LF(n) - LF(n-x)) - LF(x)   (ASCN second density)
+    double lg_sn;       // lgamma(s + n)         (beta-binomial)
+    int in_support;     // 0 <= x <= n
+};
+
+SGB_HD SgbBin sgb_bin_prepare(int model, int lik_bb, int n, int x, int c, double bb_s,
+                              const double* __restrict__ LF, const double* __restrict__ LT)
+{
+    SgbBin b;
+    b.n = n; b.x = x; b.cprime = sgb_cprime(model, c);
+    b.in_support = (x >= 0) && (x <= n);
+    b.kd = (double)x; b.nkd = (double)(n - x);
+    b.lc_x = 0.0; b.lc_y = 0.0; b.lg_sn = 0.0;
+    if (b.in_support) {
+        double fn = sgb_logfact(n, LF, LT), fx = sgb_logfact(x, LF, LT), fy = sgb_logfact(n - x, LF, LT);
+        b.lc_x = sgb_sub(sgb_sub(fn, fx), fy);
+        b.lc_y = sgb_sub(sgb_sub(fn, fy), fx);
+        if (lik_bb) b.lg_sn = sgb_lgamma(sgb_add(bb_s, (double)n), LT);
+    }
+    return b;
+}
+
+// log density of k successes out of k + nk trials for one state (dbinom / dbetabinom restated)
+SGB_HD double sgb_density(const SgbStateConst& sc, int lik_bb, double kd, double nkd, double lc, double lg_sn,
+                          int in_support, const double* __restrict__ LT)
+{
+    if (sc.kind == SGB_KIND_NAN) return sgb_nan();
+    if (!in_support) return -sgb_inf();
+    if (sc.kind == SGB_KIND_P0) return (kd == 0.0) ? 0.0 : -sgb_inf();
+    if (sc.kind == SGB_KIND_P1) return (nkd == 0.0) ? 0.0 : -sgb_inf();
+    if (!lik_bb || sc.kind == SGB_KIND_BB_AS_BINOM) return sgb_fma(nkd, sc.lq, sgb_fma(kd, sc.lp, lc));
+    double t1 = sgb_add(sgb_lgamma(sgb_add(sc.a, kd), LT), sgb_lgamma(sgb_add(sc.b, nkd), LT));
+    t1 = sgb_sub(t1, lg_sn);
+    return sgb_add(lc, sgb_sub(t1, sc.l0));
+}
+
+// emission log-likelihood l[bin, m] of a LIVE state m (masked states are -Inf and never reach here)
+SGB_HD double sgb_emission(int model, int lik_bb, const SgbBin& b, int m, const SgbStateConst& sc,
+                           const SgbScalars& sp, const double* __restrict__ LT, const double* __restrict__ ET)
+{
+    double l = sgb_density(sc, lik_bb, b.kd, b.nkd, b.lc_x, b.lg_sn, b.in_support, LT);
+    if (model == SGB_MODEL_ASCN) {
+        double l2 = sgb_density(sc, lik_bb, b.nkd, b.kd, b.lc_y, b.lg_sn, b.in_support, LT);
+        l = sgb_logspace_add(l, l2, LT, ET);                                  // R/callASCN.R:64,71
+    }
+    if (sp.use_eps) l = sgb_logspace_add(l, sp.log_eps, LT, ET);              // R/callHSCN.R:67-71
+    if (model == SGB_MODEL_HSCN && sp.use_abias && 2 * m < b.cprime)
+        l = sgb_logspace_add(l, sp.log_abias, LT, ET);                        // R/callHSCN.R:72-78
+    if (l != l) l = -sgb_inf();                                               // l[is.na(l)] <- log(0)
+    return l;
+}
+
+// ------------------------------------------------------------------ forward recursion
+// State of one sequence between bins.  Because the reference's transition matrix has one
+// value on the diagonal (tr_self) and one off it (tr_off), and rounding is monotone,
+//     max_k fl(fl(T1[k] + tr[k,i]) + e_i) = max( fl(fl(M_i + tr_off) + e_i), fl(fl(T1[i] + tr_self) + e_i) )
+// with M_i = max_{k != i} T1[k], which needs only the largest value m1 (first index i1) and the
+// largest value m2 among the other states.  That gives every T1[i,t] bit-exactly in O(S).
+// The reference's decode (src/code.cpp:35-42) only ever reads T2 at the column-wise best
+// state, so the first-index argmax over predecessors is evaluated for that one state alone,
+// by the reference's own expression (T1[k] + tr[k,i]) + e_i and strict '>' (first maximum).
+template <int SMAX>
+struct SgbSeqState {
+    double T1[SMAX];
+    double m1, m2;
+    int i1;
+};
+
+template <int SMAX>
+SGB_HD void sgb_top2(SgbSeqState<SMAX>& st, int S)
+{
+    double m1 = st.T1[0], m2 = -sgb_inf();
+    int i1 = 0;
+#pragma unroll
+    for (int i = 1; i < SMAX; i++) {
+        if (i < S) {
+            double v = st.T1[i];
+            if (v > m1) { m2 = m1; m1 = v; i1 = i; }
+            else if (v > m2) m2 = v;
+        }
+    }
+    st.m1 = m1; st.m2 = m2; st.i1 = i1;
+}
+
+// first bin of a sequence:  T1[,0] = initial + emission   (src/code.cpp:25)
+template <int SMAX>
+SGB_HD void sgb_seq_init(SgbSeqState<SMAX>& st, const double* e, int S, double init)
+{
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) st.T1[i] = (i < S) ? sgb_add(init, e[i]) : -sgb_inf();
+    sgb_top2<SMAX>(st, S);
+}
+
+// One bin (j >= 1).  Returns the state the reference emits for bin j-1:
+// T2[argmax_i T1[i,j], j]  (src/code.cpp:39-42).  e[i] must be -Inf for masked states.
+template <int SMAX>
+SGB_HD int sgb_seq_step(SgbSeqState<SMAX>& st, const double* e, int S, double tr_self, double tr_off)
+{
+    double Tn[SMAX];
+    const double u1 = sgb_add(st.m1, tr_off), u2 = sgb_add(st.m2, tr_off);
+    double m1 = -sgb_inf(), m2 = -sgb_inf();
+    int i1 = 0;
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) {
+        if (i < S) {
+            double voff = sgb_add((i == st.i1) ? u2 : u1, e[i]);
+            double vdia = sgb_add(sgb_add(st.T1[i], tr_self), e[i]);
+            double v = (S > 1 && voff > vdia) ? voff : vdia;
+            Tn[i] = v;
+            if (i == 0) { m1 = v; }
+            else if (v > m1) { m2 = m1; m1 = v; i1 = i; }
+            else if (v > m2) m2 = v;
+        } else {
+            Tn[i] = -sgb_inf();
+        }
+    }
+    // predecessor of the column-best state i1, first maximum of (T1[k] + tr[k,i1]) + e[i1]
+    double ej = e[0];
+#pragma unroll
+    for (int i = 1; i < SMAX; i++) if (i == i1) ej = e[i];
+    int back = 0;
+#pragma unroll
+    for (int k = SMAX - 1; k >= 0; k--) {
+        if (k < S) {
+            double val = sgb_add(sgb_add(st.T1[k], (k == i1) ? tr_self : tr_off), ej);
+            if (val == m1) back = k;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) st.T1[i] = Tn[i];
+    st.m1 = m1; st.m2 = m2; st.i1 = i1;
+    return back;
+}
+
+// Chained (textbook) mode: backpointers of ALL states for bin j, bp[i] = first argmax_k.
+template <int SMAX>
+SGB_HD void sgb_seq_step_chained(SgbSeqState<SMAX>& st, const double* e, int S, double tr_self, double tr_off,
+                                 unsigned char* bp)
+{
+    double Tn[SMAX];
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) {
+        Tn[i] = -sgb_inf();
+        if (i < S) {
+            double best = sgb_add(sgb_add(st.T1[0], (0 == i) ? tr_self : tr_off), e[i]);
+            int arg = 0;
+#pragma unroll
+            for (int k = 1; k < SMAX; k++) {
+                if (k < S) {
+                    double val = sgb_add(sgb_add(st.T1[k], (k == i) ? tr_self : tr_off), e[i]);
+                    if (val > best) { best = val; arg = k; }
+                }
+            }
+            Tn[i] = best;
+            bp[i] = (unsigned char)arg;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) st.T1[i] = Tn[i];
+    sgb_top2<SMAX>(st, S);
+}
