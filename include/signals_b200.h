@@ -1,0 +1,137 @@
+/* signals_b200.h -- C ABI of libsignals_b200.so: the B200 (sm_100a) implementation of the
+ * per-cell haplotype- / allele-specific copy-number HMM of shahcompbio/signals.
+ *
+ * This is the drop-in boundary.  Every entry point replaces a specific piece of the reference
+ * (citations are file:line into the reference repository); INTEGRATION.md shows the .Call shim
+ * a maintainer adds on the R side (rpkg/src/r_shim.c) so the R API stays unchanged.
+ *
+ * Conventions
+ *   - plain C types only; the caller owns every buffer; the library never retains caller memory
+ *   - every function returns 0 on success, non-zero on failure; sgb_last_error() gives the text
+ *     (the R shim turns it into Rf_error, mirroring BEGIN_RCPP/END_RCPP, src/RcppExports.cpp:16,23)
+ *   - there is NO CPU implementation behind these symbols: a missing / unusable CUDA device is an error
+ *   - work runs on the CUDA device that is current in the calling thread (cudaSetDevice / sgb_init)
+ *   - not re-entrant: one call at a time per device (R is single threaded; `ncores` is ignored)
+ */
+#ifndef SIGNALS_B200_H
+#define SIGNALS_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define SGB_API __attribute__((visibility("default")))
+#else
+#define SGB_API
+#endif
+
+#define SGB_MODEL_HSCN 0          /* HaplotypeHMM  R/callHSCN.R:36-108 */
+#define SGB_MODEL_ASCN 1          /* alleleHMM     R/callASCN.R:41-103 */
+#define SGB_LIK_BINOMIAL 0        /* stats::dbinom        R/callHSCN.R:62 */
+#define SGB_LIK_BETABINOMIAL 1    /* VGAM::dbetabinom     R/callHSCN.R:64 */
+#define SGB_DECODE_REFERENCE 0    /* the reference's decode rule, src/code.cpp:35-42 (default, bit-exact) */
+#define SGB_DECODE_CHAINED 1      /* textbook Viterbi backtrace over uint8 backpointers (opt-in extra) */
+
+/* Arguments of HaplotypeHMM / alleleHMM that reach the kernels (R/callHSCN.R:36-46, R/callASCN.R:41-49).
+ * minor_cn is always 0..n_states-1 (R/callHSCN.R:232: minor_cn <- seq(0, maxCN, 1)); n_states <= 32. */
+typedef struct sgb_params {
+    int32_t model;               /* SGB_MODEL_*  */
+    int32_t likelihood;          /* SGB_LIK_*    */
+    int32_t n_states;            /* maxCN + 1    */
+    int32_t decode;              /* SGB_DECODE_* */
+    double loherror;
+    double eps;
+    double rho;
+    double Abias;
+    double selftransitionprob;
+} sgb_params;
+
+typedef struct sgb_plan sgb_plan; /* sequence index of one batch, resident on the device */
+
+/* ---- library / device ------------------------------------------------------------------ */
+/* Select CUDA device `device` (>= 0) for this thread and create the library context on it.
+ * Optional: every entry point creates the context of the current device on first use.
+ * Replaces nothing in the reference (useDynLib(signals), NAMESPACE:107, needs no device). */
+SGB_API int sgb_init(int device);
+/* Release every context (streams, device buffers).  Counterpart of library unload. */
+SGB_API int sgb_shutdown(void);
+/* Text of the last error raised in the calling thread ("" if none). */
+SGB_API const char* sgb_last_error(void);
+/* Number of CUDA devices visible to the process (0 and an error text if CUDA is unusable). */
+SGB_API int sgb_device_count(void);
+
+/* ---- the batched hot path -------------------------------------------------------------- */
+/* Replaces the per-cell / per-chromosome loops of .callHaplotypeSpecificCN_ (R/callHSCN.R:244-280
+ * -> assignHaplotypeHMM :150-167 -> HaplotypeHMM :36-108 -> viterbi src/code.cpp:11-45) and of
+ * callAlleleSpecificCN (R/callASCN.R:382-414 -> assignalleleHMM :143-156 -> alleleHMM :41-103).
+ *
+ * The N rows are the long CNBAF table already ordered by (cell_id, chr, start) as R/callHSCN.R:241-242
+ * leaves it.  n = totalcounts, x = alleleB, cn = state (int32 when cn_itemsize == 4, uint8 when 1).
+ * Sequence s (one cell x chromosome) covers rows seg_off[s] .. seg_off[s+1]-1, nseg sequences.
+ * state_out[N] receives the decoded minor-CN state per row (the `minorcn` vector of each HMM call,
+ * concatenated as assignHaplotypeHMM :164 does).  loglik_out, if not NULL, receives the bins x states
+ * matrix `l` of every sequence (R/callHSCN.R:107): for sequence s a T x n_states column-major block
+ * at loglik_out + seg_off[s]*n_states.
+ * Host buffers may be pageable or pinned; inputs are copied to the device in chunks that overlap
+ * with the kernels.  Counts must be in [0, 2^28), cn in [0, 255]; violations are reported as errors. */
+SGB_API int sgb_hmm_decode(const sgb_params* params, int64_t N, const int32_t* n, const int32_t* x, const void* cn,
+                   int32_t cn_itemsize, int64_t nseg, const int64_t* seg_off, uint8_t* state_out,
+                   double* loglik_out);
+
+/* Same work sharded over the first `n_devices` CUDA devices of this process (contiguous blocks of
+ * sequences balanced by bin count; one host thread per device; each device writes its slice of
+ * state_out).  B200 equivalent of parallel::mclapply(mc.cores = ncores), R/callHSCN.R:244-260. */
+SGB_API int sgb_hmm_decode_multi(const sgb_params* params, int32_t n_devices, int64_t N, const int32_t* n,
+                         const int32_t* x, const void* cn, int32_t cn_itemsize, int64_t nseg,
+                         const int64_t* seg_off, uint8_t* state_out);
+
+/* Device-resident variant: inputs and outputs are device pointers on the current device.
+ * sgb_plan_create sorts the sequences by length on the host, uploads the index and reserves the
+ * packed-record scratch; the plan can be reused for any inputs with the same seg_off.
+ * sgb_hmm_decode_device only enqueues work on `stream` (a cudaStream_t, NULL = legacy default stream)
+ * and returns; sgb_plan_check synchronises that stream and reports input-validation errors. */
+SGB_API int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_states, int32_t decode,
+                    sgb_plan** plan_out);
+SGB_API int sgb_plan_destroy(sgb_plan* plan);
+SGB_API int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* plan, const int32_t* d_n, const int32_t* d_x,
+                          const void* d_cn, int32_t cn_itemsize, uint8_t* d_state_out, double* d_loglik_out,
+                          void* stream);
+SGB_API int sgb_plan_check(sgb_plan* plan, void* stream);
+/* bytes of device scratch the plan holds (packed records + optional backpointers) */
+SGB_API int64_t sgb_plan_scratch_bytes(const sgb_plan* plan);
+
+/* ---- the two Rcpp exports ---------------------------------------------------------------- */
+/* viterbi(emission, transition, observations)  src/code.cpp:11-45, R/RcppExports.R:8-10.
+ * emission: nrow_e x S column-major (rows = bins, as the R matrix); transition: S x S column-major log
+ * probabilities indexed [from, to]; observations: T 1-based row indices into emission.
+ * path_out[T]: 0-based states.  init_mode 0 = -log(S) (C++ viterbi), 1 = log(1/S) (viterbiR, R/viterbi.R:3).
+ * NaN emissions are treated as -Inf (the reference indexes with NA there: undefined).  S <= 128. */
+SGB_API int sgb_viterbi(const double* emission, int64_t nrow_e, const double* transition, const int32_t* observations,
+                int64_t T, int32_t S, int32_t init_mode, int32_t decode, int32_t* path_out);
+
+/* logspace_addcpp(logx, logy)  src/code.cpp:5-8, R/RcppExports.R:4-6 ; and its vectorised R twin
+ * logspace_add (R/callASCN.R:9-11).  Evaluated on the device with the same deterministic math as the
+ * emission kernel (a scalar call is a 1-element launch). */
+SGB_API int sgb_logspace_add(double logx, double logy, double* out);
+SGB_API int sgb_logspace_add_vec(const double* logx, const double* logy, int64_t n, double* out);
+
+/* ---- post-decode table columns ---------------------------------------------- */
+/* Clamp block R/callHSCN.R:282-290 (same arithmetic as R/callASCN.R:424-429) and the numeric part of
+ * add_states R/util.R:1078-1097.  cn/path are the `state` column and the decoded state_min of N rows.
+ * phase: 0 Balanced 1 A 2 B; state_phase: 0 Balanced 1 A-Gained 2 B-Gained 3 A-Hom 4 B-Hom; loh: 1 = "LOH". */
+SGB_API int sgb_postprocess(int64_t N, const void* cn, int32_t cn_itemsize, const uint8_t* path, int32_t* A, int32_t* B,
+                    int32_t* state_min, uint8_t* loh, uint8_t* phase, uint8_t* state_phase, double* state_baf);
+
+/* ---- diagnostics -------------------------------------------------------------------------- */
+/* Evaluate one deterministic math primitive on the device (tests pin device bits == host bits).
+ * fn: 0 exp, 1 log, 2 log1p on [0,1], 3 log1p, 4 lgamma, 5 logspace_add(in, in2), 6 log(in!) */
+SGB_API int sgb_math_eval(int32_t fn, const double* in, const double* in2, int64_t n, double* out);
+/* Time `iters` launches of an FP64 FMA throughput micro-kernel; *tflops_out = achieved DFMA TFLOP/s
+ * (the measured FP64 roofline denominator). */
+SGB_API int sgb_fp64_peak(int32_t iters, double* tflops_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

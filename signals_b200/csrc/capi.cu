@@ -1,0 +1,664 @@
+// capi.cu -- host runtime behind the C ABI of include/signals_b200.h.
+//
+// One context per CUDA device (created on first use): two slot streams for the chunked
+// host->device->host pipeline, grow-only device buffers, the per-call constant tables.
+// The host never touches the per-bin data: validation, narrowing and re-layout happen in k_pack.
+// There is no CPU execution path here -- if CUDA is unusable every entry point fails loudly.
+#include "../../include/signals_b200.h"
+#include "kernels.h"
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+namespace {
+
+thread_local std::string t_err;
+
+int fail(const std::string& msg)
+{
+    t_err = msg;
+    return 1;
+}
+
+#define SGB_CUDA(call)                                                                                       \
+    do {                                                                                                     \
+        cudaError_t e__ = (call);                                                                            \
+        if (e__ != cudaSuccess) {                                                                            \
+            char b__[512];                                                                                   \
+            snprintf(b__, sizeof b__, "CUDA error %s at %s:%d: %s", cudaGetErrorName(e__), __FILE__, __LINE__, \
+                     cudaGetErrorString(e__));                                                               \
+            return fail(b__);                                                                                \
+        }                                                                                                    \
+    } while (0)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes)
+    {
+        if (bytes <= cap) return 0;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            return fail(std::string("cudaMalloc of ") + std::to_string(want) + " bytes failed: " + cudaGetErrorString(e));
+        }
+        cap = want;
+        return 0;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+    }
+};
+
+// host-side description of a batch of sequences, sorted by length (longest first)
+struct HostPlan {
+    std::vector<long long> pstart, ostart;
+    std::vector<int> len;
+    long long packed_len = 0;   // records
+    long long nseq = 0;
+    long long rows = 0;         // total bins covered
+};
+
+// seg_off[s0..s1]; row offsets are made relative to `row_base`
+int build_host_plan(const int64_t* seg_off, int64_t s0, int64_t s1, int64_t row_base, HostPlan& hp)
+{
+    const int64_t nseg = s1 - s0;
+    hp.pstart.clear(); hp.ostart.clear(); hp.len.clear();
+    hp.packed_len = 0; hp.nseq = 0; hp.rows = 0;
+    int64_t maxlen = 0;
+    for (int64_t s = s0; s < s1; s++) {
+        int64_t L = seg_off[s + 1] - seg_off[s];
+        if (L < 0) return fail("seg_off must be non-decreasing");
+        if (L > 0x7fffffff) return fail("a sequence longer than 2^31-1 bins is not supported");
+        if (L > maxlen) maxlen = L;
+    }
+    std::vector<int64_t> order;
+    order.reserve((size_t)nseg);
+    if (maxlen <= (1 << 22)) {
+        // counting sort by length, descending, stable
+        std::vector<int64_t> cnt((size_t)maxlen + 2, 0);
+        for (int64_t s = s0; s < s1; s++) {
+            int64_t L = seg_off[s + 1] - seg_off[s];
+            if (L > 0) cnt[(size_t)(maxlen - L) + 1]++;
+        }
+        for (size_t i = 1; i < cnt.size(); i++) cnt[i] += cnt[i - 1];
+        order.resize((size_t)cnt[cnt.size() - 1]);
+        for (int64_t s = s0; s < s1; s++) {
+            int64_t L = seg_off[s + 1] - seg_off[s];
+            if (L > 0) order[(size_t)cnt[(size_t)(maxlen - L)]++] = s;
+        }
+    } else {
+        for (int64_t s = s0; s < s1; s++) if (seg_off[s + 1] > seg_off[s]) order.push_back(s);
+        std::stable_sort(order.begin(), order.end(), [&](int64_t a, int64_t b) {
+            return (seg_off[a + 1] - seg_off[a]) > (seg_off[b + 1] - seg_off[b]);
+        });
+    }
+    hp.nseq = (long long)order.size();
+    hp.pstart.resize(order.size()); hp.ostart.resize(order.size()); hp.len.resize(order.size());
+    long long p = 0;
+    for (size_t r = 0; r < order.size(); r++) {
+        int64_t s = order[r];
+        int L = (int)(seg_off[s + 1] - seg_off[s]);
+        hp.pstart[r] = p;
+        hp.ostart[r] = (long long)(seg_off[s] - row_base);
+        hp.len[r] = L;
+        p += ((long long)L + 1) & ~1ll;       // keep every sequence 16-byte aligned in the packed buffer
+        hp.rows += L;
+    }
+    hp.packed_len = p;
+    return 0;
+}
+
+struct Slot {
+    cudaStream_t st = nullptr;
+    DevBuf n, x, cn, out, packed, bp, last_state, pstart, ostart, len, loglik;
+    unsigned int* counter = nullptr;
+    HostPlan hp;
+    // pending device->host copy bookkeeping is implicit: copies are enqueued on st
+};
+
+struct Ctx {
+    int device = -1;
+    int sm_count = 148;
+    Slot slot[2];
+    cudaStream_t main = nullptr;
+    cudaEvent_t ev_setup = nullptr;
+    SgbDevTables* d_tabs = nullptr;
+    int* d_err = nullptr;
+    DevBuf scratch_a, scratch_b, scratch_c, scratch_d;   // small utilities (viterbi, logspace_add, ...)
+};
+
+std::mutex g_mu;
+Ctx* g_ctx[64] = {nullptr};
+
+int get_ctx(Ctx** out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess)
+        return fail(std::string("no usable CUDA device (this library has no CPU path): ") + cudaGetErrorString(e));
+    if (dev < 0 || dev >= 64) return fail("device index out of range");
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_ctx[dev]) {
+        Ctx* c = new Ctx();
+        c->device = dev;
+        cudaDeviceProp prop;
+        SGB_CUDA(cudaGetDeviceProperties(&prop, dev));
+        if (prop.major < 10) {
+            delete c;
+            return fail(std::string("device ") + prop.name + " is not sm_100-class; libsignals_b200 is built for sm_100a only");
+        }
+        c->sm_count = prop.multiProcessorCount;
+        SGB_CUDA(cudaStreamCreate(&c->main));
+        SGB_CUDA(cudaEventCreateWithFlags(&c->ev_setup, cudaEventDisableTiming));
+        for (int i = 0; i < 2; i++) {
+            SGB_CUDA(cudaStreamCreate(&c->slot[i].st));
+            SGB_CUDA(cudaMalloc(&c->slot[i].counter, sizeof(unsigned int)));
+        }
+        SGB_CUDA(cudaMalloc(&c->d_tabs, sizeof(SgbDevTables)));
+        SGB_CUDA(cudaMalloc(&c->d_err, sizeof(int)));
+        g_ctx[dev] = c;
+    }
+    *out = g_ctx[dev];
+    return 0;
+}
+
+int check_params(const sgb_params* P, SgbModelArgs& m)
+{
+    if (!P) return fail("params is NULL");
+    if (P->model != SGB_MODEL_HSCN && P->model != SGB_MODEL_ASCN) return fail("params.model must be SGB_MODEL_HSCN or SGB_MODEL_ASCN");
+    if (P->likelihood != SGB_LIK_BINOMIAL && P->likelihood != SGB_LIK_BETABINOMIAL)
+        return fail("Likelihood model must be one of binomial or betabinomial");      // R/callHSCN.R:778-780
+    if (P->n_states < 1 || P->n_states > SGB_MAX_STATES) return fail("n_states (maxCN+1) must be in 1..32");
+    if (P->decode != SGB_DECODE_REFERENCE && P->decode != SGB_DECODE_CHAINED) return fail("params.decode invalid");
+    if (!(P->selftransitionprob >= 0.0 && P->selftransitionprob <= 1.0)) return fail("selftransitionprob must be in [0,1]");
+    if (P->loherror != P->loherror || P->eps != P->eps || P->rho != P->rho || P->Abias != P->Abias)
+        return fail("NaN parameter");
+    m.model = P->model;
+    m.lik_bb = (P->likelihood == SGB_LIK_BETABINOMIAL && P->rho > 0.0) ? 1 : 0;   // rho == 0: VGAM falls back to dbinom
+    m.S = P->n_states;
+    m.decode = P->decode;
+    m.loherror = P->loherror;
+    m.rho = P->rho;
+    return 0;
+}
+
+const char* err_bits_text(int bits)
+{
+    if (bits & SGB_ERR_NEGATIVE_COUNT) return "negative read count in totalcounts / alleleB";
+    if (bits & SGB_ERR_COUNT_TOO_LARGE) return "read count >= 2^28 is not supported";
+    if (bits & SGB_ERR_BAD_CN) return "copy-number state outside 0..255";
+    return "unknown input error";
+}
+
+int upload_plan(Slot& S, cudaStream_t st, SgbPlanDev& pd)
+{
+    const HostPlan& hp = S.hp;
+    size_t ns = (size_t)hp.nseq;
+    if (S.pstart.reserve(ns * sizeof(long long) + 16)) return 1;
+    if (S.ostart.reserve(ns * sizeof(long long) + 16)) return 1;
+    if (S.len.reserve(ns * sizeof(int) + 16)) return 1;
+    if (ns) {
+        SGB_CUDA(cudaMemcpyAsync(S.pstart.p, hp.pstart.data(), ns * sizeof(long long), cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(S.ostart.p, hp.ostart.data(), ns * sizeof(long long), cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(S.len.p, hp.len.data(), ns * sizeof(int), cudaMemcpyHostToDevice, st));
+    }
+    pd.pstart = (const long long*)S.pstart.p;
+    pd.ostart = (const long long*)S.ostart.p;
+    pd.len = (const int*)S.len.p;
+    pd.nseq = hp.nseq;
+    pd.ngroups = (int)((hp.nseq + 31) / 32);
+    return 0;
+}
+
+long long chunk_bins_target()
+{
+    const char* e = getenv("SGB_CHUNK_BINS");
+    if (e) {
+        long long v = atoll(e);
+        if (v > 0) return v;
+    }
+    return 8ll << 20;
+}
+
+// Decode sequences [s_begin, s_end) of a host-resident batch on the current device.
+int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const int32_t* n, const int32_t* x,
+                      const void* cn, int cn_itemsize, const int64_t* seg_off, int64_t s_begin, int64_t s_end,
+                      uint8_t* state_out, double* loglik_out)
+{
+    if (s_end <= s_begin) return 0;
+    SGB_CUDA(cudaMemsetAsync(C->d_err, 0, sizeof(int), C->main));
+    SGB_CUDA(sgbk_setup(C->d_tabs, m, P->eps, P->Abias, P->selftransitionprob, C->main));
+    SGB_CUDA(cudaEventRecord(C->ev_setup, C->main));
+    const long long target = chunk_bins_target();
+    const int S = m.S;
+    int k = 0;
+    int64_t s0 = s_begin;
+    while (s0 < s_end) {
+        int64_t s1 = s0;
+        long long bins = 0;
+        while (s1 < s_end && (bins == 0 || bins + (seg_off[s1 + 1] - seg_off[s1]) <= target)) {
+            bins += seg_off[s1 + 1] - seg_off[s1];
+            s1++;
+        }
+        Slot& SL = C->slot[k & 1];
+        cudaStream_t st = SL.st;
+        SGB_CUDA(cudaStreamSynchronize(st));          // slot buffers (and its host plan) are free again
+        const int64_t r0 = seg_off[s0], r1 = seg_off[s1];
+        const long long rows = (long long)(r1 - r0);
+        if (build_host_plan(seg_off, s0, s1, r0, SL.hp)) return 1;
+        if (rows > 0) {
+            if (SL.n.reserve((size_t)rows * 4) || SL.x.reserve((size_t)rows * 4) ||
+                SL.cn.reserve((size_t)rows * cn_itemsize) || SL.out.reserve((size_t)rows) ||
+                SL.packed.reserve((size_t)SL.hp.packed_len * 8 + 16))
+                return 1;
+            if (m.decode == SGB_DECODE_CHAINED &&
+                (SL.bp.reserve((size_t)rows * S) || SL.last_state.reserve((size_t)SL.hp.nseq * 4 + 16)))
+                return 1;
+            if (loglik_out && SL.loglik.reserve((size_t)rows * S * 8)) return 1;
+            SGB_CUDA(cudaMemcpyAsync(SL.n.p, n + r0, (size_t)rows * 4, cudaMemcpyHostToDevice, st));
+            SGB_CUDA(cudaMemcpyAsync(SL.x.p, x + r0, (size_t)rows * 4, cudaMemcpyHostToDevice, st));
+            SGB_CUDA(cudaMemcpyAsync(SL.cn.p, (const char*)cn + (size_t)r0 * cn_itemsize, (size_t)rows * cn_itemsize,
+                                     cudaMemcpyHostToDevice, st));
+            SgbPlanDev pd;
+            if (upload_plan(SL, st, pd)) return 1;
+            SGB_CUDA(cudaStreamWaitEvent(st, C->ev_setup, 0));
+            SGB_CUDA(sgbk_pack((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, pd,
+                               (unsigned long long*)SL.packed.p, C->d_err, st));
+            SGB_CUDA(sgbk_decode(pd, (const unsigned long long*)SL.packed.p, C->d_tabs, m, (uint8_t*)SL.out.p,
+                                 (uint8_t*)SL.bp.p, (int*)SL.last_state.p, SL.counter, C->sm_count, st));
+            if (m.decode == SGB_DECODE_CHAINED)
+                SGB_CUDA(sgbk_backtrace(pd, (const uint8_t*)SL.bp.p, (const int*)SL.last_state.p, S, (uint8_t*)SL.out.p, st));
+            SGB_CUDA(cudaMemcpyAsync(state_out + r0, SL.out.p, (size_t)rows, cudaMemcpyDeviceToHost, st));
+            if (loglik_out) {
+                SGB_CUDA(sgbk_loglik((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, pd,
+                                     C->d_tabs, m, (double*)SL.loglik.p, st));
+                SGB_CUDA(cudaMemcpyAsync(loglik_out + (size_t)r0 * S, SL.loglik.p, (size_t)rows * S * 8,
+                                         cudaMemcpyDeviceToHost, st));
+            }
+        }
+        s0 = s1;
+        k++;
+    }
+    SGB_CUDA(cudaStreamSynchronize(C->slot[0].st));
+    SGB_CUDA(cudaStreamSynchronize(C->slot[1].st));
+    int bits = 0;
+    SGB_CUDA(cudaMemcpy(&bits, C->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (bits) return fail(err_bits_text(bits));
+    return 0;
+}
+
+int check_batch_args(int64_t N, const int32_t* n, const int32_t* x, const void* cn, int32_t cn_itemsize,
+                     int64_t nseg, const int64_t* seg_off, const uint8_t* state_out)
+{
+    if (N < 0 || nseg < 0) return fail("negative size");
+    if (cn_itemsize != 1 && cn_itemsize != 4) return fail("cn_itemsize must be 1 (uint8) or 4 (int32)");
+    if (nseg > 0 && !seg_off) return fail("seg_off is NULL");
+    if (N > 0 && (!n || !x || !cn || !state_out)) return fail("NULL data pointer");
+    if (nseg > 0) {
+        if (seg_off[0] < 0 || seg_off[nseg] > N) return fail("seg_off out of range");
+        for (int64_t s = 0; s < nseg; s++)
+            if (seg_off[s + 1] < seg_off[s]) return fail("seg_off must be non-decreasing");
+    }
+    return 0;
+}
+
+}  // namespace
+
+// ====================================================================== C ABI
+extern "C" {
+
+const char* sgb_last_error(void) { return t_err.c_str(); }
+
+int sgb_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        fail(std::string("CUDA unusable: ") + cudaGetErrorString(e));
+        return 0;
+    }
+    return n;
+}
+
+int sgb_init(int device)
+{
+    if (device >= 0) SGB_CUDA(cudaSetDevice(device));
+    Ctx* C;
+    return get_ctx(&C);
+}
+
+int sgb_shutdown(void)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (int d = 0; d < 64; d++) {
+        Ctx* c = g_ctx[d];
+        if (!c) continue;
+        cudaSetDevice(d);
+        for (int i = 0; i < 2; i++) {
+            Slot& s = c->slot[i];
+            if (s.st) { cudaStreamSynchronize(s.st); cudaStreamDestroy(s.st); }
+            s.n.release(); s.x.release(); s.cn.release(); s.out.release(); s.packed.release(); s.bp.release();
+            s.last_state.release(); s.pstart.release(); s.ostart.release(); s.len.release(); s.loglik.release();
+            if (s.counter) cudaFree(s.counter);
+        }
+        c->scratch_a.release(); c->scratch_b.release(); c->scratch_c.release(); c->scratch_d.release();
+        if (c->main) cudaStreamDestroy(c->main);
+        if (c->ev_setup) cudaEventDestroy(c->ev_setup);
+        if (c->d_tabs) cudaFree(c->d_tabs);
+        if (c->d_err) cudaFree(c->d_err);
+        delete c;
+        g_ctx[d] = nullptr;
+    }
+    cudaSetDevice(cur);
+    return 0;
+}
+
+int sgb_hmm_decode(const sgb_params* params, int64_t N, const int32_t* n, const int32_t* x, const void* cn,
+                   int32_t cn_itemsize, int64_t nseg, const int64_t* seg_off, uint8_t* state_out,
+                   double* loglik_out)
+{
+    SgbModelArgs m;
+    if (check_params(params, m)) return 1;
+    if (check_batch_args(N, n, x, cn, cn_itemsize, nseg, seg_off, state_out)) return 1;
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    return decode_host_range(C, params, m, n, x, cn, cn_itemsize, seg_off, 0, nseg, state_out, loglik_out);
+}
+
+int sgb_hmm_decode_multi(const sgb_params* params, int32_t n_devices, int64_t N, const int32_t* n,
+                         const int32_t* x, const void* cn, int32_t cn_itemsize, int64_t nseg,
+                         const int64_t* seg_off, uint8_t* state_out)
+{
+    SgbModelArgs m;
+    if (check_params(params, m)) return 1;
+    if (check_batch_args(N, n, x, cn, cn_itemsize, nseg, seg_off, state_out)) return 1;
+    int avail = sgb_device_count();
+    if (n_devices < 1 || n_devices > avail) return fail("n_devices must be between 1 and the number of visible CUDA devices");
+    if (nseg == 0) return 0;
+    // contiguous blocks of sequences, balanced by bins
+    std::vector<int64_t> cut((size_t)n_devices + 1, nseg);
+    cut[0] = 0;
+    const int64_t total = seg_off[nseg] - seg_off[0];
+    int64_t s = 0;
+    for (int d = 1; d < n_devices; d++) {
+        const int64_t want = seg_off[0] + total * d / n_devices;
+        while (s < nseg && seg_off[s] < want) s++;
+        cut[(size_t)d] = s;
+    }
+    int prev = 0;
+    cudaGetDevice(&prev);
+    std::vector<int> rc((size_t)n_devices, 0);
+    std::vector<std::string> msg((size_t)n_devices);
+    std::vector<std::thread> th;
+    for (int d = 0; d < n_devices; d++) {
+        th.emplace_back([&, d]() {
+            if (cudaSetDevice(d) != cudaSuccess) { rc[(size_t)d] = 1; msg[(size_t)d] = "cudaSetDevice failed"; return; }
+            Ctx* C;
+            if (get_ctx(&C)) { rc[(size_t)d] = 1; msg[(size_t)d] = t_err; return; }
+            rc[(size_t)d] = decode_host_range(C, params, m, n, x, cn, cn_itemsize, seg_off, cut[(size_t)d],
+                                              cut[(size_t)d + 1], state_out, nullptr);
+            if (rc[(size_t)d]) msg[(size_t)d] = t_err;
+        });
+    }
+    for (auto& t : th) t.join();
+    cudaSetDevice(prev);
+    for (int d = 0; d < n_devices; d++)
+        if (rc[(size_t)d]) return fail("device " + std::to_string(d) + ": " + msg[(size_t)d]);
+    return 0;
+}
+
+// ---------------------------------------------------------------- device-resident path
+struct sgb_plan {
+    int device = 0;
+    int64_t N = 0;
+    int n_states = 0, decode = 0;
+    HostPlan hp;
+    DevBuf pstart, ostart, len, packed, bp, last_state;
+    unsigned int* counter = nullptr;
+    int* d_err = nullptr;
+    SgbDevTables* d_tabs = nullptr;
+    SgbPlanDev pd;
+};
+
+int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_states, int32_t decode,
+                    sgb_plan** plan_out)
+{
+    if (!plan_out) return fail("plan_out is NULL");
+    *plan_out = nullptr;
+    if (N < 0 || nseg < 0 || (nseg > 0 && !seg_off)) return fail("bad plan arguments");
+    if (n_states < 1 || n_states > SGB_MAX_STATES) return fail("n_states (maxCN+1) must be in 1..32");
+    if (nseg > 0 && (seg_off[0] < 0 || seg_off[nseg] > N)) return fail("seg_off out of range");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    sgb_plan* pl = new sgb_plan();
+    pl->device = C->device; pl->N = N; pl->n_states = n_states; pl->decode = decode;
+    if (build_host_plan(seg_off, 0, nseg, 0, pl->hp)) { delete pl; return 1; }
+    size_t ns = (size_t)pl->hp.nseq;
+    int bad = pl->pstart.reserve(ns * 8 + 16) || pl->ostart.reserve(ns * 8 + 16) || pl->len.reserve(ns * 4 + 16) ||
+              pl->packed.reserve((size_t)pl->hp.packed_len * 8 + 16);
+    if (!bad && decode == SGB_DECODE_CHAINED)
+        bad = pl->bp.reserve((size_t)N * n_states + 16) || pl->last_state.reserve(ns * 4 + 16);
+    if (bad) { sgb_plan_destroy(pl); return 1; }
+    cudaError_t e = cudaSuccess;
+    if (ns) {
+        e = cudaMemcpy(pl->pstart.p, pl->hp.pstart.data(), ns * 8, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->ostart.p, pl->hp.ostart.data(), ns * 8, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->len.p, pl->hp.len.data(), ns * 4, cudaMemcpyHostToDevice);
+    }
+    if (e == cudaSuccess) e = cudaMalloc(&pl->counter, sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMalloc(&pl->d_err, sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(pl->d_err, 0, sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&pl->d_tabs, sizeof(SgbDevTables));
+    if (e != cudaSuccess) {
+        sgb_plan_destroy(pl);
+        return fail(std::string("plan allocation failed: ") + cudaGetErrorString(e));
+    }
+    pl->pd.pstart = (const long long*)pl->pstart.p;
+    pl->pd.ostart = (const long long*)pl->ostart.p;
+    pl->pd.len = (const int*)pl->len.p;
+    pl->pd.nseq = pl->hp.nseq;
+    pl->pd.ngroups = (int)((pl->hp.nseq + 31) / 32);
+    *plan_out = pl;
+    return 0;
+}
+
+int sgb_plan_destroy(sgb_plan* pl)
+{
+    if (!pl) return 0;
+    pl->pstart.release(); pl->ostart.release(); pl->len.release(); pl->packed.release(); pl->bp.release();
+    pl->last_state.release();
+    if (pl->counter) cudaFree(pl->counter);
+    if (pl->d_err) cudaFree(pl->d_err);
+    if (pl->d_tabs) cudaFree(pl->d_tabs);
+    delete pl;
+    return 0;
+}
+
+int64_t sgb_plan_scratch_bytes(const sgb_plan* pl)
+{
+    if (!pl) return 0;
+    return (int64_t)(pl->packed.cap + pl->bp.cap + pl->last_state.cap + pl->pstart.cap + pl->ostart.cap + pl->len.cap);
+}
+
+int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t* d_n, const int32_t* d_x,
+                          const void* d_cn, int32_t cn_itemsize, uint8_t* d_state_out, double* d_loglik_out,
+                          void* stream)
+{
+    SgbModelArgs m;
+    if (check_params(params, m)) return 1;
+    if (!pl) return fail("plan is NULL");
+    if (cn_itemsize != 1 && cn_itemsize != 4) return fail("cn_itemsize must be 1 (uint8) or 4 (int32)");
+    if (m.S != pl->n_states) return fail("params.n_states differs from the plan's");
+    if (m.decode == SGB_DECODE_CHAINED && pl->decode != SGB_DECODE_CHAINED)
+        return fail("plan was created without backpointer scratch (decode = chained)");
+    if (pl->hp.nseq == 0) return 0;
+    if (!d_n || !d_x || !d_cn || !d_state_out) return fail("NULL device pointer");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    if (C->device != pl->device) return fail("plan belongs to another device");
+    cudaStream_t st = (cudaStream_t)stream;
+    SGB_CUDA(sgbk_setup(pl->d_tabs, m, params->eps, params->Abias, params->selftransitionprob, st));
+    SGB_CUDA(sgbk_pack(d_n, d_x, d_cn, cn_itemsize, pl->pd, (unsigned long long*)pl->packed.p, pl->d_err, st));
+    SGB_CUDA(sgbk_decode(pl->pd, (const unsigned long long*)pl->packed.p, pl->d_tabs, m, d_state_out,
+                         (uint8_t*)pl->bp.p, (int*)pl->last_state.p, pl->counter, C->sm_count, st));
+    if (m.decode == SGB_DECODE_CHAINED)
+        SGB_CUDA(sgbk_backtrace(pl->pd, (const uint8_t*)pl->bp.p, (const int*)pl->last_state.p, m.S, d_state_out, st));
+    if (d_loglik_out)
+        SGB_CUDA(sgbk_loglik(d_n, d_x, d_cn, cn_itemsize, pl->pd, pl->d_tabs, m, d_loglik_out, st));
+    return 0;
+}
+
+int sgb_plan_check(sgb_plan* pl, void* stream)
+{
+    if (!pl) return fail("plan is NULL");
+    SGB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    int bits = 0;
+    SGB_CUDA(cudaMemcpy(&bits, pl->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (bits) {
+        cudaMemset(pl->d_err, 0, sizeof(int));
+        return fail(err_bits_text(bits));
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------- viterbi / logspace_add / utilities
+int sgb_viterbi(const double* emission, int64_t nrow_e, const double* transition, const int32_t* observations,
+                int64_t T, int32_t S, int32_t init_mode, int32_t decode, int32_t* path_out)
+{
+    if (T < 0 || nrow_e < 0) return fail("negative size");
+    if (S < 1 || S > 128) return fail("viterbi: number of states must be in 1..128");
+    if (T == 0) return 0;
+    if (!emission || !transition || !observations || !path_out) return fail("NULL pointer");
+    if (decode != SGB_DECODE_REFERENCE && decode != SGB_DECODE_CHAINED) return fail("decode invalid");
+    for (int64_t t = 0; t < T; t++)
+        if (observations[t] < 1 || observations[t] > nrow_e) return fail("observations index outside the emission matrix");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    cudaStream_t st = C->main;
+    size_t eb = (size_t)nrow_e * S * 8, tb = (size_t)S * S * 8, ob = (size_t)T * 4;
+    if (C->scratch_a.reserve(eb + tb + 64) || C->scratch_b.reserve(2 * ob + 64)) return 1;
+    if (decode == SGB_DECODE_CHAINED && C->scratch_c.reserve(sgbk_viterbi_bp_bytes(T, S) + 64)) return 1;
+    double* d_em = (double*)C->scratch_a.p;
+    double* d_tr = d_em + (size_t)nrow_e * S;
+    int32_t* d_obs = (int32_t*)C->scratch_b.p;
+    int32_t* d_path = d_obs + T;
+    SGB_CUDA(cudaMemcpyAsync(d_em, emission, eb, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(cudaMemcpyAsync(d_tr, transition, tb, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(cudaMemcpyAsync(d_obs, observations, ob, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(sgbk_viterbi(d_em, nrow_e, d_tr, d_obs, T, S, init_mode, decode, (uint8_t*)C->scratch_c.p, d_path, st));
+    SGB_CUDA(cudaMemcpyAsync(path_out, d_path, ob, cudaMemcpyDeviceToHost, st));
+    SGB_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int sgb_logspace_add_vec(const double* logx, const double* logy, int64_t n, double* out)
+{
+    if (n < 0) return fail("negative size");
+    if (n == 0) return 0;
+    if (!logx || !logy || !out) return fail("NULL pointer");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    cudaStream_t st = C->main;
+    if (C->scratch_a.reserve((size_t)n * 24 + 64)) return 1;
+    double* d_a = (double*)C->scratch_a.p;
+    double* d_b = d_a + n;
+    double* d_o = d_b + n;
+    SGB_CUDA(cudaMemcpyAsync(d_a, logx, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(cudaMemcpyAsync(d_b, logy, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(sgbk_logspace_add(d_a, d_b, n, d_o, st));
+    SGB_CUDA(cudaMemcpyAsync(out, d_o, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    SGB_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int sgb_logspace_add(double logx, double logy, double* out)
+{
+    if (!out) return fail("NULL pointer");
+    return sgb_logspace_add_vec(&logx, &logy, 1, out);
+}
+
+int sgb_math_eval(int32_t fn, const double* in, const double* in2, int64_t n, double* out)
+{
+    if (n <= 0) return 0;
+    if (!in || !out) return fail("NULL pointer");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    cudaStream_t st = C->main;
+    if (C->scratch_a.reserve((size_t)n * 24 + 64)) return 1;
+    double* d_a = (double*)C->scratch_a.p;
+    double* d_b = d_a + n;
+    double* d_o = d_b + n;
+    SGB_CUDA(cudaMemcpyAsync(d_a, in, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(cudaMemcpyAsync(d_b, in2 ? in2 : in, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(sgbk_math_eval(fn, d_a, d_b, n, d_o, st));
+    SGB_CUDA(cudaMemcpyAsync(out, d_o, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    SGB_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int sgb_postprocess(int64_t N, const void* cn, int32_t cn_itemsize, const uint8_t* path, int32_t* A, int32_t* B,
+                    int32_t* state_min, uint8_t* loh, uint8_t* phase, uint8_t* state_phase, double* state_baf)
+{
+    if (N < 0) return fail("negative size");
+    if (N == 0) return 0;
+    if (cn_itemsize != 1 && cn_itemsize != 4) return fail("cn_itemsize must be 1 (uint8) or 4 (int32)");
+    if (!cn || !path || !A || !B || !state_min || !loh || !phase || !state_phase || !state_baf) return fail("NULL pointer");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    cudaStream_t st = C->main;
+    // chunked so the scratch stays modest for very long tables
+    const int64_t chunk = 16ll << 20;
+    if (C->scratch_a.reserve((size_t)std::min(N, chunk) * (cn_itemsize + 1) + 64)) return 1;
+    if (C->scratch_b.reserve((size_t)std::min(N, chunk) * 12 + 64)) return 1;
+    if (C->scratch_c.reserve((size_t)std::min(N, chunk) * 3 + 64)) return 1;
+    if (C->scratch_d.reserve((size_t)std::min(N, chunk) * 8 + 64)) return 1;
+    for (int64_t o = 0; o < N; o += chunk) {
+        const int64_t m = std::min(chunk, N - o);
+        char* d_cn = (char*)C->scratch_a.p;
+        uint8_t* d_path = (uint8_t*)d_cn + (size_t)m * cn_itemsize;
+        int32_t* d_A = (int32_t*)C->scratch_b.p;
+        int32_t* d_B = d_A + m;
+        int32_t* d_sm = d_B + m;
+        uint8_t* d_loh = (uint8_t*)C->scratch_c.p;
+        uint8_t* d_ph = d_loh + m;
+        uint8_t* d_sp = d_ph + m;
+        double* d_baf = (double*)C->scratch_d.p;
+        SGB_CUDA(cudaMemcpyAsync(d_cn, (const char*)cn + (size_t)o * cn_itemsize, (size_t)m * cn_itemsize, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(d_path, path + o, (size_t)m, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(sgbk_postprocess(d_cn, cn_itemsize, d_path, m, d_A, d_B, d_sm, d_loh, d_ph, d_sp, d_baf, st));
+        SGB_CUDA(cudaMemcpyAsync(A + o, d_A, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
+        SGB_CUDA(cudaMemcpyAsync(B + o, d_B, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
+        SGB_CUDA(cudaMemcpyAsync(state_min + o, d_sm, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
+        SGB_CUDA(cudaMemcpyAsync(loh + o, d_loh, (size_t)m, cudaMemcpyDeviceToHost, st));
+        SGB_CUDA(cudaMemcpyAsync(phase + o, d_ph, (size_t)m, cudaMemcpyDeviceToHost, st));
+        SGB_CUDA(cudaMemcpyAsync(state_phase + o, d_sp, (size_t)m, cudaMemcpyDeviceToHost, st));
+        SGB_CUDA(cudaMemcpyAsync(state_baf + o, d_baf, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
+        SGB_CUDA(cudaStreamSynchronize(st));
+    }
+    return 0;
+}
+
+int sgb_fp64_peak(int32_t iters, double* tflops_out)
+{
+    if (!tflops_out) return fail("NULL pointer");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    double tf = 0.0;
+    SGB_CUDA(sgbk_fp64_peak(iters, C->sm_count, C->main, &tf));
+    *tflops_out = tf;
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,577 @@
+// hmm_kernels.cu -- sm_100a kernels for the signals HSCN/ASCN HMM hot path.
+//
+//   k_setup        per-call constants (log p, log1p(-p), beta-binomial shapes, transitions) on the device
+//   k_pack         caller's flat int32/uint8 columns -> 8-byte records, sequences sorted by length
+//   k_decode       fused emission + max-plus forward recursion + the reference's decode rule
+//                  (one lane per (cell, chromosome) sequence, 32 sequences per warp)
+//   k_backtrace    opt-in textbook backtrace over uint8 backpointers (decode = chained)
+//   k_loglik       bins x states log-likelihood matrix `l` (HaplotypeHMM()$l, alleleHMM()$l)
+//   k_viterbi      stand-alone viterbi(emission, transition, observations), dense S x S transition
+//   k_logspace_add, k_math_eval, k_postprocess   small element-wise kernels
+//
+// Reference functions replaced: src/code.cpp:5-45, R/callHSCN.R:36-108,135-172,217-295,
+// R/callASCN.R:41-103,128-161 (see hmm_core.cuh for the arithmetic and DESIGN.md for the design).
+#include "kernels.h"
+
+__device__ const double g_logtab[SGB_LOGTAB_LEN] = SGB_LOGTAB_INIT;
+__device__ const double g_exptab[SGB_EXPTAB_LEN] = SGB_EXPTAB_INIT;
+__device__ const double g_lftab[SGB_LFTAB_LEN] = SGB_LFTAB_INIT;
+
+#define SGB_FULL 0xffffffffu
+#define SGB_COUNT_MASK ((1ull << SGB_COUNT_BITS) - 1ull)
+
+// ------------------------------------------------------------------ k_setup
+__global__ void k_setup(SgbDevTables* T, SgbModelArgs m, double eps, double Abias, double stp)
+{
+    __shared__ double s_bb;
+    if (threadIdx.x == 0) {
+        SgbScalars sp = sgb_scalars(m.S, eps, Abias, stp, m.lik_bb ? m.rho : 0.0, g_logtab);
+        T->sp = sp;
+        s_bb = sp.bb_s;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < SGB_CN_TABLE * SGB_MAX_STATES; idx += blockDim.x) {
+        int c = idx / SGB_MAX_STATES, s = idx % SGB_MAX_STATES;
+        SgbStateConst sc = sgb_state_const(c, s, m.loherror, m.lik_bb ? SGB_LIK_BETABINOMIAL : SGB_LIK_BINOMIAL,
+                                           m.rho, s_bb, g_logtab);
+        T->lp[idx] = sc.lp; T->lq[idx] = sc.lq; T->a[idx] = sc.a; T->b[idx] = sc.b; T->l0[idx] = sc.l0;
+        T->kind[idx] = sc.kind;
+    }
+}
+
+cudaError_t sgbk_setup(SgbDevTables* d_tabs, const SgbModelArgs& m, double eps, double Abias, double stp,
+                       cudaStream_t st)
+{
+    k_setup<<<1, 256, 0, st>>>(d_tabs, m, eps, Abias, stp);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ k_pack
+// One warp per sequence, lanes over consecutive bins: coalesced 128 B reads of n / x, 32 B of cn,
+// coalesced 256 B record writes.  Counts are validated here (device side).
+__global__ void __launch_bounds__(256) k_pack(const int32_t* __restrict__ n, const int32_t* __restrict__ x,
+                                              const void* __restrict__ cn, int cn_itemsize, SgbPlanDev plan,
+                                              unsigned long long* __restrict__ packed, int* err)
+{
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    int bad = 0;
+    for (long long r = warp; r < plan.nseq; r += nwarps) {
+        const long long o = plan.ostart[r], p = plan.pstart[r];
+        const int len = plan.len[r];
+        for (int t = lane; t < len; t += 32) {
+            int nv = n[o + t], xv = x[o + t];
+            int cv = (cn_itemsize == 1) ? (int)((const uint8_t*)cn)[o + t] : ((const int32_t*)cn)[o + t];
+            if (nv < 0 || xv < 0) bad |= SGB_ERR_NEGATIVE_COUNT;
+            if (nv >= (1 << SGB_COUNT_BITS) || xv >= (1 << SGB_COUNT_BITS)) bad |= SGB_ERR_COUNT_TOO_LARGE;
+            if (cv < 0 || cv > 255) bad |= SGB_ERR_BAD_CN;
+            packed[p + t] = ((unsigned long long)(unsigned)nv & SGB_COUNT_MASK) |
+                            (((unsigned long long)(unsigned)xv & SGB_COUNT_MASK) << SGB_COUNT_BITS) |
+                            ((unsigned long long)(cv & 255) << 56);
+        }
+    }
+    if (bad) atomicOr(err, bad);
+}
+
+cudaError_t sgbk_pack(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,
+                      const SgbPlanDev& plan, unsigned long long* d_packed, int* d_err, cudaStream_t st)
+{
+    if (plan.nseq == 0) return cudaSuccess;
+    long long blocks = (plan.nseq + 7) / 8;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_pack<<<(unsigned)blocks, 256, 0, st>>>(d_n, d_x, d_cn, cn_itemsize, plan, d_packed, d_err);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ k_decode
+struct SgbDecodeArgs {
+    SgbPlanDev plan;
+    const unsigned long long* packed;
+    const SgbDevTables* tabs;
+    uint8_t* state_out;
+    uint8_t* bp;            // chained only: [(row)*S + state]
+    int* last_state;        // chained only: [nseq]
+    unsigned int* counter;  // dynamic group scheduler
+    int S, lik;
+    double loherror, rho;
+};
+
+#define SGB_DECODE_THREADS 256
+#define SGB_DECODE_WARPS (SGB_DECODE_THREADS / 32)
+
+static inline size_t decode_smem_bytes(int SMAX, int S, int lik_bb)
+{
+    size_t d = SGB_LOGTAB_LEN + SGB_EXPTAB_LEN + SGB_LFTAB_LEN;
+    d += (size_t)SGB_CN_TABLE * S * (lik_bb ? 5 : 2);
+    d += (size_t)SGB_DECODE_WARPS * SMAX * 32;
+    return d * sizeof(double) + (size_t)SGB_CN_TABLE * S * sizeof(int);
+}
+
+template <int SMAX, int MODEL, int LIKBB, int CHAINED>
+__global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs A)
+{
+    extern __shared__ __align__(16) double smem[];
+    const int S = A.S;
+    const int CTS = SGB_CN_TABLE * S;
+    double* sLT = smem;
+    double* sET = sLT + SGB_LOGTAB_LEN;
+    double* sLF = sET + SGB_EXPTAB_LEN;
+    double* sLP = sLF + SGB_LFTAB_LEN;
+    double* sLQ = sLP + CTS;
+    double* sA = sLQ + CTS;
+    double* sB = sA + (LIKBB ? CTS : 0);
+    double* sL0 = sB + (LIKBB ? CTS : 0);
+    double* sE = sL0 + (LIKBB ? CTS : 0);
+    int* sKind = (int*)(sE + SGB_DECODE_WARPS * SMAX * 32);
+
+    for (int i = threadIdx.x; i < SGB_LOGTAB_LEN; i += blockDim.x) sLT[i] = g_logtab[i];
+    for (int i = threadIdx.x; i < SGB_EXPTAB_LEN; i += blockDim.x) sET[i] = g_exptab[i];
+    for (int i = threadIdx.x; i < SGB_LFTAB_LEN; i += blockDim.x) sLF[i] = g_lftab[i];
+    for (int i = threadIdx.x; i < CTS; i += blockDim.x) {
+        int c = i / S, s = i - c * S, src = c * SGB_MAX_STATES + s;
+        sLP[i] = A.tabs->lp[src];
+        sLQ[i] = A.tabs->lq[src];
+        sKind[i] = A.tabs->kind[src];
+        if (LIKBB) { sA[i] = A.tabs->a[src]; sB[i] = A.tabs->b[src]; sL0[i] = A.tabs->l0[src]; }
+    }
+    const SgbScalars sp = A.tabs->sp;
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    const int wid = threadIdx.x >> 5;
+    double* myE = sE + wid * SMAX * 32;
+    const double NEG_INF = -sgb_inf();
+
+    for (;;) {
+        int g = 0;
+        if (lane == 0) g = (int)atomicAdd(A.counter, 1u);
+        g = __shfl_sync(SGB_FULL, g, 0);
+        if (g >= A.plan.ngroups) break;
+        const long long r = (long long)g * 32 + lane;
+        int len = 0;
+        long long ostart = 0;
+        const unsigned long long* prow = A.packed;
+        if (r < A.plan.nseq) {
+            len = A.plan.len[r];
+            ostart = A.plan.ostart[r];
+            prow = A.packed + A.plan.pstart[r];
+        }
+        const int Tmax = __reduce_max_sync(SGB_FULL, len);
+        SgbSeqState<SMAX> st;
+#pragma unroll
+        for (int i = 0; i < SMAX; i++) st.T1[i] = NEG_INF;
+        st.m1 = NEG_INF; st.m2 = NEG_INF; st.i1 = 0;
+        unsigned long long rec_next = (len > 0) ? __ldg(prow) : 0ull;
+        int back = 0;
+        for (int t = 0; t < Tmax; t++) {
+            const bool act = t < len;
+            const unsigned long long rec = rec_next;
+            if (t + 1 < len) rec_next = __ldg(prow + t + 1);
+            SgbBin b;
+            int L = 0;
+            if (act) {
+                b = sgb_bin_prepare(MODEL, LIKBB, (int)(rec & SGB_COUNT_MASK),
+                                    (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK), (int)(rec >> 56), sp.bb_s, sLF,
+                                    sLT);
+                L = sgb_live_states(MODEL, b.cprime, S);
+            }
+            const int Lw = __reduce_max_sync(SGB_FULL, L);
+            // ---- emission of the live states (masked states are -Inf by construction)
+            for (int i = 0; i < Lw; i++) {
+                if (i < L) {
+                    SgbStateConst sc;
+                    if (b.cprime < SGB_CN_TABLE) {
+                        const int ti = b.cprime * S + i;
+                        sc.lp = sLP[ti]; sc.lq = sLQ[ti]; sc.kind = sKind[ti];
+                        if (LIKBB) { sc.a = sA[ti]; sc.b = sB[ti]; sc.l0 = sL0[ti]; }
+                        else { sc.a = 0.0; sc.b = 0.0; sc.l0 = 0.0; }
+                    } else {
+                        sc = sgb_state_const(b.cprime, i, A.loherror, A.lik, A.rho, sp.bb_s, sLT);
+                    }
+                    myE[i * 32 + lane] = sgb_emission(MODEL, LIKBB, b, i, sc, sp, sLT, sET);
+                }
+            }
+            __syncwarp();
+            // ---- forward recursion + decode
+            if (act) {
+                double e[SMAX];
+#pragma unroll
+                for (int i = 0; i < SMAX; i++) e[i] = (i < L) ? myE[i * 32 + lane] : NEG_INF;
+                if (t == 0) {
+                    sgb_seq_init<SMAX>(st, e, S, sp.init);
+                    if (CHAINED == 0 && len == 1) A.state_out[ostart] = 0;
+                } else if (CHAINED == 0) {
+                    back = sgb_seq_step<SMAX>(st, e, S, sp.tr_self, sp.tr_off);
+                    A.state_out[ostart + t - 1] = (uint8_t)back;
+                    if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
+                } else {
+                    unsigned char bpv[SMAX];
+                    sgb_seq_step_chained<SMAX>(st, e, S, sp.tr_self, sp.tr_off, bpv);
+                    uint8_t* dst = A.bp + (ostart + t) * (long long)S;
+#pragma unroll
+                    for (int i = 0; i < SMAX; i++) if (i < S) dst[i] = bpv[i];
+                }
+            }
+            __syncwarp();
+        }
+        if (CHAINED && r < A.plan.nseq) A.last_state[r] = st.i1;
+    }
+}
+
+template <int SMAX, int MODEL, int LIKBB, int CHAINED>
+static cudaError_t launch_decode(const SgbDecodeArgs& A, int sm_count, cudaStream_t st)
+{
+    size_t smem = decode_smem_bytes(SMAX, A.S, LIKBB);
+    auto kern = k_decode<SMAX, MODEL, LIKBB, CHAINED>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int blocks = (A.plan.ngroups + SGB_DECODE_WARPS - 1) / SGB_DECODE_WARPS;
+    int cap = sm_count * 2;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    kern<<<blocks, SGB_DECODE_THREADS, smem, st>>>(A);
+    return cudaGetLastError();
+}
+
+template <int SMAX>
+static cudaError_t dispatch_decode(const SgbDecodeArgs& A, const SgbModelArgs& m, int sm_count, cudaStream_t st)
+{
+    const int ch = m.decode == SGB_DECODE_CHAINED;
+#define SGB_CASE(MD, LK, CH) \
+    if (m.model == MD && m.lik_bb == LK && ch == CH) return launch_decode<SMAX, MD, LK, CH>(A, sm_count, st);
+    SGB_CASE(0, 0, 0) SGB_CASE(0, 1, 0) SGB_CASE(1, 0, 0) SGB_CASE(1, 1, 0)
+    SGB_CASE(0, 0, 1) SGB_CASE(0, 1, 1) SGB_CASE(1, 0, 1) SGB_CASE(1, 1, 1)
+#undef SGB_CASE
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_packed, const SgbDevTables* d_tabs,
+                        const SgbModelArgs& m, uint8_t* d_state_out, uint8_t* d_bp, int* d_last_state,
+                        unsigned int* d_counter, int sm_count, cudaStream_t st)
+{
+    if (plan.nseq == 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(d_counter, 0, sizeof(unsigned int), st);
+    if (e != cudaSuccess) return e;
+    SgbDecodeArgs A;
+    A.plan = plan; A.packed = d_packed; A.tabs = d_tabs; A.state_out = d_state_out; A.bp = d_bp;
+    A.last_state = d_last_state; A.counter = d_counter; A.S = m.S;
+    A.lik = m.lik_bb ? SGB_LIK_BETABINOMIAL : SGB_LIK_BINOMIAL;
+    A.loherror = m.loherror; A.rho = m.rho;
+    if (m.S <= 12) return dispatch_decode<12>(A, m, sm_count, st);
+    if (m.S <= SGB_MAX_STATES) return dispatch_decode<SGB_MAX_STATES>(A, m, sm_count, st);
+    return cudaErrorInvalidValue;
+}
+
+// ------------------------------------------------------------------ k_backtrace (decode = chained)
+__global__ void k_backtrace(SgbPlanDev plan, const uint8_t* __restrict__ bp, const int* __restrict__ last_state,
+                            int S, uint8_t* __restrict__ state_out)
+{
+    long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= plan.nseq) return;
+    const int len = plan.len[r];
+    if (len <= 0) return;
+    const long long o = plan.ostart[r];
+    int cur = last_state[r];
+    state_out[o + len - 1] = (uint8_t)cur;
+    for (int t = len - 1; t > 0; t--) {
+        cur = bp[(o + t) * (long long)S + cur];
+        state_out[o + t - 1] = (uint8_t)cur;
+    }
+}
+
+cudaError_t sgbk_backtrace(const SgbPlanDev& plan, const uint8_t* d_bp, const int* d_last_state, int S,
+                           uint8_t* d_state_out, cudaStream_t st)
+{
+    if (plan.nseq == 0) return cudaSuccess;
+    k_backtrace<<<(unsigned)((plan.nseq + 127) / 128), 128, 0, st>>>(plan, d_bp, d_last_state, S, d_state_out);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ k_loglik  (K4: the `l` matrix)
+// Output layout: for the sequence starting at row o with T bins, a T x S column-major block at l + o*S
+// (what R holds as HaplotypeHMM()$l for that chromosome).
+__global__ void __launch_bounds__(256) k_loglik(const int32_t* __restrict__ n, const int32_t* __restrict__ x,
+                                                const void* __restrict__ cn, int cn_itemsize, SgbPlanDev plan,
+                                                const SgbDevTables* __restrict__ tabs, SgbModelArgs m,
+                                                double* __restrict__ l)
+{
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const SgbScalars sp = tabs->sp;
+    const int S = m.S;
+    for (long long r = warp; r < plan.nseq; r += nwarps) {
+        const long long o = plan.ostart[r];
+        const int len = plan.len[r];
+        for (int t = lane; t < len; t += 32) {
+            int cv = (cn_itemsize == 1) ? (int)((const uint8_t*)cn)[o + t] : ((const int32_t*)cn)[o + t];
+            SgbBin b = sgb_bin_prepare(m.model, m.lik_bb, n[o + t], x[o + t], cv, sp.bb_s, g_lftab, g_logtab);
+            const int L = sgb_live_states(m.model, b.cprime, S);
+            for (int i = 0; i < S; i++) {
+                double e = -sgb_inf();
+                if (i < L) {
+                    SgbStateConst sc = sgb_state_const(b.cprime, i, m.loherror,
+                                                       m.lik_bb ? SGB_LIK_BETABINOMIAL : SGB_LIK_BINOMIAL, m.rho,
+                                                       sp.bb_s, g_logtab);
+                    e = sgb_emission(m.model, m.lik_bb, b, i, sc, sp, g_logtab, g_exptab);
+                }
+                l[o * S + t + (long long)len * i] = e;
+            }
+        }
+    }
+}
+
+cudaError_t sgbk_loglik(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,
+                        const SgbPlanDev& plan, const SgbDevTables* d_tabs, const SgbModelArgs& m, double* d_l,
+                        cudaStream_t st)
+{
+    if (plan.nseq == 0) return cudaSuccess;
+    long long blocks = (plan.nseq + 7) / 8;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_loglik<<<(unsigned)blocks, 256, 0, st>>>(d_n, d_x, d_cn, cn_itemsize, plan, d_tabs, m, d_l);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ k_viterbi  (K3: src/code.cpp:11-45)
+// One warp for the sequence; lane i owns target states i, i+32, ...; the S x S log transition matrix sits
+// in shared memory transposed to [from][to] rows so a warp reads it conflict-free; the previous T1 column
+// is double-buffered in shared memory; the column argmax is a shuffle reduction ordered by
+// (value descending, index ascending) = "first maximum".  uint8 backpointers go to global scratch only in
+// chained mode.  NaN emissions are treated as -Inf (the reference's behaviour there is undefined).
+#define SGB_VIT_MAX_STATES 128
+__global__ void __launch_bounds__(32) k_viterbi(const double* __restrict__ em, long long nrow_e,
+                                                const double* __restrict__ tr, const int32_t* __restrict__ obs,
+                                                long long T, int S, int init_mode, int decode,
+                                                uint8_t* __restrict__ bp, int32_t* __restrict__ path)
+{
+    extern __shared__ __align__(16) double vsm[];
+    double* trS = vsm;                 // [from k][to i]
+    double* T1a = trS + (size_t)S * S;
+    double* T1b = T1a + S;
+    const int lane = threadIdx.x;
+    const double NEG_INF = -sgb_inf();
+    for (int idx = lane; idx < S * S; idx += 32) {
+        int k = idx % S, i = idx / S;          // tr is column-major [from=k, to=i]
+        trS[k * S + i] = tr[idx];
+    }
+    const double init = (init_mode == 0) ? -sgb_log((double)S, g_logtab)
+                                         : sgb_log(sgb_div(1.0, (double)S), g_logtab);
+    {
+        const long long row = (long long)obs[0] - 1;
+        for (int i = lane; i < S; i += 32) {
+            double e = em[row + nrow_e * i];
+            if (e != e) e = NEG_INF;
+            T1a[i] = sgb_add(init, e);
+        }
+    }
+    __syncwarp();
+    double* cur = T1a;
+    double* nxt = T1b;
+    int back = 0;
+    for (long long t = 1; t < T; t++) {
+        const long long row = (long long)obs[t] - 1;
+        double lbest = NEG_INF;
+        int lidx = 0x7fffffff, lt2 = 0;
+        for (int i = lane; i < S; i += 32) {
+            double e = em[row + nrow_e * i];
+            if (e != e) e = NEG_INF;
+            double best = sgb_add(sgb_add(cur[0], trS[i]), e);
+            int arg = 0;
+            for (int k = 1; k < S; k++) {
+                double v = sgb_add(sgb_add(cur[k], trS[k * S + i]), e);
+                if (v > best) { best = v; arg = k; }
+            }
+            nxt[i] = best;
+            if (decode == SGB_DECODE_CHAINED) bp[t * S + i] = (uint8_t)arg;
+            if (lidx == 0x7fffffff || best > lbest) { lbest = best; lidx = i; lt2 = arg; }
+        }
+        // warp argmax: larger value wins, equal values -> smaller state index ("first maximum")
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            double ov = __shfl_xor_sync(SGB_FULL, lbest, off);
+            int oi = __shfl_xor_sync(SGB_FULL, lidx, off);
+            int ot = __shfl_xor_sync(SGB_FULL, lt2, off);
+            bool take = (oi != 0x7fffffff) && (lidx == 0x7fffffff || ov > lbest || (ov == lbest && oi < lidx));
+            if (take) { lbest = ov; lidx = oi; lt2 = ot; }
+        }
+        back = lt2;
+        if (decode == SGB_DECODE_REFERENCE && lane == 0) path[t - 1] = back;
+        __syncwarp();
+        double* tmp = cur; cur = nxt; nxt = tmp;
+    }
+    if (decode == SGB_DECODE_REFERENCE) {
+        if (lane == 0) path[T - 1] = (T > 1) ? back : 0;
+    } else {
+        // final column argmax, then follow the backpointers
+        double lbest = NEG_INF;
+        int lidx = 0x7fffffff;
+        for (int i = lane; i < S; i += 32) {
+            double v = cur[i];
+            if (lidx == 0x7fffffff || v > lbest) { lbest = v; lidx = i; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            double ov = __shfl_xor_sync(SGB_FULL, lbest, off);
+            int oi = __shfl_xor_sync(SGB_FULL, lidx, off);
+            bool take = (oi != 0x7fffffff) && (lidx == 0x7fffffff || ov > lbest || (ov == lbest && oi < lidx));
+            if (take) { lbest = ov; lidx = oi; }
+        }
+        __syncwarp();
+        if (lane == 0) {
+            int c = lidx;
+            path[T - 1] = c;
+            for (long long t = T - 1; t > 0; t--) {
+                c = bp[t * S + c];
+                path[t - 1] = c;
+            }
+        }
+    }
+}
+
+size_t sgbk_viterbi_bp_bytes(long long T, int S) { return (size_t)T * (size_t)S; }
+
+cudaError_t sgbk_viterbi(const double* d_emission, long long nrow_e, const double* d_trans, const int32_t* d_obs,
+                         long long T, int S, int init_mode, int decode, uint8_t* d_bp, int32_t* d_path,
+                         cudaStream_t st)
+{
+    if (S < 1 || S > SGB_VIT_MAX_STATES) return cudaErrorInvalidValue;
+    if (T <= 0) return cudaSuccess;
+    size_t smem = ((size_t)S * S + 2 * (size_t)S) * sizeof(double);
+    cudaError_t e = cudaFuncSetAttribute(k_viterbi, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_viterbi<<<1, 32, smem, st>>>(d_emission, nrow_e, d_trans, d_obs, T, S, init_mode, decode, d_bp, d_path);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ small element-wise kernels
+__global__ void k_logspace_add(const double* __restrict__ a, const double* __restrict__ b, long long n,
+                               double* __restrict__ out)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = sgb_logspace_add(a[i], b[i], g_logtab, g_exptab);
+}
+
+cudaError_t sgbk_logspace_add(const double* d_a, const double* d_b, long long n, double* d_out, cudaStream_t st)
+{
+    if (n <= 0) return cudaSuccess;
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_logspace_add<<<(unsigned)blocks, 256, 0, st>>>(d_a, d_b, n, d_out);
+    return cudaGetLastError();
+}
+
+// test hook: evaluate one deterministic primitive on the device (fn codes as in oracle orc_math_eval)
+__global__ void k_math_eval(int fn, const double* __restrict__ in, const double* __restrict__ in2, long long n,
+                            double* __restrict__ out)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        double x = in[i], r;
+        switch (fn) {
+        case 0: r = sgb_exp(x, g_exptab); break;
+        case 1: r = sgb_log(x, g_logtab); break;
+        case 2: r = sgb_log1p_01(x, g_logtab); break;
+        case 3: r = sgb_log1p(x, g_logtab); break;
+        case 4: r = sgb_lgamma(x, g_logtab); break;
+        case 5: r = sgb_logspace_add(x, in2[i], g_logtab, g_exptab); break;
+        case 6: r = sgb_logfact((int64_t)x, g_lftab, g_logtab); break;
+        default: r = sgb_nan();
+        }
+        out[i] = r;
+    }
+}
+
+cudaError_t sgbk_math_eval(int fn, const double* d_in, const double* d_in2, long long n, double* d_out,
+                           cudaStream_t st)
+{
+    if (n <= 0) return cudaSuccess;
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_math_eval<<<(unsigned)blocks, 256, 0, st>>>(fn, d_in, d_in2, n, d_out);
+    return cudaGetLastError();
+}
+
+// Post-decode table columns (R/callHSCN.R:282-290 clamp block; numeric part of add_states R/util.R:1078-1097;
+// the ASCN block R/callASCN.R:416-447 reduces to the same arithmetic).  Codes:
+//   phase 0 Balanced / 1 A / 2 B ; state_phase 0 Balanced 1 A-Gained 2 B-Gained 3 A-Hom 4 B-Hom ; LOH 1/0
+__global__ void k_postprocess(const void* __restrict__ cn, int cn_itemsize, const uint8_t* __restrict__ path,
+                              long long N, int32_t* __restrict__ A, int32_t* __restrict__ B,
+                              int32_t* __restrict__ state_min, uint8_t* __restrict__ loh,
+                              uint8_t* __restrict__ phase, uint8_t* __restrict__ state_phase,
+                              double* __restrict__ state_baf)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (long long)gridDim.x * blockDim.x) {
+        int st = (cn_itemsize == 1) ? (int)((const uint8_t*)cn)[i] : ((const int32_t*)cn)[i];
+        int sm = path[i];
+        int a = st - sm, b = sm;
+        if (b < 0) b = 0;
+        if (a < 0) a = 0;
+        if (b > st) b = st;
+        if (a > st) a = st;
+        A[i] = a; B[i] = b;
+        int mn = a < b ? a : b;
+        state_min[i] = mn;
+        loh[i] = (uint8_t)(mn == 0);
+        phase[i] = (uint8_t)((b < a) ? 1 : (b > a) ? 2 : 0);
+        state_phase[i] = (uint8_t)(1 * ((b < a) && (b != 0)) + 2 * ((b > a) && (a != 0)) +
+                                   3 * ((b < a) && (b == 0)) + 4 * ((b > a) && (a == 0)));
+        double q = sgb_div(sgb_div((double)b, (double)st), 0.1);
+        double baf = sgb_mul(rint(q), 0.1);
+        if (baf != baf) baf = 0.5;
+        state_baf[i] = baf;
+    }
+}
+
+cudaError_t sgbk_postprocess(const void* d_cn, int cn_itemsize, const uint8_t* d_path, long long N, int32_t* d_A,
+                             int32_t* d_B, int32_t* d_state_min, uint8_t* d_loh, uint8_t* d_phase,
+                             uint8_t* d_state_phase, double* d_state_baf, cudaStream_t st)
+{
+    if (N <= 0) return cudaSuccess;
+    long long blocks = (N + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_postprocess<<<(unsigned)blocks, 256, 0, st>>>(d_cn, cn_itemsize, d_path, N, d_A, d_B, d_state_min, d_loh,
+                                                    d_phase, d_state_phase, d_state_baf);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ FP64 roofline denominator
+// Dependent-chain-free DFMA loop: 8 accumulators per thread, 16 warps per SM resident.
+__global__ void __launch_bounds__(256) k_fp64_peak(double* out, int n_iter)
+{
+    double a0 = threadIdx.x * 1e-9, a1 = a0 + 1e-3, a2 = a0 + 2e-3, a3 = a0 + 3e-3;
+    double a4 = a0 + 4e-3, a5 = a0 + 5e-3, a6 = a0 + 6e-3, a7 = a0 + 7e-3;
+    const double b = 0.9999999, c = 1e-9;
+    for (int i = 0; i < n_iter; i++) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            a0 = __fma_rn(a0, b, c); a1 = __fma_rn(a1, b, c); a2 = __fma_rn(a2, b, c); a3 = __fma_rn(a3, b, c);
+            a4 = __fma_rn(a4, b, c); a5 = __fma_rn(a5, b, c); a6 = __fma_rn(a6, b, c); a7 = __fma_rn(a7, b, c);
+        }
+    }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+}
+
+cudaError_t sgbk_fp64_peak(int iters, int sm_count, cudaStream_t st, double* tflops)
+{
+    const int blocks = sm_count * 8, threads = 256, n_iter = 4096;
+    double* d_out = nullptr;
+    cudaError_t e = cudaMalloc(&d_out, (size_t)blocks * threads * sizeof(double));
+    if (e != cudaSuccess) return e;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    k_fp64_peak<<<blocks, threads, 0, st>>>(d_out, n_iter);
+    k_fp64_peak<<<blocks, threads, 0, st>>>(d_out, n_iter);
+    cudaEventRecord(e0, st);
+    if (iters < 1) iters = 1;
+    for (int i = 0; i < iters; i++) k_fp64_peak<<<blocks, threads, 0, st>>>(d_out, n_iter);
+    cudaEventRecord(e1, st);
+    e = cudaEventSynchronize(e1);
+    float ms = 0.f;
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return e;
+    const double flops = (double)blocks * threads * (double)n_iter * 32.0 * 2.0 * (double)iters;
+    *tflops = flops / ((double)ms * 1e-3) / 1e12;
+    return cudaGetLastError();
+}

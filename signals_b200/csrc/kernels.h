@@ -1,0 +1,62 @@
+// kernels.h -- host-side launch interface of the sm_100a kernels (hmm_kernels.cu).
+// Internal to the library; the public boundary is include/signals_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "hmm_core.cuh"
+
+// Per-call constants computed ON THE DEVICE by k_setup (so they carry device bits):
+// scalar parameters plus the per-(total CN, state) tables for total CN < SGB_CN_TABLE.
+struct SgbDevTables {
+    SgbScalars sp;
+    double lp[SGB_CN_TABLE * SGB_MAX_STATES];
+    double lq[SGB_CN_TABLE * SGB_MAX_STATES];
+    double a[SGB_CN_TABLE * SGB_MAX_STATES];
+    double b[SGB_CN_TABLE * SGB_MAX_STATES];
+    double l0[SGB_CN_TABLE * SGB_MAX_STATES];
+    int kind[SGB_CN_TABLE * SGB_MAX_STATES];
+};
+
+// A "plan" describes the (cell, chromosome) sequences of one batch, sorted by length
+// (longest first) and grouped 32 to a warp; see DESIGN.md "HBM layout".
+struct SgbPlanDev {
+    const long long* pstart;   // [nseq] first record of the sequence in the packed buffer (even => 16 B aligned)
+    const long long* ostart;   // [nseq] first row of the sequence in the caller's n/x/cn/state arrays
+    const int* len;            // [nseq] number of bins
+    long long nseq;
+    int ngroups;               // ceil(nseq / 32)
+};
+
+struct SgbModelArgs {
+    int model, lik_bb, S, decode;
+    double loherror, rho;
+};
+
+// error bits raised by k_pack (validated on the device so the host never touches the counts)
+#define SGB_ERR_NEGATIVE_COUNT 1
+#define SGB_ERR_COUNT_TOO_LARGE 2
+#define SGB_ERR_BAD_CN 4
+
+cudaError_t sgbk_setup(SgbDevTables* d_tabs, const SgbModelArgs& m, double eps, double Abias, double stp,
+                       cudaStream_t st);
+cudaError_t sgbk_pack(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,
+                      const SgbPlanDev& plan, unsigned long long* d_packed, int* d_err, cudaStream_t st);
+cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_packed, const SgbDevTables* d_tabs,
+                        const SgbModelArgs& m, uint8_t* d_state_out, uint8_t* d_bp, int* d_last_state,
+                        unsigned int* d_counter, int sm_count, cudaStream_t st);
+cudaError_t sgbk_backtrace(const SgbPlanDev& plan, const uint8_t* d_bp, const int* d_last_state, int S,
+                           uint8_t* d_state_out, cudaStream_t st);
+cudaError_t sgbk_loglik(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,
+                        const SgbPlanDev& plan, const SgbDevTables* d_tabs, const SgbModelArgs& m,
+                        double* d_l, cudaStream_t st);
+cudaError_t sgbk_viterbi(const double* d_emission, long long nrow_e, const double* d_trans, const int32_t* d_obs,
+                         long long T, int S, int init_mode, int decode, uint8_t* d_bp, int32_t* d_path,
+                         cudaStream_t st);
+cudaError_t sgbk_logspace_add(const double* d_a, const double* d_b, long long n, double* d_out, cudaStream_t st);
+cudaError_t sgbk_math_eval(int fn, const double* d_in, const double* d_in2, long long n, double* d_out,
+                           cudaStream_t st);
+cudaError_t sgbk_postprocess(const void* d_cn, int cn_itemsize, const uint8_t* d_path, long long N, int32_t* d_A,
+                             int32_t* d_B, int32_t* d_state_min, uint8_t* d_loh, uint8_t* d_phase,
+                             uint8_t* d_state_phase, double* d_state_baf, cudaStream_t st);
+size_t sgbk_viterbi_bp_bytes(long long T, int S);
+cudaError_t sgbk_fp64_peak(int iters, int sm_count, cudaStream_t st, double* tflops);

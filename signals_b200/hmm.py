@@ -1,0 +1,314 @@
+"""Host-side mirror of the reference's R interface for the HSCN / ASCN HMM path.
+
+The reference is an R package; R is not available where this repository is built and tested,
+so the host layer above the C ABI is written in Python with the SAME function names, argument
+names, defaults and return shapes as the R functions it stands in for (the R shim a maintainer
+drops into the package is in rpkg/):
+
+    logspace_addcpp(logx, logy)                         src/code.cpp:5-8, R/RcppExports.R:4-6
+    logspace_add(logx, logy)                            R/callASCN.R:9-11
+    viterbi(emission, transition, observations)         src/code.cpp:11-45, R/RcppExports.R:8-10
+    viterbiR(emission, transition, observations)        R/viterbi.R:1-34
+    HaplotypeHMM(...)                                   R/callHSCN.R:36-108
+    alleleHMM(...)                                      R/callASCN.R:41-103
+    assignHaplotypeHMM(CNBAF, minor_cn, ...)            R/callHSCN.R:135-172
+    assignalleleHMM(CNBAF, minor_cn, ...)               R/callASCN.R:128-161
+    callHaplotypeSpecificCN_(CNBAF, ...)                R/callHSCN.R:217-295  (.callHaplotypeSpecificCN_)
+    callAlleleSpecificCN_(CNBAF, ...)                   R/callASCN.R:372-447  (pass-2 loop + post block)
+    add_states(df)                                      R/util.R:1078-1097
+
+All numerics run on the GPU through libsignals_b200.so; nothing here computes a likelihood or a
+state path on the CPU, and there is no fallback when the library or a device is missing.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from . import _lib
+from ._lib import SignalsB200Error, check, make_params  # noqa: F401
+
+
+def _ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def _as_counts(a, name):
+    a = np.asarray(a)
+    if a.dtype.kind == "f":
+        if a.size and (np.isnan(a).any() or (np.rint(a) != a).any()):
+            raise ValueError("%s must be integer valued" % name)
+    if a.size and (a.max() > 2 ** 31 - 1 or a.min() < -2 ** 31):
+        raise ValueError("%s does not fit in a 32-bit integer" % name)
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _check_minor_cn(minor_cn):
+    m = np.asarray(minor_cn, dtype=np.float64)
+    if m.ndim != 1 or m.size < 1 or not np.array_equal(m, np.arange(m.size)):
+        raise NotImplementedError("the GPU path requires minor_cn = 0:maxCN (as every reference driver passes, "
+                                  "R/callHSCN.R:232)")
+    if m.size > 32:
+        raise NotImplementedError("maxCN > 31 is not supported by the fused kernels")
+    return int(m.size)
+
+
+# ---------------------------------------------------------------------------------- Rcpp exports
+def logspace_addcpp(logx, logy):
+    out = ctypes.c_double(0.0)
+    check(_lib.load().sgb_logspace_add(float(logx), float(logy), ctypes.byref(out)))
+    return out.value
+
+
+def logspace_add(logx, logy):
+    a, b = np.broadcast_arrays(np.asarray(logx, dtype=np.float64), np.asarray(logy, dtype=np.float64))
+    a = np.ascontiguousarray(a); b = np.ascontiguousarray(b)
+    out = np.empty_like(a)
+    check(_lib.load().sgb_logspace_add_vec(_ptr(a), _ptr(b), a.size, _ptr(out)))
+    return out
+
+
+def _viterbi(emission, transition, observations, init_mode, decode):
+    e = np.asfortranarray(emission, dtype=np.float64)
+    if e.ndim != 2:
+        raise ValueError("emission must be a bins x states matrix")
+    tr = np.asfortranarray(transition, dtype=np.float64)
+    if tr.ndim != 2 or tr.shape[0] != tr.shape[1]:
+        raise ValueError("transition must be a square matrix")
+    if e.shape[1] != tr.shape[0]:
+        raise ValueError("emission and transition disagree on the number of states")
+    obs = _as_counts(observations, "observations")
+    path = np.zeros(obs.size, dtype=np.int32)
+    check(_lib.load().sgb_viterbi(_ptr(e), e.shape[0], _ptr(tr), _ptr(obs), obs.size, tr.shape[0], int(init_mode),
+                                  _lib.DECODE_CHAINED if decode == "chained" else _lib.DECODE_REFERENCE, _ptr(path)))
+    return path.astype(np.float64)        # the R function returns a numeric vector of 0-based states
+
+
+def viterbi(emission, transition, observations, decode="reference"):
+    return _viterbi(emission, transition, observations, 0, decode)
+
+
+def viterbiR(emission, transition, observations):
+    return _viterbi(emission, transition, observations, 1, "reference")
+
+
+# ---------------------------------------------------------------------------------- array-level batch
+def decode_arrays(n, x, cn, seg_off, model="hscn", likelihood="binomial", n_states=12, loherror=0.02, eps=1e-12,
+                  rho=0.0, Abias=0.0, selftransitionprob=0.999, decode="reference", want_loglik=False,
+                  n_devices=1):
+    """Decode every sequence of a sorted long table given as flat arrays.  Returns uint8 states
+    (and the per-sequence column-major `l` blocks when want_loglik)."""
+    lib = _lib.load()
+    n = _as_counts(n, "totalcounts"); x = _as_counts(x, "alleleB")
+    cn = np.asarray(cn)
+    if cn.dtype != np.uint8:
+        cn = _as_counts(cn, "state")
+    cn = np.ascontiguousarray(cn)
+    seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+    if not (n.size == x.size == cn.size):
+        raise ValueError("n, x and cn must have the same length")
+    P = make_params(model, likelihood, n_states, loherror, eps, rho, Abias, selftransitionprob, decode)
+    out = np.zeros(n.size, dtype=np.uint8)
+    ll = np.empty(n.size * int(n_states), dtype=np.float64) if want_loglik else None
+    if n_devices > 1:
+        if want_loglik:
+            raise ValueError("want_loglik is single-device only")
+        check(lib.sgb_hmm_decode_multi(ctypes.byref(P), int(n_devices), n.size, _ptr(n), _ptr(x), _ptr(cn),
+                                       cn.dtype.itemsize, seg_off.size - 1, _ptr(seg_off), _ptr(out)))
+    else:
+        check(lib.sgb_hmm_decode(ctypes.byref(P), n.size, _ptr(n), _ptr(x), _ptr(cn), cn.dtype.itemsize,
+                                 seg_off.size - 1, _ptr(seg_off), _ptr(out), _ptr(ll) if want_loglik else None))
+    return (out, ll) if want_loglik else out
+
+
+def postprocess_arrays(cn, path):
+    """device version of the clamp block + numeric add_states columns (integer codes)"""
+    cn = np.asarray(cn)
+    if cn.dtype != np.uint8:
+        cn = _as_counts(cn, "state")
+    cn = np.ascontiguousarray(cn)
+    path = np.ascontiguousarray(path, dtype=np.uint8)
+    N = cn.size
+    A = np.empty(N, np.int32); B = np.empty(N, np.int32); smin = np.empty(N, np.int32)
+    loh = np.empty(N, np.uint8); phase = np.empty(N, np.uint8); sp = np.empty(N, np.uint8)
+    baf = np.empty(N, np.float64)
+    check(_lib.load().sgb_postprocess(N, _ptr(cn), cn.dtype.itemsize, _ptr(path), _ptr(A), _ptr(B), _ptr(smin),
+                                      _ptr(loh), _ptr(phase), _ptr(sp), _ptr(baf)))
+    return dict(A=A, B=B, state_min=smin, LOH=loh, phase=phase, state_phase=sp, state_BAF=baf)
+
+
+class DevicePlan:
+    """Device-resident decode: inputs/outputs are torch CUDA tensors (or anything with data_ptr())."""
+
+    def __init__(self, N, seg_off, n_states=12, decode="reference"):
+        self._lib = _lib.load()
+        seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+        self.N, self.nseg, self.n_states = int(N), int(seg_off.size - 1), int(n_states)
+        h = ctypes.c_void_p()
+        check(self._lib.sgb_plan_create(self.N, self.nseg, _ptr(seg_off), self.n_states,
+                                        _lib.DECODE_CHAINED if decode == "chained" else _lib.DECODE_REFERENCE,
+                                        ctypes.byref(h)))
+        self._h = h
+
+    def decode(self, params, d_n, d_x, d_cn, d_out, d_loglik=None, stream=0):
+        itemsize = d_cn.element_size()
+        check(self._lib.sgb_hmm_decode_device(ctypes.byref(params), self._h, d_n.data_ptr(), d_x.data_ptr(),
+                                              d_cn.data_ptr(), itemsize, d_out.data_ptr(),
+                                              d_loglik.data_ptr() if d_loglik is not None else None,
+                                              ctypes.c_void_p(stream)))
+
+    def check(self, stream=0):
+        check(self._lib.sgb_plan_check(self._h, ctypes.c_void_p(stream)))
+
+    def scratch_bytes(self):
+        return int(self._lib.sgb_plan_scratch_bytes(self._h))
+
+    def close(self):
+        if self._h:
+            self._lib.sgb_plan_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+# ---------------------------------------------------------------------------------- single-sequence HMMs
+def _single(model, n, x, binstates, minor_cn, loherror, selftransitionprob, eps, likelihood, rho, Abias):
+    if likelihood not in ("binomial", "betabinomial"):
+        raise ValueError("Likelihood model must be one of binomial or betabinomial")
+    S = _check_minor_cn(minor_cn)
+    n = _as_counts(n, "n"); x = _as_counts(x, "x"); cn = _as_counts(binstates, "binstates")
+    T = n.size
+    seg = np.array([0, T], dtype=np.int64)
+    path, ll = decode_arrays(n, x, cn, seg, model, likelihood, S, loherror, eps, rho, Abias, selftransitionprob,
+                             want_loglik=True)
+    l = ll.reshape(S, T).T.copy() if T else np.zeros((0, S))
+    return {"minorcn": path.astype(np.float64), "l": l}
+
+
+def HaplotypeHMM(n, x, binstates, minor_cn, loherror=0.02, selftransitionprob=0.999, eps=1e-12,
+                 likelihood="binomial", rho=0.0, Abias=0.0, viterbiver="cpp"):
+    res = _single("hscn", n, x, binstates, minor_cn, loherror, selftransitionprob, eps, likelihood, rho, Abias)
+    if viterbiver == "R":
+        # R/callHSCN.R:101-105: the pure-R twin is run on the same l / transition matrix
+        S = len(minor_cn)
+        if selftransitionprob == 0.0:
+            tp = np.full((S, S), 1.0 / S)
+        else:
+            tp = np.full((S, S), (1.0 - selftransitionprob) / (S - 1))
+            np.fill_diagonal(tp, selftransitionprob)
+        with np.errstate(divide="ignore"):
+            res["minorcn"] = viterbiR(res["l"], np.log(tp), np.arange(1, len(res["minorcn"]) + 1))
+    return res
+
+
+def alleleHMM(n, x, binstates, minor_cn, loherror=0.02, selftransitionprob=0.999, eps=1e-12, rho=0.0,
+              likelihood="binomial"):
+    return _single("ascn", n, x, binstates, minor_cn, loherror, selftransitionprob, eps, likelihood, rho, 0.0)
+
+
+# ---------------------------------------------------------------------------------- data.frame level
+def _segments(df, by_cell=True):
+    """row-run boundaries of (cell_id, chr) (or chr only) in the CURRENT row order, like unique(CNBAF$chr)
+    followed by dplyr::filter does for a table sorted by chromosome (R/callHSCN.R:150-154)"""
+    chr_codes = df["chr"].astype("category").cat.codes.to_numpy()
+    change = np.ones(len(df), dtype=bool)
+    if len(df) > 1:
+        change[1:] = chr_codes[1:] != chr_codes[:-1]
+        if by_cell and "cell_id" in df.columns:
+            cell_codes = df["cell_id"].astype("category").cat.codes.to_numpy()
+            change[1:] |= cell_codes[1:] != cell_codes[:-1]
+    starts = np.nonzero(change)[0]
+    return np.concatenate((starts, [len(df)])).astype(np.int64)
+
+
+def _assign(model, CNBAF, minor_cn, eps, loherror, selftransitionprob, likelihood, rho, Abias):
+    S = _check_minor_cn(minor_cn)
+    df = CNBAF.copy()
+    # the reference gathers rows per unique(chr) and writes the concatenated result back in row order
+    # (R/callHSCN.R:150-167); that is only self-consistent when each chromosome's rows are contiguous
+    if len(df) and df["chr"].nunique() != len(_segments(df, by_cell=False)) - 1:
+        raise ValueError("rows of each chromosome must be contiguous")
+    seg = _segments(df, by_cell=False)
+    path = decode_arrays(df["totalcounts"].to_numpy(), df["alleleB"].to_numpy(), df["state"].to_numpy(), seg, model,
+                         likelihood, S, loherror, eps, rho, Abias, selftransitionprob)
+    df["state_min"] = path.astype(np.float64)
+    return df
+
+
+def assignHaplotypeHMM(CNBAF, minor_cn, eps=1e-12, loherror=0.02, selftransitionprob=0.999, pb=None,
+                       likelihood="binomial", rho=0.0, Abias=0.0, viterbiver="cpp"):
+    return _assign("hscn", CNBAF, minor_cn, eps, loherror, selftransitionprob, likelihood, rho, Abias)
+
+
+def assignalleleHMM(CNBAF, minor_cn, eps=1e-12, loherror=0.02, selftransitionprob=0.999, pb=None, rho=0.0,
+                    likelihood="binomial"):
+    return _assign("ascn", CNBAF, minor_cn, eps, loherror, selftransitionprob, likelihood, rho, 0.0)
+
+
+_PHASE = np.array(["Balanced", "A", "B"], dtype=object)
+_STATE_PHASE = np.array(["Balanced", "A-Gained", "B-Gained", "A-Hom", "B-Hom"], dtype=object)
+
+
+def _attach_states(df, cols):
+    """materialise the string columns of add_states from the device-computed integer codes"""
+    A, B, st = cols["A"], cols["B"], df["state"].to_numpy().astype(np.int64)
+    df["A"] = A; df["B"] = B
+    a_s, b_s = A.astype(str), B.astype(str)
+    df["state_AS_phased"] = np.char.add(np.char.add(a_s, "|"), b_s)
+    hi = np.maximum(st - B, B).astype(str); lo = np.minimum(st - B, B).astype(str)
+    state_as = np.char.add(np.char.add(hi, "|"), lo).astype(object)
+    big = st > 4
+    state_as[big] = st[big].astype(str)
+    df["state_AS"] = state_as
+    df["state_min"] = cols["state_min"]
+    df["LOH"] = np.where(cols["LOH"] == 1, "LOH", "NO")
+    df["phase"] = _PHASE[cols["phase"]]
+    df["state_phase"] = _STATE_PHASE[cols["state_phase"]]
+    df["state_BAF"] = cols["state_BAF"]
+    return df
+
+
+def add_states(df):
+    """R/util.R:1078-1097 for a table that already has A, B and state"""
+    out = df.copy()
+    path = np.ascontiguousarray(out["B"].to_numpy(), dtype=np.uint8)
+    cols = postprocess_arrays(out["state"].to_numpy(), path)
+    # add_states does not re-clamp: keep the caller's A / B
+    cols["A"] = out["A"].to_numpy(); cols["B"] = out["B"].to_numpy()
+    cols["state_min"] = np.minimum(cols["A"], cols["B"])
+    return _attach_states(out, cols)
+
+
+def _batch(model, CNBAF, eps, loherror, maxCN, selftransitionprob, likelihood, rho, Abias, n_devices):
+    if likelihood not in ("binomial", "betabinomial"):
+        raise ValueError("Likelihood model must be one of binomial or betabinomial")
+    minor_cn = np.arange(0, maxCN + 1)
+    S = _check_minor_cn(minor_cn)
+    # "Make sure dataframe is in chromosome position order"  R/callHSCN.R:241-242 (chr is character)
+    df = CNBAF.copy()
+    df["chr"] = df["chr"].astype(str)
+    df = df.sort_values(["cell_id", "chr", "start"], kind="stable").reset_index(drop=True)
+    seg = _segments(df, by_cell=True)
+    path = decode_arrays(df["totalcounts"].to_numpy(), df["alleleB"].to_numpy(), df["state"].to_numpy(), seg, model,
+                         likelihood, S, loherror, eps, rho, Abias, selftransitionprob, n_devices=n_devices)
+    cols = postprocess_arrays(df["state"].to_numpy(), path)
+    return _attach_states(df, cols)
+
+
+def callHaplotypeSpecificCN_(CNBAF, eps=1e-12, loherror=0.02, maxCN=10, selftransitionprob=0.999,
+                             progressbar=True, ncores=1, likelihood="binomial", rho=0.0, Abias=0.0,
+                             viterbiver="cpp", n_devices=1):
+    """.callHaplotypeSpecificCN_ (R/callHSCN.R:217-295): one batched launch instead of the per-cell loop.
+    `progressbar`, `ncores` and `viterbiver` are accepted for signature parity and ignored."""
+    return _batch("hscn", CNBAF, eps, loherror, maxCN, selftransitionprob, likelihood, rho, Abias, n_devices)
+
+
+def callAlleleSpecificCN_(CNBAF, eps=1e-12, loherror=0.02, maxCN=10, selftransitionprob=0.999, progressbar=True,
+                          ncores=1, likelihood="binomial", rho=0.0, n_devices=1):
+    """pass-2 loop of callAlleleSpecificCN (R/callASCN.R:382-414) plus its post block (:416-447)"""
+    return _batch("ascn", CNBAF, eps, loherror, maxCN, selftransitionprob, likelihood, rho, 0.0, n_devices)

@@ -1,0 +1,64 @@
+"""Shared test inputs: hand-written edge cases and seeded cohorts (used by the golden generator too)."""
+import numpy as np
+
+from signals_b200 import synth
+
+# (name, model, likelihood, S, loherror, eps, rho, Abias, selftransitionprob)
+PARAM_SETS = [
+    ("hscn_binom_default", "hscn", "binomial", 12, 0.02, 1e-12, 0.0, 0.0, 0.95),
+    ("hscn_binom_stp999", "hscn", "binomial", 12, 0.02, 1e-12, 0.0, 0.0, 0.999),
+    ("hscn_bb", "hscn", "betabinomial", 12, 0.03, 1e-12, 0.02, 0.0, 0.95),
+    ("ascn_binom", "ascn", "binomial", 12, 0.02, 1e-12, 0.0, 0.0, 0.95),
+    ("ascn_bb", "ascn", "betabinomial", 12, 0.025, 1e-12, 0.02, 0.0, 0.95),
+    ("hscn_iid", "hscn", "binomial", 12, 0.02, 1e-12, 0.0, 0.0, 0.0),
+    ("hscn_stp1", "hscn", "binomial", 12, 0.02, 1e-12, 0.0, 0.0, 1.0),
+    ("hscn_noeps_noloh", "hscn", "binomial", 12, 0.0, 0.0, 0.0, 0.0, 0.95),
+    ("hscn_abias", "hscn", "binomial", 12, 0.02, 1e-12, 0.0, 0.1, 0.95),
+    ("hscn_maxcn2", "hscn", "binomial", 3, 0.02, 1e-12, 0.0, 0.0, 0.95),
+    ("hscn_maxcn10", "hscn", "binomial", 11, 0.02, 1e-12, 0.0, 0.0, 0.95),
+    ("hscn_maxcn19", "hscn", "binomial", 20, 0.02, 1e-12, 0.0, 0.0, 0.95),
+    ("ascn_bb_rho0", "ascn", "betabinomial", 12, 0.02, 1e-12, 0.0, 0.0, 0.95),
+    ("ascn_noeps", "ascn", "binomial", 12, 0.02, 0.0, 0.0, 0.0, 0.9),
+    ("hscn_bb_bigloh", "hscn", "betabinomial", 12, 0.6, 1e-12, 0.3, 0.0, 0.5),
+]
+
+
+def param_dict(ps):
+    name, model, lik, S, loh, eps, rho, Ab, stp = ps
+    return dict(model=model, likelihood=lik, S=S, loherror=loh, eps=eps, rho=rho, Abias=Ab, selftransitionprob=stp)
+
+
+def edge_sequences():
+    """list of (name, n, x, cn) single sequences covering the reference's corner cases"""
+    out = []
+    out.append(("T1", [20], [7], [2]))
+    out.append(("T2", [20, 30], [7, 29], [2, 3]))
+    out.append(("x0_xn_n1", [1, 1, 50, 50, 1, 3], [0, 1, 0, 50, 1, 0], [2, 2, 3, 3, 1, 4]))
+    out.append(("cn0_homdel", [1, 2, 4, 4, 3, 2, 2, 5, 1], [0, 1, 2, 3, 1, 0, 2, 2, 1], [0] * 9))
+    out.append(("cn0_inside", [30, 28, 2, 3, 33, 31], [10, 9, 1, 2, 11, 12], [3, 3, 0, 0, 3, 3]))
+    out.append(("cn_gt_maxstate", [200, 210, 190, 220], [100, 110, 95, 20], [11, 11, 14, 20]))
+    out.append(("n0_bins", [0, 10, 0, 12], [0, 5, 0, 6], [2, 2, 2, 2]))
+    out.append(("x_gt_n", [10, 10, 10], [5, 12, 5], [2, 2, 2]))
+    out.append(("ties_symmetric", [2, 2, 2, 2, 2, 2], [1, 1, 1, 1, 1, 1], [2, 2, 2, 2, 2, 2]))
+    out.append(("big_counts", [3000, 2500, 5000, 2047, 2048, 2049], [1500, 100, 4999, 1000, 1024, 7],
+                [2, 3, 4, 2, 2, 5]))
+    out.append(("cn1_only", [15, 12, 18, 11], [0, 12, 1, 11], [1, 1, 1, 1]))
+    rng = np.random.default_rng(7)
+    T = 300
+    cn = np.repeat([2, 3, 1, 4, 6, 2], 50)
+    b = np.repeat([1, 1, 0, 2, 5, 0], 50)
+    n = rng.poisson(12 * np.maximum(cn, 1)) + 1
+    x = rng.binomial(n, np.where(b == 0, 0.02, b / cn))
+    out.append(("piecewise300", n.tolist(), x.tolist(), cn.tolist()))
+    return [(nm, np.array(a, np.int32), np.array(b_, np.int32), np.array(c, np.int32)) for nm, a, b_, c in out]
+
+
+def concat_sequences(seqs):
+    n = np.concatenate([s[1] for s in seqs]); x = np.concatenate([s[2] for s in seqs])
+    cn = np.concatenate([s[3] for s in seqs])
+    seg = np.concatenate(([0], np.cumsum([len(s[1]) for s in seqs]))).astype(np.int64)
+    return n, x, cn, seg
+
+
+def small_cohort(likelihood="binomial", n_cells=40, seed=11, ragged=0.05):
+    return synth.make_cohort(n_cells, lens=synth.LENS_DLPBINS, seed=seed, likelihood=likelihood, ragged_drop=ragged)
