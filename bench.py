@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the HSCN/ASCN HMM hot path (emission + Viterbi-style decode).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload target|cfg2|cfg3] [--impl reference]
+
+A "step" is one pass of the hot path over one batch of synthetic DLP-shaped cell-bins.
+  value     cell-bins/s with inputs already resident in HBM (k_setup + k_pack + k_decode [+ NCCL gather of
+            the uint8 state paths when N > 1]); CUDA events on the launch stream, max over ranks
+  e2e       the same metric through the host-buffer C-ABI call sgb_hmm_decode: pinned host inputs are
+            copied to the device, decoded, and the state paths copied back, every step
+  roofline  k_decode against the FP64 pipe (the path is FP64-bound, not HBM- or tensor-bound):
+            algorithmic flop-eq per launch / mean k_decode duration (CUDA events over the timed region) vs a
+            DFMA peak measured in this process; the HBM view (10 B per cell-bin) is reported beside it
+  cpu_baseline  the oracle's libm flavour (CPU restatement of the reference) on this box's host cores
+Under torchrun (N > 1) every rank owns one GPU and an independent shard of cells (weak scaling).
+"""
+import argparse
+import ctypes
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (n_cells, lens-key, model, likelihood, rho, seed, description)
+    "target": (10000, "5700", "hscn", "binomial", 0.0, 20260002,
+               "synthetic 10,000 cells x 5,700 500kb bins HSCN, maxCN=11, binomial (north_star target)"),
+    "cfg2": (1000, "5700", "hscn", "binomial", 0.0, 20260001,
+             "synthetic 1,000 cells x 5,700 500kb bins HSCN, maxCN=11, binomial (BASELINE configs[1])"),
+    "cfg3": (10000, "5700", "ascn", "betabinomial", 0.02, 20260003,
+             "synthetic 10,000 cells x 5,700 bins ASCN beta-binomial rho=0.02 (BASELINE configs[2])"),
+}
+PARAMS = dict(n_states=12, loherror=0.02, eps=1e-12, Abias=0.0, selftransitionprob=0.95)
+F_BIN = {("hscn", "binomial"): 303, ("hscn", "betabinomial"): 404, ("ascn", "binomial"): 303, ("ascn", "betabinomial"): 404}
+F_STATE = {("hscn", "binomial"): 99, ("hscn", "betabinomial"): 300, ("ascn", "binomial"): 198, ("ascn", "betabinomial"): 600}
+
+
+def make_data(name, rank=0):
+    from signals_b200 import synth
+    n_cells, lens, model, lik, rho, seed, desc = WORKLOADS[name]
+    lens = synth.LENS_5700 if lens == "5700" else synth.LENS_30000
+    d = synth.make_cohort(n_cells, lens=lens, seed=seed + 1000 * rank, likelihood=lik)
+    return d
+
+
+def flop_eq(d, model, lik, S=12):
+    """algorithmic flop-eq of one pass, SURVEY 8(d) convention: F = F_bin + L*F_state + 3*L_prev*L + L per cell-bin"""
+    c = d["cn"].astype(np.int64)
+    if model == "hscn":
+        L = np.minimum(np.maximum(c, 1), S - 1) + 1
+    else:
+        L = np.where(c == 0, 0, np.minimum(c // 2, S - 1) + 1)
+    Lp = np.empty_like(L)
+    Lp[1:] = L[:-1]
+    Lp[d["seg_off"][:-1]] = 0
+    key = (model, lik)
+    return float((F_BIN[key] + L * F_STATE[key] + 3 * Lp * L + L).sum())
+
+
+class ClockSampler(threading.Thread):
+    """polls NVML while the timed regions run (clocks + throttle reasons)"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag, self.ok = index, [], False, False
+        self.active = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_sm = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                if self.active:
+                    self.samples.append((sm, rs, pw))
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def summary(self):
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": getattr(self, "max_sm", None), "reasons": ["unavailable"]}
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        seen = set()
+        for _, rs, _ in self.samples:
+            for bit, nm in names.items():
+                if rs & bit:
+                    seen.add(nm)
+        sms = sorted(s for s, _, _ in self.samples)
+        return {"sm_mhz": float(sms[len(sms) // 2]), "sm_max_mhz": float(self.max_sm), "reasons": sorted(seen),
+                "samples": len(sms), "power_w_max": max(p for _, _, p in self.samples)}
+
+
+def cpu_reference_run(d, model, lik, rho, seconds_target, steps, warmup):
+    """times the oracle's libm flavour (the CPU restatement of the reference path) on all host threads"""
+    from oracle import cpu_oracle as co
+    co.build()
+    cores = os.cpu_count() or 1
+    P = co.params(model=model, likelihood=lik, S=PARAMS["n_states"], loherror=PARAMS["loherror"], eps=PARAMS["eps"],
+                  rho=rho, Abias=PARAMS["Abias"], selftransitionprob=PARAMS["selftransitionprob"])
+    cn32 = d["cn"].astype(np.int32)
+    so = d["seg_off"]
+    nseq_per_cell = len(d["lens"])
+    # calibrate on a few cells, then size the sample for ~seconds_target of work per step
+    cal_cells = min(d["n_cells"], max(2 * cores, 8))
+    m = so[cal_cells * nseq_per_cell]
+    t0 = time.perf_counter()
+    co.decode_batch(d["n"][:m], d["x"][:m], cn32[:m], so[: cal_cells * nseq_per_cell + 1], P, co.MATH_LIBM, nthreads=cores)
+    rate = m / (time.perf_counter() - t0)
+    cells = int(min(d["n_cells"], max(cal_cells, rate * seconds_target / (m / cal_cells))))
+    m = so[cells * nseq_per_cell]
+    args = (d["n"][:m], d["x"][:m], cn32[:m], so[: cells * nseq_per_cell + 1], P, co.MATH_LIBM)
+    for _ in range(warmup):
+        co.decode_batch(*args, nthreads=cores)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        co.decode_batch(*args, nthreads=cores)
+    dt = (time.perf_counter() - t0) / steps
+    return dict(value=float(m / dt), unit="cell-bins/s", cores=cores, kind="port",
+                sample="first %d cells (%d cell-bins) of the workload per step, oracle/oracle.c libm flavour, -O2, %d threads"
+                       % (cells, m, cores)), dt, int(m)
+
+
+def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=True):
+    import torch
+    from signals_b200 import _lib, hmm
+    n_cells, _, model, lik, rho, seed, desc = WORKLOADS[name]
+    dev = torch.device("cuda", torch.cuda.current_device())
+    P = hmm.make_params(model=model, likelihood=lik, rho=rho, **PARAMS)
+    N = d["n"].size
+    # pinned host buffers (e2e inputs / outputs) and resident device copies (value)
+    hn = torch.from_numpy(d["n"]).pin_memory(); hx = torch.from_numpy(d["x"]).pin_memory()
+    hc = torch.from_numpy(d["cn"]).pin_memory()
+    hout = torch.zeros(N, dtype=torch.uint8).pin_memory()
+    tn, tx, tc = hn.to(dev), hx.to(dev), hc.to(dev)
+    out = torch.zeros(N, dtype=torch.uint8, device=dev)
+    gathered = torch.empty(N * world, dtype=torch.uint8, device=dev) if world > 1 else None
+    plan = hmm.DevicePlan(N, d["seg_off"], n_states=PARAMS["n_states"])
+    plan.enable_timing(True)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        plan.decode(P, tn, tx, tc, out, stream=stream)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, out)
+
+    for _ in range(max(warmup, 3)):
+        step()
+    plan.check(stream)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    plan.enable_timing(True)            # restart the ring so it only holds timed steps
+    small = N * 9 < 200e6               # inputs fit in the 126 MB L2: flush it between (individually timed) steps
+    sampler.active = True
+    if not small:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        elapsed = e0.elapsed_time(e1)
+    else:
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+        elapsed = 0.0
+        for _ in range(steps):
+            flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); step(); e1.record()
+            torch.cuda.synchronize()
+            elapsed += e0.elapsed_time(e1)
+        del flush
+    sampler.active = False
+    if world > 1:
+        dist.barrier()
+    ms = torch.tensor([elapsed], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total_ms = float(ms.item())
+    plan.check(stream)
+    pack_ms, decode_ms = plan.read_timing(64)
+    res = dict(ms_per_step=total_ms / steps, value=N * world * steps / (total_ms * 1e-3),
+               decode_ms=float(decode_ms.mean()), pack_ms=float(pack_ms.mean()), N=N,
+               scratch_bytes=plan.scratch_bytes(), checksum=int(out.to(torch.int64).sum().item()))
+
+    if want_e2e:
+        lib = _lib.load()
+        args = (ctypes.byref(P), N, hn.data_ptr(), hx.data_ptr(), hc.data_ptr(), 1, d["seg_off"].size - 1,
+                d["seg_off"].ctypes.data, hout.data_ptr(), None)
+        for _ in range(max(2, min(warmup, 3))):
+            hmm.check(lib.sgb_hmm_decode(*args))
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e2e_steps = max(3, min(steps, 10))
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.active = True
+        t0 = time.perf_counter()
+        f0.record()
+        for _ in range(e2e_steps):
+            hmm.check(lib.sgb_hmm_decode(*args))       # synchronous: returns when the paths are back on the host
+        f1.record()
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        sampler.active = False
+        ems = torch.tensor([max(f0.elapsed_time(f1), wall * 1e3)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ems, op=dist.ReduceOp.MAX)
+        e2e_ms = float(ems.item()) / e2e_steps
+        nseq = d["seg_off"].size - 1
+        res["e2e"] = dict(value=N * world / (e2e_ms * 1e-3), unit="cell-bins/s", ms_per_step=e2e_ms,
+                          h2d_bytes_per_step=int(N * 9 + nseq * 20), d2h_bytes_per_step=int(N), steps=e2e_steps,
+                          api="sgb_hmm_decode (host buffers, pinned, chunked copy/compute overlap)")
+        assert int(hout.to(torch.int64).sum().item()) == res["checksum"], "host-API and device-API results differ"
+    plan.close()
+    del tn, tx, tc, out, hn, hx, hc, hout
+    torch.cuda.empty_cache()
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="target", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-extras", action="store_true", help="skip the other workloads and the CPU baseline")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    n_cells, lens, model, lik, rho, seed, desc = WORKLOADS[a.workload]
+    config = {"workload": desc, "cells_per_gpu": n_cells, "bins_per_cell": 5700, "sequences_per_cell": 23,
+              "maxCN": 11, "n_states": 12, "likelihood": lik, "model": model.upper(), "selftransitionprob": 0.95,
+              "loherror": 0.02, "eps": 1e-12, "rho": rho, "sharding": "cells, %d rank(s), 1 GPU each" % max(world, 1),
+              "l2": "inputs (%d MB per GPU) %s" % (n_cells * 5700 * 9 // 1000000,
+                                                   "larger than L2; no explicit flush" if n_cells * 5700 * 9 > 200e6
+                                                   else "fit in L2: 256 MB flush write between individually timed steps")}
+
+    if a.impl == "reference":
+        # The reference's own CPU implementation cannot run (no R / Rcpp / VGAM in this image; src/code.cpp needs
+        # <Rcpp.h>), so this arm times the oracle: the C restatement of the same path, all host threads.
+        if rank != 0:
+            return 0
+        d = make_data(a.workload)
+        per_step = max(0.5, min(8.0, 100.0 / max(a.steps + a.warmup, 1)))      # whole run stays within a few minutes
+        cb, dt, m = cpu_reference_run(d, model, lik, rho, per_step, max(a.steps, 1), max(a.warmup, 0))
+        line = {"impl": "reference", "metric": "cell_bins_per_sec", "value": cb["value"], "unit": "cell-bins/s",
+                "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": dt * 1e3,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": config, "cpu_baseline": cb,
+                "e2e": {"value": cb["value"], "unit": "cell-bins/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "note": "reference = oracle port (R toolchain absent); each step decodes a bounded sample of the workload"}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    from signals_b200 import _lib, hmm
+    lib = _lib.load()
+    hmm.check(lib.sgb_init(local_rank))
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+
+    d = make_data(a.workload, rank)
+    main_res = gpu_measure(a.workload, d, a.steps, a.warmup, rank, world, dist, sampler)
+    fe = flop_eq(d, model, lik)
+    clocks = sampler.summary()
+    peak = ctypes.c_double(0.0)
+    hmm.check(lib.sgb_fp64_peak(20, ctypes.byref(peak)))
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        hbm_peak, hbm_src = float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+    dec_s = main_res["decode_ms"] * 1e-3
+    achieved_tf = fe / dec_s / 1e12
+    roofline = {"bound": "fp64", "kernel": "k_decode", "achieved": achieved_tf, "peak": peak.value, "unit": "TFLOP/s",
+                "frac": achieved_tf / peak.value if peak.value > 0 else None, "traffic": None,
+                "peak_source": "DFMA micro-kernel measured in this process (sgb_fp64_peak); nominal 37.2 at 1965 MHz",
+                "flop_eq_per_cell_bin": fe / main_res["N"], "flop_eq_convention": "SURVEY 8(d): FMA=2, exp=40, log=log1p=50, lgamma=100, live states only",
+                "kernel_ms": main_res["decode_ms"], "pack_ms": main_res["pack_ms"],
+                "hbm": {"achieved": 10.0 * main_res["N"] / dec_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": 10.0 * main_res["N"] / dec_s / 1e9 / hbm_peak, "peak_source": hbm_src,
+                        "algorithmic_bytes_per_cell_bin": 10}}
+    line = {"metric": "cell_bins_per_sec", "value": main_res["value"], "unit": "cell-bins/s", "n_gpus": world,
+            "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": main_res["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+            "clocks": clocks, "e2e": main_res.get("e2e"), "gpu_launches": 3 * a.steps,
+            "gpu_kernels_per_step": ["k_setup", "k_pack", "k_decode"], "roofline": roofline,
+            "scratch_bytes": main_res["scratch_bytes"]}
+
+    if rank == 0 and world == 1 and not a.no_extras:
+        others = {}
+        for nm in sorted(WORKLOADS):
+            if nm == a.workload:
+                continue
+            dd = make_data(nm)
+            r = gpu_measure(nm, dd, max(5, a.steps // 2), 3, 0, 1, None, sampler, want_e2e=True)
+            f2 = flop_eq(dd, WORKLOADS[nm][2], WORKLOADS[nm][3])
+            others[nm] = {"workload": WORKLOADS[nm][6], "value": r["value"], "ms_per_step": r["ms_per_step"],
+                          "kernel_ms": r["decode_ms"], "e2e_value": r["e2e"]["value"],
+                          "fp64_frac": f2 / (r["decode_ms"] * 1e-3) / 1e12 / peak.value if peak.value > 0 else None,
+                          "flop_eq_per_cell_bin": f2 / r["N"]}
+            del dd
+        line["other_workloads"] = others
+        cb, _, _ = cpu_reference_run(d, model, lik, rho, 12.0, 1, 0)
+        line["cpu_baseline"] = cb
+    sampler.stop_flag = True
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -98,6 +98,12 @@ SGB_API int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* plan, cons
                           const void* d_cn, int32_t cn_itemsize, uint8_t* d_state_out, double* d_loglik_out,
                           void* stream);
 SGB_API int sgb_plan_check(sgb_plan* plan, void* stream);
+/* Optional kernel timing for the device-resident path: when enabled, every sgb_hmm_decode_device call
+ * records CUDA events on its stream around k_pack and k_decode (ring of the last 64 calls);
+ * sgb_plan_read_timing returns the most recent durations in milliseconds, oldest first. */
+SGB_API int sgb_plan_enable_timing(sgb_plan* plan, int32_t on);
+SGB_API int sgb_plan_read_timing(sgb_plan* plan, int32_t max_records, float* pack_ms, float* decode_ms,
+                                 int32_t* n_out);
 /* bytes of device scratch the plan holds (packed records + optional backpointers) */
 SGB_API int64_t sgb_plan_scratch_bytes(const sgb_plan* plan);
 

@@ -430,6 +430,12 @@ struct sgb_plan {
     int* d_err = nullptr;
     SgbDevTables* d_tabs = nullptr;
     SgbPlanDev pd;
+    // optional per-call kernel timing: ring of event triples (before pack, after pack, after decode)
+    bool timing = false;
+    static const int kRing = 64;
+    cudaEvent_t ev[kRing][3];
+    bool ev_ready = false;
+    long long calls = 0;
 };
 
 int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_states, int32_t decode,
@@ -477,6 +483,9 @@ int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_s
 int sgb_plan_destroy(sgb_plan* pl)
 {
     if (!pl) return 0;
+    if (pl->ev_ready)
+        for (int i = 0; i < sgb_plan::kRing; i++)
+            for (int j = 0; j < 3; j++) cudaEventDestroy(pl->ev[i][j]);
     pl->pstart.release(); pl->ostart.release(); pl->len.release(); pl->packed.release(); pl->bp.release();
     pl->last_state.release();
     if (pl->counter) cudaFree(pl->counter);
@@ -510,13 +519,47 @@ int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t*
     if (C->device != pl->device) return fail("plan belongs to another device");
     cudaStream_t st = (cudaStream_t)stream;
     SGB_CUDA(sgbk_setup(pl->d_tabs, m, params->eps, params->Abias, params->selftransitionprob, st));
+    const int slot = (int)(pl->calls % sgb_plan::kRing);
+    if (pl->timing) SGB_CUDA(cudaEventRecord(pl->ev[slot][0], st));
     SGB_CUDA(sgbk_pack(d_n, d_x, d_cn, cn_itemsize, pl->pd, (unsigned long long*)pl->packed.p, pl->d_err, st));
+    if (pl->timing) SGB_CUDA(cudaEventRecord(pl->ev[slot][1], st));
     SGB_CUDA(sgbk_decode(pl->pd, (const unsigned long long*)pl->packed.p, pl->d_tabs, m, d_state_out,
                          (uint8_t*)pl->bp.p, (int*)pl->last_state.p, pl->counter, C->sm_count, st));
+    if (pl->timing) { SGB_CUDA(cudaEventRecord(pl->ev[slot][2], st)); pl->calls++; }
     if (m.decode == SGB_DECODE_CHAINED)
         SGB_CUDA(sgbk_backtrace(pl->pd, (const uint8_t*)pl->bp.p, (const int*)pl->last_state.p, m.S, d_state_out, st));
     if (d_loglik_out)
         SGB_CUDA(sgbk_loglik(d_n, d_x, d_cn, cn_itemsize, pl->pd, pl->d_tabs, m, d_loglik_out, st));
+    return 0;
+}
+
+int sgb_plan_enable_timing(sgb_plan* pl, int32_t on)
+{
+    if (!pl) return fail("plan is NULL");
+    if (on && !pl->ev_ready) {
+        for (int i = 0; i < sgb_plan::kRing; i++)
+            for (int j = 0; j < 3; j++) SGB_CUDA(cudaEventCreate(&pl->ev[i][j]));
+        pl->ev_ready = true;
+    }
+    pl->timing = on != 0;
+    pl->calls = 0;
+    return 0;
+}
+
+int sgb_plan_read_timing(sgb_plan* pl, int32_t max_records, float* pack_ms, float* decode_ms, int32_t* n_out)
+{
+    if (!pl || !pack_ms || !decode_ms || !n_out) return fail("NULL pointer");
+    *n_out = 0;
+    if (!pl->ev_ready) return 0;
+    long long have = pl->calls < sgb_plan::kRing ? pl->calls : sgb_plan::kRing;
+    if (have > max_records) have = max_records;
+    for (long long i = 0; i < have; i++) {
+        int slot = (int)((pl->calls - have + i) % sgb_plan::kRing);
+        SGB_CUDA(cudaEventSynchronize(pl->ev[slot][2]));
+        SGB_CUDA(cudaEventElapsedTime(&pack_ms[i], pl->ev[slot][0], pl->ev[slot][1]));
+        SGB_CUDA(cudaEventElapsedTime(&decode_ms[i], pl->ev[slot][1], pl->ev[slot][2]));
+    }
+    *n_out = (int32_t)have;
     return 0;
 }
 

@@ -161,6 +161,16 @@ class DevicePlan:
     def check(self, stream=0):
         check(self._lib.sgb_plan_check(self._h, ctypes.c_void_p(stream)))
 
+    def enable_timing(self, on=True):
+        check(self._lib.sgb_plan_enable_timing(self._h, 1 if on else 0))
+
+    def read_timing(self, max_records=64):
+        """(pack_ms[], decode_ms[]) of the most recent calls, measured with CUDA events on the launch stream"""
+        pk = np.zeros(max_records, np.float32); dc = np.zeros(max_records, np.float32)
+        k = ctypes.c_int32(0)
+        check(self._lib.sgb_plan_read_timing(self._h, max_records, _ptr(pk), _ptr(dc), ctypes.byref(k)))
+        return pk[: k.value].copy(), dc[: k.value].copy()
+
     def scratch_bytes(self):
         return int(self._lib.sgb_plan_scratch_bytes(self._h))
 
