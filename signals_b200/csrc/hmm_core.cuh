@@ -51,6 +51,8 @@ struct SgbScalars {
     double bb_s;        // (1-rho)/rho
     int use_eps;
     int use_abias;
+    int fast_ok;        // the lean emission path is valid (no Abias, log(eps) finite)
+    int diag_dominant;  // tr_self >= tr_off: the O(S) recursion needs only the column maximum
 };
 
 // total CN as the model sees it: HaplotypeHMM remaps 0 -> 1 (R/callHSCN.R:49), alleleHMM does not
@@ -103,8 +105,11 @@ SGB_HD SgbScalars sgb_scalars(int S, double eps, double Abias, double stp, doubl
         s.tr_self = sgb_log(stp, LT);
         s.tr_off = sgb_log(sgb_div(sgb_sub(1.0, stp), (double)(S - 1)), LT);
     }
+    if (S == 1) s.tr_off = -sgb_inf();                       // a 1 x 1 transition matrix has no off-diagonal entry
     s.init = -sgb_log((double)S, LT);
     s.bb_s = (rho > 0.0) ? sgb_div(sgb_sub(1.0, rho), rho) : 0.0;
+    s.fast_ok = !s.use_abias && (!s.use_eps || (s.log_eps == s.log_eps && sgb_fabs(s.log_eps) != sgb_inf()));
+    s.diag_dominant = (s.tr_self >= s.tr_off) ? 1 : 0;
     return s;
 }
 
@@ -165,6 +170,85 @@ SGB_HD double sgb_emission(int model, int lik_bb, const SgbBin& b, int m, const 
     return l;
 }
 
+// Lean emission for the common case: tabulated total CN, 0 < p < 1 (kind NORMAL), 0 <= x <= n, no Abias,
+// finite log(eps).  Same operations in the same order as sgb_density / sgb_emission, minus the branches
+// that cannot be taken under these conditions -- so the bits are identical (tests/test_hostemu.py).
+template <int MODEL, int LIKBB>
+SGB_HD double sgb_emission_fast(double kd, double nkd, double lc_x, double lc_y, double lg_sn, double lp, double lq,
+                                double a, double b, double l0, const SgbScalars& sp,
+                                const double* __restrict__ LT, const double* __restrict__ ET)
+{
+    double l;
+    if (!LIKBB) {
+        l = sgb_fma(nkd, lq, sgb_fma(kd, lp, lc_x));
+    } else {
+        double t1 = sgb_add(sgb_lgamma_pos(sgb_add(a, kd), LT), sgb_lgamma_pos(sgb_add(b, nkd), LT));
+        t1 = sgb_sub(t1, lg_sn);
+        l = sgb_add(lc_x, sgb_sub(t1, l0));
+    }
+    if (MODEL == SGB_MODEL_ASCN) {
+        double l2;
+        if (!LIKBB) {
+            l2 = sgb_fma(kd, lq, sgb_fma(nkd, lp, lc_y));
+        } else {
+            double t1 = sgb_add(sgb_lgamma_pos(sgb_add(a, nkd), LT), sgb_lgamma_pos(sgb_add(b, kd), LT));
+            t1 = sgb_sub(t1, lg_sn);
+            l2 = sgb_add(lc_y, sgb_sub(t1, l0));
+        }
+        l = sgb_logspace_add_lean(l, l2, LT, ET);
+    }
+    if (sp.use_eps) l = sgb_logspace_add_lean(l, sp.log_eps, LT, ET);
+    return l;
+}
+
+#if defined(__CUDA_ARCH__)
+#define SGB_NOINLINE __device__ __noinline__
+#else
+#define SGB_NOINLINE static __attribute__((noinline))
+#endif
+
+// Tables of the per-(total CN, state) constants for total CN < SGB_CN_TABLE, row pitch S
+// (shared memory in the kernel, plain arrays in the host emulation), plus what the
+// untabulated path needs to recompute an entry on the fly.
+struct SgbTables {
+    const double *LT, *ET, *LP, *LQ, *A, *B, *L0;
+    const int* KIND;
+    int S, lik;
+    double loherror, rho;
+};
+
+// rare cases: untabulated total CN (>= 16), p at or outside {0,1}, x outside 0..n, Abias, odd eps
+template <int MODEL, int LIKBB>
+SGB_NOINLINE double sgb_emit_item_slow(int cprime, int in_support, double kd, double nkd, double lc_x, double lc_y,
+                                       double lg_sn, int m, const SgbTables& T, const SgbScalars& sp)
+{
+    SgbStateConst sc;
+    if (cprime < SGB_CN_TABLE) {
+        const int ti = cprime * T.S + m;
+        sc.lp = T.LP[ti]; sc.lq = T.LQ[ti]; sc.kind = T.KIND[ti];
+        sc.a = LIKBB ? T.A[ti] : 0.0; sc.b = LIKBB ? T.B[ti] : 0.0; sc.l0 = LIKBB ? T.L0[ti] : 0.0;
+    } else {
+        sc = sgb_state_const(cprime, m, T.loherror, T.lik, T.rho, sp.bb_s, T.LT);
+    }
+    SgbBin b;
+    b.n = 0; b.x = 0; b.cprime = cprime; b.kd = kd; b.nkd = nkd; b.lc_x = lc_x; b.lc_y = lc_y; b.lg_sn = lg_sn;
+    b.in_support = in_support;
+    return sgb_emission(MODEL, LIKBB, b, m, sc, sp, T.LT, T.ET);
+}
+
+// emission of live state m of one bin: lean path when its preconditions hold, else the general one
+template <int MODEL, int LIKBB>
+SGB_HD double sgb_emit_item(int cprime, int in_support, double kd, double nkd, double lc_x, double lc_y,
+                            double lg_sn, int m, const SgbTables& T, const SgbScalars& sp)
+{
+    const int ti = (cprime < SGB_CN_TABLE) ? cprime * T.S + m : 0;
+    const bool fast = (cprime < SGB_CN_TABLE) && in_support && sp.fast_ok && (T.KIND[ti] == SGB_KIND_NORMAL);
+    if (fast)
+        return sgb_emission_fast<MODEL, LIKBB>(kd, nkd, lc_x, lc_y, lg_sn, T.LP[ti], T.LQ[ti], LIKBB ? T.A[ti] : 0.0,
+                                               LIKBB ? T.B[ti] : 0.0, LIKBB ? T.L0[ti] : 0.0, sp, T.LT, T.ET);
+    return sgb_emit_item_slow<MODEL, LIKBB>(cprime, in_support, kd, nkd, lc_x, lc_y, lg_sn, m, T, sp);
+}
+
 // ------------------------------------------------------------------ forward recursion
 // State of one sequence between bins.  Because the reference's transition matrix has one
 // value on the diagonal (tr_self) and one off it (tr_off), and rounding is monotone,
@@ -206,10 +290,18 @@ SGB_HD void sgb_seq_init(SgbSeqState<SMAX>& st, const double* e, int S, double i
     sgb_top2<SMAX>(st, S);
 }
 
-// One bin (j >= 1).  Returns the state the reference emits for bin j-1:
-// T2[argmax_i T1[i,j], j]  (src/code.cpp:39-42).  e[i] must be -Inf for masked states.
+SGB_HD int sgb_ffs32(unsigned int m)
+{
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)m);
+#else
+    return __builtin_ffs((int)m);
+#endif
+}
+
+// General variant (tr_self < tr_off, i.e. selftransitionprob below 1/S): needs the two largest values.
 template <int SMAX>
-SGB_HD int sgb_seq_step(SgbSeqState<SMAX>& st, const double* e, int S, double tr_self, double tr_off)
+SGB_HD int sgb_seq_step_general(SgbSeqState<SMAX>& st, const double* e, int S, double tr_self, double tr_off)
 {
     double Tn[SMAX];
     const double u1 = sgb_add(st.m1, tr_off), u2 = sgb_add(st.m2, tr_off);
@@ -229,7 +321,6 @@ SGB_HD int sgb_seq_step(SgbSeqState<SMAX>& st, const double* e, int S, double tr
             Tn[i] = -sgb_inf();
         }
     }
-    // predecessor of the column-best state i1, first maximum of (T1[k] + tr[k,i1]) + e[i1]
     double ej = e[0];
 #pragma unroll
     for (int i = 1; i < SMAX; i++) if (i == i1) ej = e[i];
@@ -244,6 +335,65 @@ SGB_HD int sgb_seq_step(SgbSeqState<SMAX>& st, const double* e, int S, double tr
 #pragma unroll
     for (int i = 0; i < SMAX; i++) st.T1[i] = Tn[i];
     st.m1 = m1; st.m2 = m2; st.i1 = i1;
+    return back;
+}
+
+// One bin (j >= 1).  Returns the state the reference emits for bin j-1:
+// T2[argmax_i T1[i,j], j]  (src/code.cpp:39-42).  e[i] must be -Inf for masked states.
+//
+// Diagonal-dominant transition (tr_self >= tr_off, every realistic selftransitionprob): for the state that
+// holds the column maximum m1 the diagonal candidate fl(fl(m1+tr_self)+e) already dominates any
+// off-diagonal one, so fl(fl(m1+tr_off)+e) can stand in for "max over k != i" for EVERY i without
+// changing a bit.  Branch-free: 3 adds + 1 compare per state, one max chain, one equality mask.
+// The predecessor scan runs only when the winner was not reached strictly through its own diagonal.
+// States i >= S (when S < SMAX) are carried as permanently masked states: their e[i] and T1[i] are -Inf,
+// they can never win a strict '>' or an equality against a finite maximum, and when everything is -Inf the
+// first-index rule picks state 0 -- so the loops below run over all SMAX slots without guards.
+// ecol/estride: the same emissions addressable by a run-time index (shared-memory column in the kernel).
+template <int SMAX>
+SGB_HD int sgb_seq_step(SgbSeqState<SMAX>& st, const double* e, const double* ecol, int estride, int S,
+                        double tr_self, double tr_off, int diag_dominant)
+{
+    if (!diag_dominant) return sgb_seq_step_general<SMAX>(st, e, S, tr_self, tr_off);
+    double Tn[SMAX];
+    const double u1 = sgb_add(st.m1, tr_off);
+    unsigned int dmask = 0;                 // bit i: the diagonal candidate of state i is strictly the larger one
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) {
+        double voff = sgb_add(u1, e[i]);
+        double vdia = sgb_add(sgb_add(st.T1[i], tr_self), e[i]);
+        bool dg = vdia > voff;
+        Tn[i] = dg ? vdia : voff;
+        dmask |= dg ? (1u << i) : 0u;
+    }
+    double m1 = Tn[0];
+#pragma unroll
+    for (int i = 1; i < SMAX; i++) m1 = sgb_max(m1, Tn[i]);
+    unsigned int emask = 0;
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) emask |= (Tn[i] == m1) ? (1u << i) : 0u;
+    const int i1 = sgb_ffs32(emask) - 1;    // first maximum (emask is never empty: no NaN reaches here)
+    int back = i1;
+    if (!((dmask >> i1) & 1u)) {
+        // the winner's value came (also) from an off-diagonal predecessor: first k with
+        // (T1[k] + tr[k,i1]) + e[i1] == m1, the reference's own expression
+        const double ej = ecol[i1 * estride];
+        double tj = st.T1[0];
+#pragma unroll
+        for (int i = 1; i < SMAX; i++) if (i == i1) tj = st.T1[i];
+        unsigned int pm = 0;
+#pragma unroll
+        for (int k = 0; k < SMAX; k++) {
+            double val = sgb_add(sgb_add(st.T1[k], tr_off), ej);
+            pm |= (val == m1) ? (1u << k) : 0u;
+        }
+        const double wd = sgb_add(sgb_add(tj, tr_self), ej);
+        pm = (pm & ~(1u << i1)) | ((wd == m1) ? (1u << i1) : 0u);
+        back = sgb_ffs32(pm) - 1;
+    }
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) st.T1[i] = Tn[i];
+    st.m1 = m1; st.i1 = i1;
     return back;
 }
 

@@ -100,20 +100,38 @@ struct SgbDecodeArgs {
 #define SGB_DECODE_THREADS 256
 #define SGB_DECODE_WARPS (SGB_DECODE_THREADS / 32)
 
-static inline size_t decode_smem_bytes(int SMAX, int S, int lik_bb)
+// per-warp shared-memory scratch (in doubles): emission tile E[SMAX][32], per-lane bin fields
+// (x, n-x, log-choose terms, lgamma(s+n)) [NF][32], then 32 ints of (cprime | in_support << 16)
+// and the work queue of (lane | state << 5) entries, SMAX * 32 uint16.
+static inline int decode_nf(int model, int lik_bb) { return 3 + (model == SGB_MODEL_ASCN ? 1 : 0) + (lik_bb ? 1 : 0); }
+static inline size_t decode_warp_doubles(int SMAX, int model, int lik_bb)
+{
+    return (size_t)SMAX * 32 + (size_t)decode_nf(model, lik_bb) * 32 + 16 /* 32 ints */ + (size_t)SMAX * 8 /* SMAX*32 u16 */;
+}
+static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb)
 {
     size_t d = SGB_LOGTAB_LEN + SGB_EXPTAB_LEN + SGB_LFTAB_LEN;
     d += (size_t)SGB_CN_TABLE * S * (lik_bb ? 5 : 2);
-    d += (size_t)SGB_DECODE_WARPS * SMAX * 32;
+    d += (size_t)SGB_DECODE_WARPS * decode_warp_doubles(SMAX, model, lik_bb);
     return d * sizeof(double) + (size_t)SGB_CN_TABLE * S * sizeof(int);
 }
 
+// Fused emission + forward recursion + decode.  One lane per (cell, chromosome) sequence, 32 sequences
+// of similar length per warp, warps fetch groups from a global counter (longest first).
+// Per bin step a warp (1) unpacks its 32 records and looks the log-factorials up in shared memory,
+// (2) compacts the LIVE (lane, state) pairs of all 32 lanes into a queue (prefix sum of the live-state
+// counts), (3) evaluates them two per lane per round -- so lanes with copy number 2 do not idle while a
+// lane with copy number 9 works, and two independent FP64 chains are in flight per thread -- writing
+// E[state][lane], (4) runs the O(S) max-plus step of its own sequence from registers and stores the
+// decoded state of the previous bin.
 template <int SMAX, int MODEL, int LIKBB, int CHAINED>
 __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs A)
 {
     extern __shared__ __align__(16) double smem[];
     const int S = A.S;
     const int CTS = SGB_CN_TABLE * S;
+    constexpr int NF = 3 + (MODEL == SGB_MODEL_ASCN ? 1 : 0) + (LIKBB ? 1 : 0);
+    constexpr int WARP_DOUBLES = SMAX * 32 + NF * 32 + 16 + SMAX * 8;
     double* sLT = smem;
     double* sET = sLT + SGB_LOGTAB_LEN;
     double* sLF = sET + SGB_EXPTAB_LEN;
@@ -122,8 +140,8 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
     double* sA = sLQ + CTS;
     double* sB = sA + (LIKBB ? CTS : 0);
     double* sL0 = sB + (LIKBB ? CTS : 0);
-    double* sE = sL0 + (LIKBB ? CTS : 0);
-    int* sKind = (int*)(sE + SGB_DECODE_WARPS * SMAX * 32);
+    double* sW = sL0 + (LIKBB ? CTS : 0);
+    int* sKind = (int*)(sW + SGB_DECODE_WARPS * WARP_DOUBLES);
 
     for (int i = threadIdx.x; i < SGB_LOGTAB_LEN; i += blockDim.x) sLT[i] = g_logtab[i];
     for (int i = threadIdx.x; i < SGB_EXPTAB_LEN; i += blockDim.x) sET[i] = g_exptab[i];
@@ -138,9 +156,20 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
     const SgbScalars sp = A.tabs->sp;
     __syncthreads();
 
+    SgbTables TB;
+    TB.LT = sLT; TB.ET = sET; TB.LP = sLP; TB.LQ = sLQ; TB.A = sA; TB.B = sB; TB.L0 = sL0; TB.KIND = sKind;
+    TB.S = S; TB.lik = A.lik; TB.loherror = A.loherror; TB.rho = A.rho;
+
     const int lane = threadIdx.x & 31;
     const int wid = threadIdx.x >> 5;
-    double* myE = sE + wid * SMAX * 32;
+    double* myE = sW + wid * WARP_DOUBLES;
+    double* bKD = myE + SMAX * 32;
+    double* bNKD = bKD + 32;
+    double* bLCX = bNKD + 32;
+    double* bLCY = bLCX + 32;                                   // ASCN only
+    double* bLGS = bLCX + (MODEL == SGB_MODEL_ASCN ? 64 : 32);  // beta-binomial only
+    int* bI = (int*)(bKD + NF * 32);
+    unsigned short* q = (unsigned short*)(bI + 32);
     const double NEG_INF = -sgb_inf();
 
     for (;;) {
@@ -164,45 +193,86 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
         st.m1 = NEG_INF; st.m2 = NEG_INF; st.i1 = 0;
         unsigned long long rec_next = (len > 0) ? __ldg(prow) : 0ull;
         int back = 0;
+        int Lprev = SMAX;          // states >= L hold -Inf in this lane's E column; refreshed when L shrinks
         for (int t = 0; t < Tmax; t++) {
             const bool act = t < len;
             const unsigned long long rec = rec_next;
             if (t + 1 < len) rec_next = __ldg(prow + t + 1);
-            SgbBin b;
+            // ---- (1) per-bin quantities of this lane's sequence
             int L = 0;
             if (act) {
-                b = sgb_bin_prepare(MODEL, LIKBB, (int)(rec & SGB_COUNT_MASK),
-                                    (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK), (int)(rec >> 56), sp.bb_s, sLF,
-                                    sLT);
-                L = sgb_live_states(MODEL, b.cprime, S);
-            }
-            const int Lw = __reduce_max_sync(SGB_FULL, L);
-            // ---- emission of the live states (masked states are -Inf by construction)
-            for (int i = 0; i < Lw; i++) {
-                if (i < L) {
-                    SgbStateConst sc;
-                    if (b.cprime < SGB_CN_TABLE) {
-                        const int ti = b.cprime * S + i;
-                        sc.lp = sLP[ti]; sc.lq = sLQ[ti]; sc.kind = sKind[ti];
-                        if (LIKBB) { sc.a = sA[ti]; sc.b = sB[ti]; sc.l0 = sL0[ti]; }
-                        else { sc.a = 0.0; sc.b = 0.0; sc.l0 = 0.0; }
-                    } else {
-                        sc = sgb_state_const(b.cprime, i, A.loherror, A.lik, A.rho, sp.bb_s, sLT);
-                    }
-                    myE[i * 32 + lane] = sgb_emission(MODEL, LIKBB, b, i, sc, sp, sLT, sET);
+                const int n = (int)(rec & SGB_COUNT_MASK), x = (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK);
+                const int cprime = sgb_cprime(MODEL, (int)(rec >> 56));
+                const int ins = x <= n;
+                L = sgb_live_states(MODEL, cprime, S);
+                double lcx = 0.0, lcy = 0.0, lgs = 0.0;
+                if (ins) {
+                    const double fn = sgb_logfact(n, sLF, sLT), fx = sgb_logfact(x, sLF, sLT),
+                                 fy = sgb_logfact(n - x, sLF, sLT);
+                    lcx = sgb_sub(sgb_sub(fn, fx), fy);
+                    if (MODEL == SGB_MODEL_ASCN) lcy = sgb_sub(sgb_sub(fn, fy), fx);
+                    if (LIKBB) lgs = sgb_lgamma(sgb_add(sp.bb_s, (double)n), sLT);
                 }
+                bKD[lane] = (double)x;
+                bNKD[lane] = (double)(n - x);
+                bLCX[lane] = lcx;
+                if (MODEL == SGB_MODEL_ASCN) bLCY[lane] = lcy;
+                if (LIKBB) bLGS[lane] = lgs;
+                bI[lane] = cprime | (ins << 16);
+                for (int i = L; i < Lprev; i++) myE[i * 32 + lane] = NEG_INF;      // rare: only when L shrinks
+                Lprev = L;
+            }
+            // ---- (2) queue of live (lane, state) pairs
+            int incl = L;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int v = __shfl_up_sync(SGB_FULL, incl, d);
+                if (lane >= d) incl += v;
+            }
+            const int tot = __shfl_sync(SGB_FULL, incl, 31);
+            const int qoff = incl - L;
+            for (int m = 0; m < L; m++) q[qoff + m] = (unsigned short)(lane | (m << 5));
+            __syncwarp();
+            // ---- (3) emissions, two queue entries per lane per round
+            for (int base = 0; base < tot; base += 64) {
+                const int j0 = base + lane, j1 = j0 + 32;
+                const bool v0 = j0 < tot, v1 = j1 < tot;
+                const int en0 = v0 ? q[j0] : 0, en1 = v1 ? q[j1] : 0;
+                const int ol0 = en0 & 31, m0 = en0 >> 5, ol1 = en1 & 31, m1 = en1 >> 5;
+                const int bi0 = bI[ol0], bi1 = bI[ol1];
+                const int c0 = bi0 & 0xffff, c1 = bi1 & 0xffff, in0 = bi0 >> 16, in1 = bi1 >> 16;
+                const double kd0 = bKD[ol0], nk0 = bNKD[ol0], lx0 = bLCX[ol0];
+                const double kd1 = bKD[ol1], nk1 = bNKD[ol1], lx1 = bLCX[ol1];
+                const double ly0 = (MODEL == SGB_MODEL_ASCN) ? bLCY[ol0] : 0.0, ly1 = (MODEL == SGB_MODEL_ASCN) ? bLCY[ol1] : 0.0;
+                const double gs0 = LIKBB ? bLGS[ol0] : 0.0, gs1 = LIKBB ? bLGS[ol1] : 0.0;
+                const int t0 = (c0 < SGB_CN_TABLE) ? c0 * S + m0 : 0, t1 = (c1 < SGB_CN_TABLE) ? c1 * S + m1 : 0;
+                const bool f0 = (c0 < SGB_CN_TABLE) && in0 && (sKind[t0] == SGB_KIND_NORMAL);
+                const bool f1 = (c1 < SGB_CN_TABLE) && in1 && (sKind[t1] == SGB_KIND_NORMAL);
+                double r0, r1;
+                if (f0 && f1 && sp.fast_ok) {
+                    // both lean: one basic block, two independent dependency chains
+                    r0 = sgb_emission_fast<MODEL, LIKBB>(kd0, nk0, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
+                                                         LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, sp, sLT, sET);
+                    r1 = sgb_emission_fast<MODEL, LIKBB>(kd1, nk1, lx1, ly1, gs1, sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0,
+                                                         LIKBB ? sB[t1] : 0.0, LIKBB ? sL0[t1] : 0.0, sp, sLT, sET);
+                } else {
+                    r0 = sgb_emit_item<MODEL, LIKBB>(c0, in0, kd0, nk0, lx0, ly0, gs0, m0, TB, sp);
+                    r1 = v1 ? sgb_emit_item<MODEL, LIKBB>(c1, in1, kd1, nk1, lx1, ly1, gs1, m1, TB, sp) : 0.0;
+                }
+                if (v0) myE[m0 * 32 + ol0] = r0;
+                if (v1) myE[m1 * 32 + ol1] = r1;
             }
             __syncwarp();
-            // ---- forward recursion + decode
+            // ---- (4) forward recursion + decode of this lane's sequence
             if (act) {
                 double e[SMAX];
 #pragma unroll
-                for (int i = 0; i < SMAX; i++) e[i] = (i < L) ? myE[i * 32 + lane] : NEG_INF;
+                for (int i = 0; i < SMAX; i++) e[i] = myE[i * 32 + lane];
                 if (t == 0) {
                     sgb_seq_init<SMAX>(st, e, S, sp.init);
                     if (CHAINED == 0 && len == 1) A.state_out[ostart] = 0;
                 } else if (CHAINED == 0) {
-                    back = sgb_seq_step<SMAX>(st, e, S, sp.tr_self, sp.tr_off);
+                    back = sgb_seq_step<SMAX>(st, e, myE + lane, 32, S, sp.tr_self, sp.tr_off, sp.diag_dominant);
                     A.state_out[ostart + t - 1] = (uint8_t)back;
                     if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
                 } else {
@@ -222,7 +292,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
 template <int SMAX, int MODEL, int LIKBB, int CHAINED>
 static cudaError_t launch_decode(const SgbDecodeArgs& A, int sm_count, cudaStream_t st)
 {
-    size_t smem = decode_smem_bytes(SMAX, A.S, LIKBB);
+    size_t smem = decode_smem_bytes(SMAX, A.S, MODEL, LIKBB);
     auto kern = k_decode<SMAX, MODEL, LIKBB, CHAINED>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

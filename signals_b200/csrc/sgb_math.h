@@ -34,6 +34,17 @@
 
 #define SGB_SHIFT (0x1.8p52)
 
+// Scalar constants: host code uses the hex-float literals; device code reads the same values from
+// the constant bank (operand-folded into DFMA/DADD instead of two 32-bit immediate moves per use).
+#if defined(__CUDACC__)
+static __constant__ double sgb_kdev[SGB_NK] = SGB_KTAB_INIT;
+#endif
+#if defined(__CUDA_ARCH__)
+#define SGB_C(name) (sgb_kdev[SGB_KI_##name])
+#else
+#define SGB_C(name) (SGB_##name)
+#endif
+
 // ---------------------------------------------------------------- primitives
 SGB_HD uint64_t sgb_d2u(double x)
 {
@@ -106,25 +117,31 @@ SGB_HD double sgb_fmax(double a, double b)
 // exp(x) = 2^q * T[j] * (1 + p(r)),  x = (64 q + j) ln2/64 + r,  |r| <= ln2/128.
 // Results below 2^-1022 are flushed to +0 (x <= -708): the only caller that can
 // get there is logspace_add, where exp(d) is added to 1 -- irrelevant there.
+// core: valid for x in [-708, 709], no special-value handling
+SGB_HD double sgb_exp_core(double x, const double* __restrict__ ET)
+{
+    double t  = sgb_fma(x, SGB_C(INVLN2_N), SGB_SHIFT);
+    double kd = sgb_sub(t, SGB_SHIFT);
+    int32_t k = (int32_t)(uint32_t)sgb_d2u(t);
+    double r  = sgb_fma(kd, -SGB_C(LN2N_HI), x);
+    r = sgb_fma(kd, -SGB_C(LN2N_LO), r);
+    int32_t j = k & (SGB_NEXP - 1);
+    int64_t q = (int64_t)(k >> 6);
+    double s = sgb_u2d(sgb_d2u(ET[j]) + ((uint64_t)q << 52));
+    double p = sgb_fma(r, SGB_C(EXPC6), SGB_C(EXPC5));
+    p = sgb_fma(r, p, SGB_C(EXPC4));
+    p = sgb_fma(r, p, SGB_C(EXPC3));
+    p = sgb_fma(r, p, SGB_C(EXPC2));
+    p = sgb_fma(r, p, 1.0);
+    p = sgb_mul(r, p);
+    return sgb_fma(s, p, s);
+}
+
 SGB_HD double sgb_exp(double x, const double* __restrict__ ET)
 {
     if (!(x > -708.0)) return (x != x) ? x : 0.0;
     if (x > 709.0) return sgb_inf();      // (overflow threshold rounded down from 709.78; never reached: callers pass x <= 0)
-    double t  = sgb_fma(x, SGB_INVLN2_N, SGB_SHIFT);
-    double kd = sgb_sub(t, SGB_SHIFT);
-    int32_t k = (int32_t)(uint32_t)sgb_d2u(t);
-    double r  = sgb_fma(kd, -SGB_LN2N_HI, x);
-    r = sgb_fma(kd, -SGB_LN2N_LO, r);
-    int32_t j = k & (SGB_NEXP - 1);
-    int64_t q = (int64_t)(k >> 6);
-    double s = sgb_u2d(sgb_d2u(ET[j]) + ((uint64_t)q << 52));
-    double p = sgb_fma(r, SGB_EXPC6, SGB_EXPC5);
-    p = sgb_fma(r, p, SGB_EXPC4);
-    p = sgb_fma(r, p, SGB_EXPC3);
-    p = sgb_fma(r, p, SGB_EXPC2);
-    p = sgb_fma(r, p, 1.0);
-    p = sgb_mul(r, p);
-    return sgb_fma(s, p, s);
+    return sgb_exp_core(x, ET);
 }
 
 // ---------------------------------------------------------------- log
@@ -141,16 +158,16 @@ SGB_HD double sgb_log_core(uint64_t ix, int32_t kadj, const double* __restrict__
     if (rcp_seed) *rcp_seed = sgb_u2d(sgb_d2u(invc) - ((uint64_t)(int64_t)k << 52));
     double r = sgb_fma(w, invc, -1.0);
     double kd = (double)(k + kadj);
-    double p = sgb_fma(r, SGB_LOGC9, SGB_LOGC8);
-    p = sgb_fma(r, p, SGB_LOGC7);
-    p = sgb_fma(r, p, SGB_LOGC6);
-    p = sgb_fma(r, p, SGB_LOGC5);
-    p = sgb_fma(r, p, SGB_LOGC4);
-    p = sgb_fma(r, p, SGB_LOGC3);
-    p = sgb_fma(r, p, SGB_LOGC2);
+    double p = sgb_fma(r, SGB_C(LOGC9), SGB_C(LOGC8));
+    p = sgb_fma(r, p, SGB_C(LOGC7));
+    p = sgb_fma(r, p, SGB_C(LOGC6));
+    p = sgb_fma(r, p, SGB_C(LOGC5));
+    p = sgb_fma(r, p, SGB_C(LOGC4));
+    p = sgb_fma(r, p, SGB_C(LOGC3));
+    p = sgb_fma(r, p, SGB_C(LOGC2));
     double r2 = sgb_mul(r, r);
-    double lo = sgb_fma(r2, p, sgb_mul(kd, SGB_LN2_LO));
-    double hi = sgb_fma(kd, SGB_LN2_HI, logc);
+    double lo = sgb_fma(r2, p, sgb_mul(kd, SGB_C(LN2_LO)));
+    double hi = sgb_fma(kd, SGB_C(LN2_HI), logc);
     return sgb_add(hi, sgb_add(r, lo));
 }
 
@@ -169,19 +186,19 @@ SGB_HD double sgb_log1pf_series(double f)
 {
     double s = sgb_div(f, sgb_add(2.0, f));
     double z = sgb_mul(s, s);
-    double R = sgb_fma(z, SGB_ATHC14, SGB_ATHC13);
-    R = sgb_fma(z, R, SGB_ATHC12);
-    R = sgb_fma(z, R, SGB_ATHC11);
-    R = sgb_fma(z, R, SGB_ATHC10);
-    R = sgb_fma(z, R, SGB_ATHC9);
-    R = sgb_fma(z, R, SGB_ATHC8);
-    R = sgb_fma(z, R, SGB_ATHC7);
-    R = sgb_fma(z, R, SGB_ATHC6);
-    R = sgb_fma(z, R, SGB_ATHC5);
-    R = sgb_fma(z, R, SGB_ATHC4);
-    R = sgb_fma(z, R, SGB_ATHC3);
-    R = sgb_fma(z, R, SGB_ATHC2);
-    R = sgb_fma(z, R, SGB_ATHC1);
+    double R = sgb_fma(z, SGB_C(ATHC14), SGB_C(ATHC13));
+    R = sgb_fma(z, R, SGB_C(ATHC12));
+    R = sgb_fma(z, R, SGB_C(ATHC11));
+    R = sgb_fma(z, R, SGB_C(ATHC10));
+    R = sgb_fma(z, R, SGB_C(ATHC9));
+    R = sgb_fma(z, R, SGB_C(ATHC8));
+    R = sgb_fma(z, R, SGB_C(ATHC7));
+    R = sgb_fma(z, R, SGB_C(ATHC6));
+    R = sgb_fma(z, R, SGB_C(ATHC5));
+    R = sgb_fma(z, R, SGB_C(ATHC4));
+    R = sgb_fma(z, R, SGB_C(ATHC3));
+    R = sgb_fma(z, R, SGB_C(ATHC2));
+    R = sgb_fma(z, R, SGB_C(ATHC1));
     R = sgb_mul(z, R);
     double hfsq = sgb_mul(0.5, sgb_mul(f, f));
     return sgb_sub(f, sgb_sub(hfsq, sgb_mul(s, sgb_add(hfsq, R))));
@@ -199,27 +216,33 @@ SGB_HD double sgb_log(double x, const double* __restrict__ LT)
     return sgb_log_tab(x, LT);
 }
 
-// log1p(u) for u in [0,1] (hot path: u = exp(-|a-b|) inside logspace_add).
-SGB_HD double sgb_log1p_01(double u, const double* __restrict__ LT)
+// core of log1p(u) for u in [0,1) given w = fl(1+u) < 2 (no checks)
+SGB_HD double sgb_log1p01_core(double u, double w, const double* __restrict__ LT)
 {
-    if (!(u < 1.0)) return (u == 1.0) ? SGB_LN2 : ((u != u) ? u : sgb_nan());
-    double w = sgb_add(1.0, u);
-    if (w >= 2.0) return SGB_LN2;
     double c = sgb_sub(u, sgb_sub(w, 1.0));          // exact rounding residual of 1+u
     uint64_t m = sgb_d2u(w) & 0x000fffffffffffffULL;
     int32_t i = (int32_t)(m >> 45);
     double invc = LT[2 * i], logc = LT[2 * i + 1];
     double r = sgb_fma(w, invc, -1.0);
-    double p = sgb_fma(r, SGB_LOGC9, SGB_LOGC8);
-    p = sgb_fma(r, p, SGB_LOGC7);
-    p = sgb_fma(r, p, SGB_LOGC6);
-    p = sgb_fma(r, p, SGB_LOGC5);
-    p = sgb_fma(r, p, SGB_LOGC4);
-    p = sgb_fma(r, p, SGB_LOGC3);
-    p = sgb_fma(r, p, SGB_LOGC2);
+    double p = sgb_fma(r, SGB_C(LOGC9), SGB_C(LOGC8));
+    p = sgb_fma(r, p, SGB_C(LOGC7));
+    p = sgb_fma(r, p, SGB_C(LOGC6));
+    p = sgb_fma(r, p, SGB_C(LOGC5));
+    p = sgb_fma(r, p, SGB_C(LOGC4));
+    p = sgb_fma(r, p, SGB_C(LOGC3));
+    p = sgb_fma(r, p, SGB_C(LOGC2));
     double r2 = sgb_mul(r, r);
     double lo = sgb_fma(r2, p, sgb_mul(c, invc));
     return sgb_add(logc, sgb_add(r, lo));
+}
+
+// log1p(u) for u in [0,1] (hot path: u = exp(-|a-b|) inside logspace_add).
+SGB_HD double sgb_log1p_01(double u, const double* __restrict__ LT)
+{
+    if (!(u < 1.0)) return (u == 1.0) ? SGB_C(LN2) : ((u != u) ? u : sgb_nan());
+    double w = sgb_add(1.0, u);
+    if (w >= 2.0) return SGB_C(LN2);
+    return sgb_log1p01_core(u, w, LT);
 }
 
 // General log1p for x > -1 (cold path: log1p(-p) for the per-(CN,state) tables).
@@ -237,22 +260,39 @@ SGB_HD double sgb_log1p(double x, const double* __restrict__ LT)
 
 // ---------------------------------------------------------------- logspace_add
 // src/code.cpp:5-8  fmax(a,b) + log1p(exp(-fabs(a-b))), same NaN/Inf behaviour.
+SGB_HD double sgb_max(double a, double b)            // operands are never NaN here (fmax would add NaN fix-ups)
+{
+    return (a > b) ? a : b;
+}
+
+// Branch-free body, valid when neither operand is NaN and they are not the same infinity.
+// exp(d) is +0 for d <= -708 and log1p(1) is ln 2, as in sgb_exp / sgb_log1p_01.
+SGB_HD double sgb_logspace_add_lean(double a, double b, const double* __restrict__ LT, const double* __restrict__ ET)
+{
+    double mx = sgb_max(a, b);
+    double d = sgb_u2d(sgb_d2u(sgb_sub(a, b)) | 0x8000000000000000ULL);      // -fabs(a-b)
+    double u = sgb_exp_core(sgb_max(d, -708.0), ET);
+    u = (d > -708.0) ? u : 0.0;
+    double w = sgb_add(1.0, u);
+    double lp = sgb_log1p01_core(u, w, LT);
+    lp = (w >= 2.0) ? SGB_C(LN2) : lp;
+    return sgb_add(mx, lp);
+}
+
 SGB_HD double sgb_logspace_add(double a, double b, const double* __restrict__ LT, const double* __restrict__ ET)
 {
-    double mx = sgb_fmax(a, b);
-    double d = sgb_u2d(sgb_d2u(sgb_sub(a, b)) | 0x8000000000000000ULL);   // -fabs(a-b), NaN stays NaN
-    return sgb_add(mx, sgb_log1p_01(sgb_exp(d, ET), LT));
+    if (a != a || b != b) return sgb_nan();
+    if (a == b && sgb_fabs(a) == sgb_inf()) return sgb_nan();               // Inf - Inf
+    return sgb_logspace_add_lean(a, b, LT, ET);
 }
 
 // ---------------------------------------------------------------- lgamma (z > 0)
 // z < 10 is shifted up with the recurrence (P = z(z+1)...(z+k-1)), then
 // Stirling with 7 correction terms; 1/y by two cubic Newton steps from the
 // table seed (no division instruction on the hot path).
-SGB_HD double sgb_lgamma(double z, const double* __restrict__ LT)
+// core: finite z > 0, no special-value handling
+SGB_HD double sgb_lgamma_pos(double z, const double* __restrict__ LT)
 {
-    if (z != z) return z;
-    if (!(z > 0.0)) return (z == 0.0) ? sgb_inf() : sgb_nan();
-    if (z == sgb_inf()) return z;
     double P = 1.0, y = z;
     int k = 0;
     while (y < 10.0) {
@@ -271,20 +311,28 @@ SGB_HD double sgb_lgamma(double z, const double* __restrict__ LT)
         t = sgb_fma(e, e, e);
         rr = sgb_fma(rr, t, rr);
         double r2 = sgb_mul(rr, rr);
-        double c = sgb_fma(r2, SGB_STIR7, SGB_STIR6);
-        c = sgb_fma(r2, c, SGB_STIR5);
-        c = sgb_fma(r2, c, SGB_STIR4);
-        c = sgb_fma(r2, c, SGB_STIR3);
-        c = sgb_fma(r2, c, SGB_STIR2);
-        c = sgb_fma(r2, c, SGB_STIR1);
+        double c = sgb_fma(r2, SGB_C(STIR7), SGB_C(STIR6));
+        c = sgb_fma(r2, c, SGB_C(STIR5));
+        c = sgb_fma(r2, c, SGB_C(STIR4));
+        c = sgb_fma(r2, c, SGB_C(STIR3));
+        c = sgb_fma(r2, c, SGB_C(STIR2));
+        c = sgb_fma(r2, c, SGB_C(STIR1));
         corr = sgb_mul(rr, c);
         // y = fl(z+k): fold the rounding residual back in with lgamma'(y) ~ log y - 1/(2y)
         double dy = sgb_sub(z, sgb_sub(y, (double)k));
         corr = sgb_fma(dy, sgb_fma(-0.5, rr, ly), corr);
     }
-    double res = sgb_add(sgb_fma(sgb_sub(y, 0.5), ly, -y), sgb_add(SGB_HALF_LN_2PI, corr));
+    double res = sgb_add(sgb_fma(sgb_sub(y, 0.5), ly, -y), sgb_add(SGB_C(HALF_LN_2PI), corr));
     if (k > 0) res = sgb_sub(res, sgb_log_tab(P, LT));
     return res;
+}
+
+SGB_HD double sgb_lgamma(double z, const double* __restrict__ LT)
+{
+    if (z != z) return z;
+    if (!(z > 0.0)) return (z == 0.0) ? sgb_inf() : sgb_nan();
+    if (z == sgb_inf()) return z;
+    return sgb_lgamma_pos(z, LT);
 }
 
 // ---------------------------------------------------------------- log-factorial

@@ -9,27 +9,38 @@ static const double LT[SGB_LOGTAB_LEN] = SGB_LOGTAB_INIT;
 static const double ET[SGB_EXPTAB_LEN] = SGB_EXPTAB_INIT;
 static const double LF[SGB_LFTAB_LEN] = SGB_LFTAB_INIT;
 
-template <int SMAX>
-static void run(int model, int lik, int S, int decode, double loherror, double eps, double rho, double Abias,
-                double stp, long T, const int* n, const int* x, const int* cn, unsigned char* out, double* l_out)
+template <int SMAX, int MODEL, int LIKBB>
+static void run(int S, int decode, double loherror, double eps, double rho, double Abias, double stp, long T,
+                const int* n, const int* x, const int* cn, unsigned char* out, double* l_out)
 {
-    const int lik_bb = (lik == SGB_LIK_BETABINOMIAL) && rho > 0.0;
-    SgbScalars sp = sgb_scalars(S, eps, Abias, stp, rho, LT);
+    const int lik = LIKBB ? SGB_LIK_BETABINOMIAL : SGB_LIK_BINOMIAL;
+    SgbScalars sp = sgb_scalars(S, eps, Abias, stp, LIKBB ? rho : 0.0, LT);
+    // the per-(CN, state) tables exactly as k_setup fills them
+    std::vector<double> tLP(SGB_CN_TABLE * S), tLQ(SGB_CN_TABLE * S), tA(SGB_CN_TABLE * S), tB(SGB_CN_TABLE * S),
+        tL0(SGB_CN_TABLE * S);
+    std::vector<int> tK(SGB_CN_TABLE * S);
+    for (int c = 0; c < SGB_CN_TABLE; c++)
+        for (int m = 0; m < S; m++) {
+            SgbStateConst sc = sgb_state_const(c, m, loherror, lik, rho, sp.bb_s, LT);
+            int i = c * S + m;
+            tLP[i] = sc.lp; tLQ[i] = sc.lq; tA[i] = sc.a; tB[i] = sc.b; tL0[i] = sc.l0; tK[i] = sc.kind;
+        }
+    SgbTables TB;
+    TB.LT = LT; TB.ET = ET; TB.LP = tLP.data(); TB.LQ = tLQ.data(); TB.A = tA.data(); TB.B = tB.data();
+    TB.L0 = tL0.data(); TB.KIND = tK.data(); TB.S = S; TB.lik = lik; TB.loherror = loherror; TB.rho = rho;
     SgbSeqState<SMAX> st;
     std::vector<unsigned char> bp((size_t)T * S);
     for (long t = 0; t < T; t++) {
-        SgbBin b = sgb_bin_prepare(model, lik_bb, n[t], x[t], cn[t], sp.bb_s, LF, LT);
-        int L = sgb_live_states(model, b.cprime, S);
+        SgbBin b = sgb_bin_prepare(MODEL, LIKBB, n[t], x[t], cn[t], sp.bb_s, LF, LT);
+        int L = sgb_live_states(MODEL, b.cprime, S);
         double e[SMAX];
         for (int i = 0; i < SMAX; i++) e[i] = -sgb_inf();
-        for (int i = 0; i < L; i++) {
-            SgbStateConst sc = sgb_state_const(b.cprime, i, loherror, lik, rho, sp.bb_s, LT);
-            e[i] = sgb_emission(model, lik_bb, b, i, sc, sp, LT, ET);
-        }
+        for (int i = 0; i < L; i++)
+            e[i] = sgb_emit_item<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, i, TB, sp);
         if (l_out) for (int i = 0; i < S; i++) l_out[t + T * i] = e[i];
         if (t == 0) { sgb_seq_init<SMAX>(st, e, S, sp.init); continue; }
         if (decode == SGB_DECODE_REFERENCE) {
-            int back = sgb_seq_step<SMAX>(st, e, S, sp.tr_self, sp.tr_off);
+            int back = sgb_seq_step<SMAX>(st, e, e, 1, S, sp.tr_self, sp.tr_off, sp.diag_dominant);
             out[t - 1] = (unsigned char)back;
         } else {
             sgb_seq_step_chained<SMAX>(st, e, S, sp.tr_self, sp.tr_off, &bp[(size_t)t * S]);
@@ -44,13 +55,24 @@ static void run(int model, int lik, int S, int decode, double loherror, double e
     }
 }
 
+template <int SMAX>
+static void run_s(int model, int lik_bb, int S, int decode, double loherror, double eps, double rho, double Abias,
+                  double stp, long T, const int* n, const int* x, const int* cn, unsigned char* out, double* l_out)
+{
+    if (model == 0 && !lik_bb) run<SMAX, 0, 0>(S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
+    else if (model == 0) run<SMAX, 0, 1>(S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
+    else if (!lik_bb) run<SMAX, 1, 0>(S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
+    else run<SMAX, 1, 1>(S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
+}
+
 extern "C" int emu_decode_sequence(int model, int lik, int S, int decode, double loherror, double eps, double rho,
                                    double Abias, double stp, long T, const int* n, const int* x, const int* cn,
                                    unsigned char* out, double* l_out)
 {
     if (T <= 0) return 0;
-    if (S <= 12) run<12>(model, lik, S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
-    else if (S <= 32) run<32>(model, lik, S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
+    const int lik_bb = (lik == SGB_LIK_BETABINOMIAL) && rho > 0.0;
+    if (S <= 12) run_s<12>(model, lik_bb, S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
+    else if (S <= 32) run_s<32>(model, lik_bb, S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
     else return -1;
     return 0;
 }
