@@ -129,6 +129,7 @@ struct Slot {
 struct Ctx {
     int device = -1;
     int sm_count = 148;
+    int stage = 1;              // record staging of k_decode: 1 = TMA bulk copies (default), 0 = plain LDG (SGB_STAGE=ldg)
     Slot slot[2];
     cudaStream_t main = nullptr;
     cudaEvent_t ev_setup = nullptr;
@@ -158,6 +159,10 @@ int get_ctx(Ctx** out)
             return fail(std::string("device ") + prop.name + " is not sm_100-class; libsignals_b200 is built for sm_100a only");
         }
         c->sm_count = prop.multiProcessorCount;
+        {
+            const char* e = getenv("SGB_STAGE");
+            c->stage = (e && (!strcmp(e, "ldg") || !strcmp(e, "0"))) ? 0 : 1;
+        }
         SGB_CUDA(cudaStreamCreate(&c->main));
         SGB_CUDA(cudaEventCreateWithFlags(&c->ev_setup, cudaEventDisableTiming));
         for (int i = 0; i < 2; i++) {
@@ -275,7 +280,7 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
             SGB_CUDA(sgbk_pack((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, pd,
                                (unsigned long long*)SL.packed.p, C->d_err, st));
             SGB_CUDA(sgbk_decode(pd, (const unsigned long long*)SL.packed.p, C->d_tabs, m, (uint8_t*)SL.out.p,
-                                 (uint8_t*)SL.bp.p, (int*)SL.last_state.p, SL.counter, C->sm_count, st));
+                                 (uint8_t*)SL.bp.p, (int*)SL.last_state.p, SL.counter, C->sm_count, C->stage, st));
             if (m.decode == SGB_DECODE_CHAINED)
                 SGB_CUDA(sgbk_backtrace(pd, (const uint8_t*)SL.bp.p, (const int*)SL.last_state.p, S, (uint8_t*)SL.out.p, st));
             SGB_CUDA(cudaMemcpyAsync(state_out + r0, SL.out.p, (size_t)rows, cudaMemcpyDeviceToHost, st));
@@ -524,7 +529,7 @@ int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t*
     SGB_CUDA(sgbk_pack(d_n, d_x, d_cn, cn_itemsize, pl->pd, (unsigned long long*)pl->packed.p, pl->d_err, st));
     if (pl->timing) SGB_CUDA(cudaEventRecord(pl->ev[slot][1], st));
     SGB_CUDA(sgbk_decode(pl->pd, (const unsigned long long*)pl->packed.p, pl->d_tabs, m, d_state_out,
-                         (uint8_t*)pl->bp.p, (int*)pl->last_state.p, pl->counter, C->sm_count, st));
+                         (uint8_t*)pl->bp.p, (int*)pl->last_state.p, pl->counter, C->sm_count, C->stage, st));
     if (pl->timing) { SGB_CUDA(cudaEventRecord(pl->ev[slot][2], st)); pl->calls++; }
     if (m.decode == SGB_DECODE_CHAINED)
         SGB_CUDA(sgbk_backtrace(pl->pd, (const uint8_t*)pl->bp.p, (const int*)pl->last_state.p, m.S, d_state_out, st));

@@ -357,34 +357,33 @@ SGB_HD int sgb_seq_step(SgbSeqState<SMAX>& st, const double* e, const double* ec
     if (!diag_dominant) return sgb_seq_step_general<SMAX>(st, e, S, tr_self, tr_off);
     double Tn[SMAX];
     const double u1 = sgb_add(st.m1, tr_off);
-    unsigned int dmask = 0;                 // bit i: the diagonal candidate of state i is strictly the larger one
 #pragma unroll
     for (int i = 0; i < SMAX; i++) {
-        double voff = sgb_add(u1, e[i]);
-        double vdia = sgb_add(sgb_add(st.T1[i], tr_self), e[i]);
-        bool dg = vdia > voff;
-        Tn[i] = dg ? vdia : voff;
-        dmask |= dg ? (1u << i) : 0u;
+        const double voff = sgb_add(u1, e[i]);
+        const double vdia = sgb_add(sgb_add(st.T1[i], tr_self), e[i]);
+        Tn[i] = (vdia > voff) ? vdia : voff;
     }
     double m1 = Tn[0];
+    int i1 = 0;
 #pragma unroll
-    for (int i = 1; i < SMAX; i++) m1 = sgb_max(m1, Tn[i]);
-    unsigned int emask = 0;
-#pragma unroll
-    for (int i = 0; i < SMAX; i++) emask |= (Tn[i] == m1) ? (1u << i) : 0u;
-    const int i1 = sgb_ffs32(emask) - 1;    // first maximum (emask is never empty: no NaN reaches here)
+    for (int i = 1; i < SMAX; i++) {
+        const bool gt = Tn[i] > m1;          // strict: the first maximum keeps the lowest index
+        m1 = gt ? Tn[i] : m1;
+        i1 = gt ? i : i1;
+    }
     int back = i1;
-    if (!((dmask >> i1) & 1u)) {
-        // the winner's value came (also) from an off-diagonal predecessor: first k with
-        // (T1[k] + tr[k,i1]) + e[i1] == m1, the reference's own expression
-        const double ej = ecol[i1 * estride];
+    const double ej = ecol[i1 * estride];
+    if (m1 == sgb_add(u1, ej)) {
+        // The winner's value equals its off-diagonal candidate (its diagonal one is not strictly larger), so a
+        // predecessor other than i1 may hold the first maximum: find the first k with
+        // (T1[k] + tr[k,i1]) + e[i1] == m1 -- the reference's own expression (src/code.cpp:29-31).
         double tj = st.T1[0];
 #pragma unroll
         for (int i = 1; i < SMAX; i++) if (i == i1) tj = st.T1[i];
         unsigned int pm = 0;
 #pragma unroll
         for (int k = 0; k < SMAX; k++) {
-            double val = sgb_add(sgb_add(st.T1[k], tr_off), ej);
+            const double val = sgb_add(sgb_add(st.T1[k], tr_off), ej);
             pm |= (val == m1) ? (1u << k) : 0u;
         }
         const double wd = sgb_add(sgb_add(tj, tr_self), ej);

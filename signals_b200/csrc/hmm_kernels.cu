@@ -99,39 +99,73 @@ struct SgbDecodeArgs {
 
 #define SGB_DECODE_THREADS 256
 #define SGB_DECODE_WARPS (SGB_DECODE_THREADS / 32)
+#define SGB_STAGE_LDG 0        // records read straight from global memory (one LDG.64 per lane per bin)
+#define SGB_STAGE_TMA 1        // records staged through shared memory by 1-D bulk copies (cp.async.bulk + mbarrier)
+#define SGB_CH 8               // records per lane per staged chunk
+#define SGB_PITCH 10           // row pitch of a staged chunk in records (80 B: 16-byte aligned rows)
 
-// per-warp shared-memory scratch (in doubles): emission tile E[SMAX][32], per-lane bin fields
-// (x, n-x, log-choose terms, lgamma(s+n)) [NF][32], then 32 ints of (cprime | in_support << 16)
-// and the work queue of (lane | state << 5) entries, SMAX * 32 uint16.
-static inline int decode_nf(int model, int lik_bb) { return 3 + (model == SGB_MODEL_ASCN ? 1 : 0) + (lik_bb ? 1 : 0); }
-static inline size_t decode_warp_doubles(int SMAX, int model, int lik_bb)
+// ---- TMA (bulk asynchronous copy) / mbarrier wrappers --------------------------------------
+__device__ __forceinline__ unsigned sgb_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void sgb_mbar_init(unsigned long long* bar, unsigned count)
 {
-    return (size_t)SMAX * 32 + (size_t)decode_nf(model, lik_bb) * 32 + 16 /* 32 ints */ + (size_t)SMAX * 8 /* SMAX*32 u16 */;
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(sgb_smem_u32(bar)), "r"(count) : "memory");
 }
-static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb)
+__device__ __forceinline__ void sgb_mbar_expect_tx(unsigned long long* bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(sgb_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void sgb_tma_load_1d(void* dst, const void* src, unsigned bytes, unsigned long long* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(sgb_smem_u32(dst)), "l"(src), "r"(bytes), "r"(sgb_smem_u32(bar)) : "memory");
+}
+// bounded spin: a mis-programmed pipeline traps instead of hanging the device
+__device__ __forceinline__ void sgb_mbar_wait(unsigned long long* bar, unsigned parity)
+{
+    unsigned done = 0;
+    for (unsigned spin = 0; !done; ++spin) {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(sgb_smem_u32(bar)), "r"(parity) : "memory");
+        if (spin > (1u << 26)) __trap();
+    }
+}
+
+// per-warp shared-memory scratch, in doubles (see the pointer carving in k_decode)
+static inline size_t decode_warp_doubles(int SMAX, int model, int lik_bb, int stage)
+{
+    size_t d = (size_t)SMAX * 32 + 64 + (model == SGB_MODEL_ASCN ? 64 : 32) + (lik_bb ? 32 : 0) + 16 + (size_t)SMAX * 8;
+    if (stage == SGB_STAGE_TMA) d += 2 * 32 * SGB_PITCH + 2;
+    return d;
+}
+static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb, int stage)
 {
     size_t d = SGB_LOGTAB_LEN + SGB_EXPTAB_LEN + SGB_LFTAB_LEN;
     d += (size_t)SGB_CN_TABLE * S * (lik_bb ? 5 : 2);
-    d += (size_t)SGB_DECODE_WARPS * decode_warp_doubles(SMAX, model, lik_bb);
-    return d * sizeof(double) + (size_t)SGB_CN_TABLE * S * sizeof(int);
+    d += (size_t)SGB_DECODE_WARPS * decode_warp_doubles(SMAX, model, lik_bb, stage);
+    return d * sizeof(double) + ((size_t)SGB_CN_TABLE * S + SGB_CN_TABLE) * sizeof(int);
 }
 
 // Fused emission + forward recursion + decode.  One lane per (cell, chromosome) sequence, 32 sequences
 // of similar length per warp, warps fetch groups from a global counter (longest first).
-// Per bin step a warp (1) unpacks its 32 records and looks the log-factorials up in shared memory,
-// (2) compacts the LIVE (lane, state) pairs of all 32 lanes into a queue (prefix sum of the live-state
-// counts), (3) evaluates them two per lane per round -- so lanes with copy number 2 do not idle while a
-// lane with copy number 9 works, and two independent FP64 chains are in flight per thread -- writing
-// E[state][lane], (4) runs the O(S) max-plus step of its own sequence from registers and stores the
-// decoded state of the previous bin.
-template <int SMAX, int MODEL, int LIKBB, int CHAINED>
+// Per bin step a warp
+//  (0) takes its 32 packed records from a shared-memory stage that 1-D TMA bulk copies filled one chunk
+//      (8 bins per sequence) ahead, completion tracked by an mbarrier per stage,
+//  (1) unpacks them and looks the log-factorials up in shared memory,
+//  (2) compacts the LIVE (lane, state) pairs of all 32 lanes into a queue (prefix sum of the live-state
+//      counts) -- lanes with copy number 2 do not idle while a lane with copy number 9 works,
+//  (3) evaluates the queue two entries per lane per round (two independent FP64 chains per thread),
+//      writing E[state][lane],
+//  (4) runs the O(S) max-plus step of its own sequence from registers and stores the decoded state of
+//      the previous bin.
+template <int SMAX, int MODEL, int LIKBB, int CHAINED, int STAGE>
 __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs A)
 {
     extern __shared__ __align__(16) double smem[];
     const int S = A.S;
     const int CTS = SGB_CN_TABLE * S;
-    constexpr int NF = 3 + (MODEL == SGB_MODEL_ASCN ? 1 : 0) + (LIKBB ? 1 : 0);
-    constexpr int WARP_DOUBLES = SMAX * 32 + NF * 32 + 16 + SMAX * 8;
+    constexpr int NL = (MODEL == SGB_MODEL_ASCN) ? 64 : 32;
+    constexpr int WARP_DOUBLES = SMAX * 32 + 64 + NL + (LIKBB ? 32 : 0) + 16 + SMAX * 8 +
+                                 (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_PITCH + 2 : 0);
     double* sLT = smem;
     double* sET = sLT + SGB_LOGTAB_LEN;
     double* sLF = sET + SGB_EXPTAB_LEN;
@@ -142,6 +176,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
     double* sL0 = sB + (LIKBB ? CTS : 0);
     double* sW = sL0 + (LIKBB ? CTS : 0);
     int* sKind = (int*)(sW + SGB_DECODE_WARPS * WARP_DOUBLES);
+    int* sKM = sKind + CTS;                 // per total-CN bit mask of the states on the lean path
 
     for (int i = threadIdx.x; i < SGB_LOGTAB_LEN; i += blockDim.x) sLT[i] = g_logtab[i];
     for (int i = threadIdx.x; i < SGB_EXPTAB_LEN; i += blockDim.x) sET[i] = g_exptab[i];
@@ -153,24 +188,37 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
         sKind[i] = A.tabs->kind[src];
         if (LIKBB) { sA[i] = A.tabs->a[src]; sB[i] = A.tabs->b[src]; sL0[i] = A.tabs->l0[src]; }
     }
+    if (threadIdx.x < SGB_CN_TABLE) {
+        int mask = 0;
+        for (int s = 0; s < S; s++)
+            if (A.tabs->kind[threadIdx.x * SGB_MAX_STATES + s] == SGB_KIND_NORMAL) mask |= 1 << s;
+        sKM[threadIdx.x] = mask;
+    }
     const SgbScalars sp = A.tabs->sp;
+
+    const int lane = threadIdx.x & 31;
+    const int wid = threadIdx.x >> 5;
+    double* myE = sW + wid * WARP_DOUBLES;
+    double2* bD = (double2*)(myE + SMAX * 32);                // {x, n-x}
+    double* bL = (double*)(bD + 32);                          // HSCN: lcx[32]; ASCN: {lcx, lcy}[32]
+    double* bG = bL + NL;                                     // beta-binomial: lgamma(s+n)[32]
+    int* bI = (int*)(bG + (LIKBB ? 32 : 0));                  // cprime | in_support << 16
+    unsigned short* q = (unsigned short*)(bI + 32);
+    unsigned long long* stg = (unsigned long long*)(q + SMAX * 32);     // [2][32][SGB_PITCH] records
+    unsigned long long* bar = stg + 2 * 32 * SGB_PITCH;                 // [2] mbarriers
+    if (STAGE == SGB_STAGE_TMA && lane == 0) {
+        sgb_mbar_init(&bar[0], 1);
+        sgb_mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async;" ::: "memory");
+    }
     __syncthreads();
 
     SgbTables TB;
     TB.LT = sLT; TB.ET = sET; TB.LP = sLP; TB.LQ = sLQ; TB.A = sA; TB.B = sB; TB.L0 = sL0; TB.KIND = sKind;
     TB.S = S; TB.lik = A.lik; TB.loherror = A.loherror; TB.rho = A.rho;
-
-    const int lane = threadIdx.x & 31;
-    const int wid = threadIdx.x >> 5;
-    double* myE = sW + wid * WARP_DOUBLES;
-    double* bKD = myE + SMAX * 32;
-    double* bNKD = bKD + 32;
-    double* bLCX = bNKD + 32;
-    double* bLCY = bLCX + 32;                                   // ASCN only
-    double* bLGS = bLCX + (MODEL == SGB_MODEL_ASCN ? 64 : 32);  // beta-binomial only
-    int* bI = (int*)(bKD + NF * 32);
-    unsigned short* q = (unsigned short*)(bI + 32);
     const double NEG_INF = -sgb_inf();
+    unsigned use0 = 0, use1 = 0;            // completed phases of the two stage barriers
 
     for (;;) {
         int g = 0;
@@ -187,19 +235,47 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
             prow = A.packed + A.plan.pstart[r];
         }
         const int Tmax = __reduce_max_sync(SGB_FULL, len);
+        const int plen = (len + 1) & ~1;    // rows are padded to an even record count (16-byte multiples)
         SgbSeqState<SMAX> st;
 #pragma unroll
         for (int i = 0; i < SMAX; i++) st.T1[i] = NEG_INF;
         st.m1 = NEG_INF; st.m2 = NEG_INF; st.i1 = 0;
-        unsigned long long rec_next = (len > 0) ? __ldg(prow) : 0ull;
+        unsigned long long rec_next = 0ull;
+        // issue the bulk copies of chunk c (bins c*CH .. c*CH+CH-1 of every lane's row) into stage c&1
+        auto issue_chunk = [&](int c) {
+            int rem = plen - c * SGB_CH;
+            rem = rem < 0 ? 0 : (rem > SGB_CH ? SGB_CH : rem);
+            const unsigned bytes = (unsigned)rem * 8u;
+            const unsigned total = __reduce_add_sync(SGB_FULL, bytes);
+            unsigned long long* b = &bar[c & 1];
+            if (lane == 0) sgb_mbar_expect_tx(b, total);
+            __syncwarp();
+            if (bytes) sgb_tma_load_1d(stg + ((c & 1) * 32 + lane) * SGB_PITCH, prow + (long long)c * SGB_CH, bytes, b);
+        };
+        if (STAGE == SGB_STAGE_TMA) {
+            if (Tmax > 0) issue_chunk(0);
+        } else {
+            rec_next = (len > 0) ? __ldg(prow) : 0ull;
+        }
         int back = 0;
         int Lprev = SMAX;          // states >= L hold -Inf in this lane's E column; refreshed when L shrinks
         for (int t = 0; t < Tmax; t++) {
             const bool act = t < len;
-            const unsigned long long rec = rec_next;
-            if (t + 1 < len) rec_next = __ldg(prow + t + 1);
+            unsigned long long rec;
+            if (STAGE == SGB_STAGE_TMA) {
+                const int ci = t / SGB_CH, w = t % SGB_CH;
+                if (w == 0) {
+                    if (ci & 1) { sgb_mbar_wait(&bar[1], use1 & 1); use1++; }
+                    else { sgb_mbar_wait(&bar[0], use0 & 1); use0++; }
+                    if ((ci + 1) * SGB_CH < Tmax) issue_chunk(ci + 1);
+                }
+                rec = act ? stg[((ci & 1) * 32 + lane) * SGB_PITCH + w] : 0ull;
+            } else {
+                rec = rec_next;
+                if (t + 1 < len) rec_next = __ldg(prow + t + 1);
+            }
             // ---- (1) per-bin quantities of this lane's sequence
-            int L = 0;
+            int L = 0, ebase = 0, fastmask = 0;
             if (act) {
                 const int n = (int)(rec & SGB_COUNT_MASK), x = (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK);
                 const int cprime = sgb_cprime(MODEL, (int)(rec >> 56));
@@ -207,22 +283,25 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
                 L = sgb_live_states(MODEL, cprime, S);
                 double lcx = 0.0, lcy = 0.0, lgs = 0.0;
                 if (ins) {
-                    const double fn = sgb_logfact(n, sLF, sLT), fx = sgb_logfact(x, sLF, sLT),
-                                 fy = sgb_logfact(n - x, sLF, sLT);
+                    double fn, fx, fy;
+                    if (n < SGB_NLF) { fn = sLF[n]; fx = sLF[x]; fy = sLF[n - x]; }
+                    else { fn = sgb_logfact(n, sLF, sLT); fx = sgb_logfact(x, sLF, sLT); fy = sgb_logfact(n - x, sLF, sLT); }
                     lcx = sgb_sub(sgb_sub(fn, fx), fy);
                     if (MODEL == SGB_MODEL_ASCN) lcy = sgb_sub(sgb_sub(fn, fy), fx);
-                    if (LIKBB) lgs = sgb_lgamma(sgb_add(sp.bb_s, (double)n), sLT);
+                    if (LIKBB) lgs = sgb_lgamma_pos(sgb_add(sp.bb_s, (double)n), sLT);
                 }
-                bKD[lane] = (double)x;
-                bNKD[lane] = (double)(n - x);
-                bLCX[lane] = lcx;
-                if (MODEL == SGB_MODEL_ASCN) bLCY[lane] = lcy;
-                if (LIKBB) bLGS[lane] = lgs;
+                bD[lane] = make_double2((double)x, (double)(n - x));
+                if (MODEL == SGB_MODEL_ASCN) ((double2*)bL)[lane] = make_double2(lcx, lcy);
+                else bL[lane] = lcx;
+                if (LIKBB) bG[lane] = lgs;
                 bI[lane] = cprime | (ins << 16);
+                const bool tab = cprime < SGB_CN_TABLE;
+                fastmask = (tab && ins && sp.fast_ok) ? sKM[cprime] : 0;
+                ebase = lane | ((tab ? cprime : 0) << 11);
                 for (int i = L; i < Lprev; i++) myE[i * 32 + lane] = NEG_INF;      // rare: only when L shrinks
                 Lprev = L;
             }
-            // ---- (2) queue of live (lane, state) pairs
+            // ---- (2) queue of live (lane, state) pairs: lane | lean << 5 | state << 6 | cprime << 11
             int incl = L;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
@@ -231,33 +310,36 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
             }
             const int tot = __shfl_sync(SGB_FULL, incl, 31);
             const int qoff = incl - L;
-            for (int m = 0; m < L; m++) q[qoff + m] = (unsigned short)(lane | (m << 5));
+            for (int m = 0; m < L; m++)
+                q[qoff + m] = (unsigned short)(ebase | (m << 6) | (((fastmask >> m) & 1) << 5));
             __syncwarp();
             // ---- (3) emissions, two queue entries per lane per round
             for (int base = 0; base < tot; base += 64) {
                 const int j0 = base + lane, j1 = j0 + 32;
                 const bool v0 = j0 < tot, v1 = j1 < tot;
-                const int en0 = v0 ? q[j0] : 0, en1 = v1 ? q[j1] : 0;
-                const int ol0 = en0 & 31, m0 = en0 >> 5, ol1 = en1 & 31, m1 = en1 >> 5;
-                const int bi0 = bI[ol0], bi1 = bI[ol1];
-                const int c0 = bi0 & 0xffff, c1 = bi1 & 0xffff, in0 = bi0 >> 16, in1 = bi1 >> 16;
-                const double kd0 = bKD[ol0], nk0 = bNKD[ol0], lx0 = bLCX[ol0];
-                const double kd1 = bKD[ol1], nk1 = bNKD[ol1], lx1 = bLCX[ol1];
-                const double ly0 = (MODEL == SGB_MODEL_ASCN) ? bLCY[ol0] : 0.0, ly1 = (MODEL == SGB_MODEL_ASCN) ? bLCY[ol1] : 0.0;
-                const double gs0 = LIKBB ? bLGS[ol0] : 0.0, gs1 = LIKBB ? bLGS[ol1] : 0.0;
-                const int t0 = (c0 < SGB_CN_TABLE) ? c0 * S + m0 : 0, t1 = (c1 < SGB_CN_TABLE) ? c1 * S + m1 : 0;
-                const bool f0 = (c0 < SGB_CN_TABLE) && in0 && (sKind[t0] == SGB_KIND_NORMAL);
-                const bool f1 = (c1 < SGB_CN_TABLE) && in1 && (sKind[t1] == SGB_KIND_NORMAL);
+                const int en0 = q[v0 ? j0 : 0], en1 = q[v1 ? j1 : (v0 ? j0 : 0)];
+                const int ol0 = en0 & 31, m0 = (en0 >> 6) & 31, ol1 = en1 & 31, m1 = (en1 >> 6) & 31;
+                const int t0 = (en0 >> 11) * S + m0, t1 = (en1 >> 11) * S + m1;
+                const double2 d0 = bD[ol0], d1 = bD[ol1];
+                double lx0, ly0 = 0.0, lx1, ly1 = 0.0;
+                if (MODEL == SGB_MODEL_ASCN) {
+                    const double2 a0 = ((const double2*)bL)[ol0], a1 = ((const double2*)bL)[ol1];
+                    lx0 = a0.x; ly0 = a0.y; lx1 = a1.x; ly1 = a1.y;
+                } else {
+                    lx0 = bL[ol0]; lx1 = bL[ol1];
+                }
+                const double gs0 = LIKBB ? bG[ol0] : 0.0, gs1 = LIKBB ? bG[ol1] : 0.0;
                 double r0, r1;
-                if (f0 && f1 && sp.fast_ok) {
-                    // both lean: one basic block, two independent dependency chains
-                    r0 = sgb_emission_fast<MODEL, LIKBB>(kd0, nk0, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
+                if (en0 & en1 & 32) {
+                    // both on the lean path: one basic block, two independent dependency chains
+                    r0 = sgb_emission_fast<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
                                                          LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, sp, sLT, sET);
-                    r1 = sgb_emission_fast<MODEL, LIKBB>(kd1, nk1, lx1, ly1, gs1, sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0,
+                    r1 = sgb_emission_fast<MODEL, LIKBB>(d1.x, d1.y, lx1, ly1, gs1, sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0,
                                                          LIKBB ? sB[t1] : 0.0, LIKBB ? sL0[t1] : 0.0, sp, sLT, sET);
                 } else {
-                    r0 = sgb_emit_item<MODEL, LIKBB>(c0, in0, kd0, nk0, lx0, ly0, gs0, m0, TB, sp);
-                    r1 = v1 ? sgb_emit_item<MODEL, LIKBB>(c1, in1, kd1, nk1, lx1, ly1, gs1, m1, TB, sp) : 0.0;
+                    const int bi0 = bI[ol0], bi1 = bI[ol1];
+                    r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
+                    r1 = v1 ? sgb_emit_item<MODEL, LIKBB>(bi1 & 0xffff, bi1 >> 16, d1.x, d1.y, lx1, ly1, gs1, m1, TB, sp) : 0.0;
                 }
                 if (v0) myE[m0 * 32 + ol0] = r0;
                 if (v1) myE[m1 * 32 + ol1] = r1;
@@ -289,11 +371,11 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
     }
 }
 
-template <int SMAX, int MODEL, int LIKBB, int CHAINED>
+template <int SMAX, int MODEL, int LIKBB, int CHAINED, int STAGE>
 static cudaError_t launch_decode(const SgbDecodeArgs& A, int sm_count, cudaStream_t st)
 {
-    size_t smem = decode_smem_bytes(SMAX, A.S, MODEL, LIKBB);
-    auto kern = k_decode<SMAX, MODEL, LIKBB, CHAINED>;
+    size_t smem = decode_smem_bytes(SMAX, A.S, MODEL, LIKBB, STAGE);
+    auto kern = k_decode<SMAX, MODEL, LIKBB, CHAINED, STAGE>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int blocks = (A.plan.ngroups + SGB_DECODE_WARPS - 1) / SGB_DECODE_WARPS;
@@ -305,20 +387,22 @@ static cudaError_t launch_decode(const SgbDecodeArgs& A, int sm_count, cudaStrea
 }
 
 template <int SMAX>
-static cudaError_t dispatch_decode(const SgbDecodeArgs& A, const SgbModelArgs& m, int sm_count, cudaStream_t st)
+static cudaError_t dispatch_decode(const SgbDecodeArgs& A, const SgbModelArgs& m, int stage, int sm_count, cudaStream_t st)
 {
     const int ch = m.decode == SGB_DECODE_CHAINED;
-#define SGB_CASE(MD, LK, CH) \
-    if (m.model == MD && m.lik_bb == LK && ch == CH) return launch_decode<SMAX, MD, LK, CH>(A, sm_count, st);
-    SGB_CASE(0, 0, 0) SGB_CASE(0, 1, 0) SGB_CASE(1, 0, 0) SGB_CASE(1, 1, 0)
-    SGB_CASE(0, 0, 1) SGB_CASE(0, 1, 1) SGB_CASE(1, 0, 1) SGB_CASE(1, 1, 1)
+    if (ch) stage = SGB_STAGE_LDG;      // the opt-in chained mode keeps the plain global-load path
+#define SGB_CASE(MD, LK, CH, SG) \
+    if (m.model == MD && m.lik_bb == LK && ch == CH && stage == SG) return launch_decode<SMAX, MD, LK, CH, SG>(A, sm_count, st);
+    SGB_CASE(0, 0, 0, 1) SGB_CASE(0, 1, 0, 1) SGB_CASE(1, 0, 0, 1) SGB_CASE(1, 1, 0, 1)
+    SGB_CASE(0, 0, 0, 0) SGB_CASE(0, 1, 0, 0) SGB_CASE(1, 0, 0, 0) SGB_CASE(1, 1, 0, 0)
+    SGB_CASE(0, 0, 1, 0) SGB_CASE(0, 1, 1, 0) SGB_CASE(1, 0, 1, 0) SGB_CASE(1, 1, 1, 0)
 #undef SGB_CASE
     return cudaErrorInvalidValue;
 }
 
 cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_packed, const SgbDevTables* d_tabs,
                         const SgbModelArgs& m, uint8_t* d_state_out, uint8_t* d_bp, int* d_last_state,
-                        unsigned int* d_counter, int sm_count, cudaStream_t st)
+                        unsigned int* d_counter, int sm_count, int stage, cudaStream_t st)
 {
     if (plan.nseq == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(d_counter, 0, sizeof(unsigned int), st);
@@ -328,8 +412,8 @@ cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_pack
     A.last_state = d_last_state; A.counter = d_counter; A.S = m.S;
     A.lik = m.lik_bb ? SGB_LIK_BETABINOMIAL : SGB_LIK_BINOMIAL;
     A.loherror = m.loherror; A.rho = m.rho;
-    if (m.S <= 12) return dispatch_decode<12>(A, m, sm_count, st);
-    if (m.S <= SGB_MAX_STATES) return dispatch_decode<SGB_MAX_STATES>(A, m, sm_count, st);
+    if (m.S <= 12) return dispatch_decode<12>(A, m, stage, sm_count, st);
+    if (m.S <= SGB_MAX_STATES) return dispatch_decode<SGB_MAX_STATES>(A, m, stage, sm_count, st);
     return cudaErrorInvalidValue;
 }
 

@@ -43,7 +43,7 @@ cudaError_t sgbk_pack(const int32_t* d_n, const int32_t* d_x, const void* d_cn, 
                       const SgbPlanDev& plan, unsigned long long* d_packed, int* d_err, cudaStream_t st);
 cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_packed, const SgbDevTables* d_tabs,
                         const SgbModelArgs& m, uint8_t* d_state_out, uint8_t* d_bp, int* d_last_state,
-                        unsigned int* d_counter, int sm_count, cudaStream_t st);
+                        unsigned int* d_counter, int sm_count, int stage, cudaStream_t st);
 cudaError_t sgbk_backtrace(const SgbPlanDev& plan, const uint8_t* d_bp, const int* d_last_state, int S,
                            uint8_t* d_state_out, cudaStream_t st);
 cudaError_t sgbk_loglik(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,

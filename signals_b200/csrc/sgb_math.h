@@ -216,12 +216,12 @@ SGB_HD double sgb_log(double x, const double* __restrict__ LT)
     return sgb_log_tab(x, LT);
 }
 
-// core of log1p(u) for u in [0,1) given w = fl(1+u) < 2 (no checks)
+// core of log1p(u) for u in [0,1] given w = fl(1+u) in [1,2] (no checks).  w == 2.0 lands on table
+// entry 128 (invc = 1/2, logc = ln 2), so the result there is exactly SGB_LN2.
 SGB_HD double sgb_log1p01_core(double u, double w, const double* __restrict__ LT)
 {
     double c = sgb_sub(u, sgb_sub(w, 1.0));          // exact rounding residual of 1+u
-    uint64_t m = sgb_d2u(w) & 0x000fffffffffffffULL;
-    int32_t i = (int32_t)(m >> 45);
+    int32_t i = (int32_t)((sgb_d2u(w) - 0x3ff0000000000000ULL) >> 45);
     double invc = LT[2 * i], logc = LT[2 * i + 1];
     double r = sgb_fma(w, invc, -1.0);
     double p = sgb_fma(r, SGB_C(LOGC9), SGB_C(LOGC8));
@@ -239,10 +239,8 @@ SGB_HD double sgb_log1p01_core(double u, double w, const double* __restrict__ LT
 // log1p(u) for u in [0,1] (hot path: u = exp(-|a-b|) inside logspace_add).
 SGB_HD double sgb_log1p_01(double u, const double* __restrict__ LT)
 {
-    if (!(u < 1.0)) return (u == 1.0) ? SGB_C(LN2) : ((u != u) ? u : sgb_nan());
-    double w = sgb_add(1.0, u);
-    if (w >= 2.0) return SGB_C(LN2);
-    return sgb_log1p01_core(u, w, LT);
+    if (!(u <= 1.0)) return (u != u) ? u : sgb_nan();
+    return sgb_log1p01_core(u, sgb_add(1.0, u), LT);
 }
 
 // General log1p for x > -1 (cold path: log1p(-p) for the per-(CN,state) tables).
@@ -266,17 +264,14 @@ SGB_HD double sgb_max(double a, double b)            // operands are never NaN h
 }
 
 // Branch-free body, valid when neither operand is NaN and they are not the same infinity.
-// exp(d) is +0 for d <= -708 and log1p(1) is ln 2, as in sgb_exp / sgb_log1p_01.
+// The exponent is clamped at -708 (exp(-708) ~ 3e-308 instead of an underflowing value: it vanishes
+// against any max(a,b) that is not itself below 1e-290 in magnitude).
 SGB_HD double sgb_logspace_add_lean(double a, double b, const double* __restrict__ LT, const double* __restrict__ ET)
 {
     double mx = sgb_max(a, b);
     double d = sgb_u2d(sgb_d2u(sgb_sub(a, b)) | 0x8000000000000000ULL);      // -fabs(a-b)
     double u = sgb_exp_core(sgb_max(d, -708.0), ET);
-    u = (d > -708.0) ? u : 0.0;
-    double w = sgb_add(1.0, u);
-    double lp = sgb_log1p01_core(u, w, LT);
-    lp = (w >= 2.0) ? SGB_C(LN2) : lp;
-    return sgb_add(mx, lp);
+    return sgb_add(mx, sgb_log1p01_core(u, sgb_add(1.0, u), LT));
 }
 
 SGB_HD double sgb_logspace_add(double a, double b, const double* __restrict__ LT, const double* __restrict__ ET)
