@@ -59,11 +59,12 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(SO_PATH):
+    path = os.environ.get("SGB_LIB", SO_PATH)       # SGB_LIB: an experimental build made by signals_b200.build --variant
+    if not os.path.exists(path):
         raise SignalsB200Error(
             "libsignals_b200.so is not built (%s). Run `python -m signals_b200.build`; "
-            "there is no CPU fallback." % SO_PATH)
-    lib = ctypes.CDLL(SO_PATH)
+            "there is no CPU fallback." % path)
+    lib = ctypes.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)       # AttributeError if a declared symbol is missing
         fn.restype = res

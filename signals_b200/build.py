@@ -31,18 +31,26 @@ def needs_build():
     return any(os.path.exists(f) and os.path.getmtime(f) > t for f in files)
 
 
-def build(force=False, verbose=False):
-    if not force and not needs_build():
+def build(force=False, verbose=False, variant=None, defines=()):
+    """variant/defines: experimental builds (libsignals_b200_<variant>.so, selected with SGB_LIB=<path>)"""
+    so = SO if not variant else os.path.join(HERE, "libsignals_b200_%s.so" % variant)
+    if not variant and not force and not needs_build():
         return SO
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-          [os.path.join(CSRC, s) for s in SOURCES] + ["-o", SO]
+    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + \
+          [os.path.join(CSRC, s) for s in SOURCES] + ["-o", so]
     if verbose:
         print(" ".join(cmd))
     subprocess.check_call(cmd)
-    return SO
+    return so
 
 
 if __name__ == "__main__":
-    build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
-    print(SO)
+    variant = None
+    defines = []
+    for i, a in enumerate(sys.argv):
+        if a == "--variant":
+            variant = sys.argv[i + 1]
+        if a == "--define":
+            defines.append(sys.argv[i + 1])
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, variant=variant, defines=defines))

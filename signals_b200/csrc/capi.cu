@@ -61,7 +61,7 @@ struct DevBuf {
 
 // host-side description of a batch of sequences, sorted by length (longest first)
 struct HostPlan {
-    std::vector<long long> pstart, ostart;
+    std::vector<long long> goff, ostart;       // goff: per group of 32 sequences, ostart: per sequence
     std::vector<int> len;
     long long packed_len = 0;   // records
     long long nseq = 0;
@@ -72,7 +72,7 @@ struct HostPlan {
 int build_host_plan(const int64_t* seg_off, int64_t s0, int64_t s1, int64_t row_base, HostPlan& hp)
 {
     const int64_t nseg = s1 - s0;
-    hp.pstart.clear(); hp.ostart.clear(); hp.len.clear();
+    hp.goff.clear(); hp.ostart.clear(); hp.len.clear();
     hp.packed_len = 0; hp.nseq = 0; hp.rows = 0;
     int64_t maxlen = 0;
     for (int64_t s = s0; s < s1; s++) {
@@ -103,16 +103,20 @@ int build_host_plan(const int64_t* seg_off, int64_t s0, int64_t s1, int64_t row_
         });
     }
     hp.nseq = (long long)order.size();
-    hp.pstart.resize(order.size()); hp.ostart.resize(order.size()); hp.len.resize(order.size());
+    hp.ostart.resize(order.size()); hp.len.resize(order.size());
+    hp.goff.resize((order.size() + 31) / 32);
     long long p = 0;
     for (size_t r = 0; r < order.size(); r++) {
         int64_t s = order[r];
         int L = (int)(seg_off[s + 1] - seg_off[s]);
-        hp.pstart[r] = p;
         hp.ostart[r] = (long long)(seg_off[s] - row_base);
         hp.len[r] = L;
-        p += ((long long)L + 1) & ~1ll;       // keep every sequence 16-byte aligned in the packed buffer
         hp.rows += L;
+        if ((r & 31) == 0) {
+            // the first sequence of a group is its longest; tile = roundup(T, SGB_CH) bins x 32 lanes
+            hp.goff[r >> 5] = p;
+            p += (((long long)L + SGB_CH - 1) / SGB_CH) * SGB_CH * 32;
+        }
     }
     hp.packed_len = p;
     return 0;
@@ -120,7 +124,7 @@ int build_host_plan(const int64_t* seg_off, int64_t s0, int64_t s1, int64_t row_
 
 struct Slot {
     cudaStream_t st = nullptr;
-    DevBuf n, x, cn, out, packed, bp, last_state, pstart, ostart, len, loglik;
+    DevBuf n, x, cn, out, packed, bp, last_state, goff, ostart, len, loglik;
     unsigned int* counter = nullptr;
     HostPlan hp;
     // pending device->host copy bookkeeping is implicit: copies are enqueued on st
@@ -209,15 +213,16 @@ int upload_plan(Slot& S, cudaStream_t st, SgbPlanDev& pd)
 {
     const HostPlan& hp = S.hp;
     size_t ns = (size_t)hp.nseq;
-    if (S.pstart.reserve(ns * sizeof(long long) + 16)) return 1;
+    size_t ng = hp.goff.size();
+    if (S.goff.reserve(ng * sizeof(long long) + 16)) return 1;
     if (S.ostart.reserve(ns * sizeof(long long) + 16)) return 1;
     if (S.len.reserve(ns * sizeof(int) + 16)) return 1;
     if (ns) {
-        SGB_CUDA(cudaMemcpyAsync(S.pstart.p, hp.pstart.data(), ns * sizeof(long long), cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(S.goff.p, hp.goff.data(), ng * sizeof(long long), cudaMemcpyHostToDevice, st));
         SGB_CUDA(cudaMemcpyAsync(S.ostart.p, hp.ostart.data(), ns * sizeof(long long), cudaMemcpyHostToDevice, st));
         SGB_CUDA(cudaMemcpyAsync(S.len.p, hp.len.data(), ns * sizeof(int), cudaMemcpyHostToDevice, st));
     }
-    pd.pstart = (const long long*)S.pstart.p;
+    pd.goff = (const long long*)S.goff.p;
     pd.ostart = (const long long*)S.ostart.p;
     pd.len = (const int*)S.len.p;
     pd.nseq = hp.nseq;
@@ -355,7 +360,7 @@ int sgb_shutdown(void)
             Slot& s = c->slot[i];
             if (s.st) { cudaStreamSynchronize(s.st); cudaStreamDestroy(s.st); }
             s.n.release(); s.x.release(); s.cn.release(); s.out.release(); s.packed.release(); s.bp.release();
-            s.last_state.release(); s.pstart.release(); s.ostart.release(); s.len.release(); s.loglik.release();
+            s.last_state.release(); s.goff.release(); s.ostart.release(); s.len.release(); s.loglik.release();
             if (s.counter) cudaFree(s.counter);
         }
         c->scratch_a.release(); c->scratch_b.release(); c->scratch_c.release(); c->scratch_d.release();
@@ -430,7 +435,7 @@ struct sgb_plan {
     int64_t N = 0;
     int n_states = 0, decode = 0;
     HostPlan hp;
-    DevBuf pstart, ostart, len, packed, bp, last_state;
+    DevBuf goff, ostart, len, packed, bp, last_state;
     unsigned int* counter = nullptr;
     int* d_err = nullptr;
     SgbDevTables* d_tabs = nullptr;
@@ -457,14 +462,15 @@ int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_s
     pl->device = C->device; pl->N = N; pl->n_states = n_states; pl->decode = decode;
     if (build_host_plan(seg_off, 0, nseg, 0, pl->hp)) { delete pl; return 1; }
     size_t ns = (size_t)pl->hp.nseq;
-    int bad = pl->pstart.reserve(ns * 8 + 16) || pl->ostart.reserve(ns * 8 + 16) || pl->len.reserve(ns * 4 + 16) ||
+    size_t ng = pl->hp.goff.size();
+    int bad = pl->goff.reserve(ng * 8 + 16) || pl->ostart.reserve(ns * 8 + 16) || pl->len.reserve(ns * 4 + 16) ||
               pl->packed.reserve((size_t)pl->hp.packed_len * 8 + 16);
     if (!bad && decode == SGB_DECODE_CHAINED)
         bad = pl->bp.reserve((size_t)N * n_states + 16) || pl->last_state.reserve(ns * 4 + 16);
     if (bad) { sgb_plan_destroy(pl); return 1; }
     cudaError_t e = cudaSuccess;
     if (ns) {
-        e = cudaMemcpy(pl->pstart.p, pl->hp.pstart.data(), ns * 8, cudaMemcpyHostToDevice);
+        e = cudaMemcpy(pl->goff.p, pl->hp.goff.data(), ng * 8, cudaMemcpyHostToDevice);
         if (e == cudaSuccess) e = cudaMemcpy(pl->ostart.p, pl->hp.ostart.data(), ns * 8, cudaMemcpyHostToDevice);
         if (e == cudaSuccess) e = cudaMemcpy(pl->len.p, pl->hp.len.data(), ns * 4, cudaMemcpyHostToDevice);
     }
@@ -476,7 +482,7 @@ int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_s
         sgb_plan_destroy(pl);
         return fail(std::string("plan allocation failed: ") + cudaGetErrorString(e));
     }
-    pl->pd.pstart = (const long long*)pl->pstart.p;
+    pl->pd.goff = (const long long*)pl->goff.p;
     pl->pd.ostart = (const long long*)pl->ostart.p;
     pl->pd.len = (const int*)pl->len.p;
     pl->pd.nseq = pl->hp.nseq;
@@ -491,7 +497,7 @@ int sgb_plan_destroy(sgb_plan* pl)
     if (pl->ev_ready)
         for (int i = 0; i < sgb_plan::kRing; i++)
             for (int j = 0; j < 3; j++) cudaEventDestroy(pl->ev[i][j]);
-    pl->pstart.release(); pl->ostart.release(); pl->len.release(); pl->packed.release(); pl->bp.release();
+    pl->goff.release(); pl->ostart.release(); pl->len.release(); pl->packed.release(); pl->bp.release();
     pl->last_state.release();
     if (pl->counter) cudaFree(pl->counter);
     if (pl->d_err) cudaFree(pl->d_err);
@@ -503,7 +509,7 @@ int sgb_plan_destroy(sgb_plan* pl)
 int64_t sgb_plan_scratch_bytes(const sgb_plan* pl)
 {
     if (!pl) return 0;
-    return (int64_t)(pl->packed.cap + pl->bp.cap + pl->last_state.cap + pl->pstart.cap + pl->ostart.cap + pl->len.cap);
+    return (int64_t)(pl->packed.cap + pl->bp.cap + pl->last_state.cap + pl->goff.cap + pl->ostart.cap + pl->len.cap);
 }
 
 int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t* d_n, const int32_t* d_x,

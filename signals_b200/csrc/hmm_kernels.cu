@@ -47,28 +47,50 @@ cudaError_t sgbk_setup(SgbDevTables* d_tabs, const SgbModelArgs& m, double eps, 
 }
 
 // ------------------------------------------------------------------ k_pack
-// One warp per sequence, lanes over consecutive bins: coalesced 128 B reads of n / x, 32 B of cn,
-// coalesced 256 B record writes.  Counts are validated here (device side).
-__global__ void __launch_bounds__(256) k_pack(const int32_t* __restrict__ n, const int32_t* __restrict__ x,
+// Caller's flat columns -> 8-byte records (n:28 | x:28 | cn:8) in the group-tiled, lane-interleaved
+// layout k_decode streams (see SgbPlanDev).  One warp per group of 32 sequences; per block of 32 bins it
+// reads each sequence's n / x / cn with lanes over consecutive bins (coalesced 128 B / 32 B segments),
+// transposes through a padded shared-memory tile and writes 256 B per bin, lanes over sequences.
+// Counts are validated here, on the device, so the host never touches the per-bin data.
+__global__ void __launch_bounds__(128) k_pack(const int32_t* __restrict__ n, const int32_t* __restrict__ x,
                                               const void* __restrict__ cn, int cn_itemsize, SgbPlanDev plan,
                                               unsigned long long* __restrict__ packed, int* err)
 {
-    const int lane = threadIdx.x & 31;
+    __shared__ unsigned long long tile[4][32][33];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     int bad = 0;
-    for (long long r = warp; r < plan.nseq; r += nwarps) {
-        const long long o = plan.ostart[r], p = plan.pstart[r];
-        const int len = plan.len[r];
-        for (int t = lane; t < len; t += 32) {
-            int nv = n[o + t], xv = x[o + t];
-            int cv = (cn_itemsize == 1) ? (int)((const uint8_t*)cn)[o + t] : ((const int32_t*)cn)[o + t];
-            if (nv < 0 || xv < 0) bad |= SGB_ERR_NEGATIVE_COUNT;
-            if (nv >= (1 << SGB_COUNT_BITS) || xv >= (1 << SGB_COUNT_BITS)) bad |= SGB_ERR_COUNT_TOO_LARGE;
-            if (cv < 0 || cv > 255) bad |= SGB_ERR_BAD_CN;
-            packed[p + t] = ((unsigned long long)(unsigned)nv & SGB_COUNT_MASK) |
-                            (((unsigned long long)(unsigned)xv & SGB_COUNT_MASK) << SGB_COUNT_BITS) |
-                            ((unsigned long long)(cv & 255) << 56);
+    for (long long g = warp; g < plan.ngroups; g += nwarps) {
+        const long long r0 = g * 32;
+        const int nrow = (int)((plan.nseq - r0) < 32 ? (plan.nseq - r0) : 32);
+        const int Tg = plan.len[r0];
+        const int Tpad = ((Tg + SGB_CH - 1) / SGB_CH) * SGB_CH;
+        const long long base = plan.goff[g];
+        for (int t0 = 0; t0 < Tpad; t0 += 32) {
+            for (int j = 0; j < 32; j++) {
+                unsigned long long rec = 0ull;
+                if (j < nrow) {
+                    const int lenj = plan.len[r0 + j];
+                    const int t = t0 + lane;
+                    if (t < lenj) {
+                        const long long o = plan.ostart[r0 + j] + t;
+                        const int nv = n[o], xv = x[o];
+                        const int cv = (cn_itemsize == 1) ? (int)((const uint8_t*)cn)[o] : ((const int32_t*)cn)[o];
+                        if (nv < 0 || xv < 0) bad |= SGB_ERR_NEGATIVE_COUNT;
+                        if (nv >= (1 << SGB_COUNT_BITS) || xv >= (1 << SGB_COUNT_BITS)) bad |= SGB_ERR_COUNT_TOO_LARGE;
+                        if (cv < 0 || cv > 255) bad |= SGB_ERR_BAD_CN;
+                        rec = ((unsigned long long)(unsigned)nv & SGB_COUNT_MASK) |
+                              (((unsigned long long)(unsigned)xv & SGB_COUNT_MASK) << SGB_COUNT_BITS) |
+                              ((unsigned long long)(cv & 255) << 56);
+                    }
+                }
+                tile[wid][j][lane] = rec;
+            }
+            __syncwarp();
+            const int nb = (Tpad - t0) < 32 ? (Tpad - t0) : 32;
+            for (int jb = 0; jb < nb; jb++) packed[base + (long long)(t0 + jb) * 32 + lane] = tile[wid][lane][jb];
+            __syncwarp();
         }
     }
     if (bad) atomicOr(err, bad);
@@ -78,9 +100,9 @@ cudaError_t sgbk_pack(const int32_t* d_n, const int32_t* d_x, const void* d_cn, 
                       const SgbPlanDev& plan, unsigned long long* d_packed, int* d_err, cudaStream_t st)
 {
     if (plan.nseq == 0) return cudaSuccess;
-    long long blocks = (plan.nseq + 7) / 8;
-    if (blocks > 148 * 16) blocks = 148 * 16;
-    k_pack<<<(unsigned)blocks, 256, 0, st>>>(d_n, d_x, d_cn, cn_itemsize, plan, d_packed, d_err);
+    long long blocks = ((long long)plan.ngroups + 3) / 4;
+    if (blocks > 148 * 6) blocks = 148 * 6;
+    k_pack<<<(unsigned)blocks, 128, 0, st>>>(d_n, d_x, d_cn, cn_itemsize, plan, d_packed, d_err);
     return cudaGetLastError();
 }
 
@@ -99,10 +121,11 @@ struct SgbDecodeArgs {
 
 #define SGB_DECODE_THREADS 256
 #define SGB_DECODE_WARPS (SGB_DECODE_THREADS / 32)
+#ifndef SGB_DECODE_MINBLOCKS
+#define SGB_DECODE_MINBLOCKS 2   // resident CTAs per SM the register allocation is bounded for
+#endif
 #define SGB_STAGE_LDG 0        // records read straight from global memory (one LDG.64 per lane per bin)
 #define SGB_STAGE_TMA 1        // records staged through shared memory by 1-D bulk copies (cp.async.bulk + mbarrier)
-#define SGB_CH 8               // records per lane per staged chunk
-#define SGB_PITCH 10           // row pitch of a staged chunk in records (80 B: 16-byte aligned rows)
 
 // ---- TMA (bulk asynchronous copy) / mbarrier wrappers --------------------------------------
 __device__ __forceinline__ unsigned sgb_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -134,7 +157,7 @@ __device__ __forceinline__ void sgb_mbar_wait(unsigned long long* bar, unsigned 
 static inline size_t decode_warp_doubles(int SMAX, int model, int lik_bb, int stage)
 {
     size_t d = (size_t)SMAX * 32 + 64 + (model == SGB_MODEL_ASCN ? 64 : 32) + (lik_bb ? 32 : 0) + 16 + (size_t)SMAX * 8;
-    if (stage == SGB_STAGE_TMA) d += 2 * 32 * SGB_PITCH + 2;
+    if (stage == SGB_STAGE_TMA) d += 2 * 32 * SGB_CH + 2;
     return d;
 }
 static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb, int stage)
@@ -158,14 +181,14 @@ static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb, i
 //  (4) runs the O(S) max-plus step of its own sequence from registers and stores the decoded state of
 //      the previous bin.
 template <int SMAX, int MODEL, int LIKBB, int CHAINED, int STAGE>
-__global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs A)
+__global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_decode(SgbDecodeArgs A)
 {
     extern __shared__ __align__(16) double smem[];
     const int S = A.S;
     const int CTS = SGB_CN_TABLE * S;
     constexpr int NL = (MODEL == SGB_MODEL_ASCN) ? 64 : 32;
     constexpr int WARP_DOUBLES = SMAX * 32 + 64 + NL + (LIKBB ? 32 : 0) + 16 + SMAX * 8 +
-                                 (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_PITCH + 2 : 0);
+                                 (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_CH + 2 : 0);
     double* sLT = smem;
     double* sET = sLT + SGB_LOGTAB_LEN;
     double* sLF = sET + SGB_EXPTAB_LEN;
@@ -204,8 +227,8 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
     double* bG = bL + NL;                                     // beta-binomial: lgamma(s+n)[32]
     int* bI = (int*)(bG + (LIKBB ? 32 : 0));                  // cprime | in_support << 16
     unsigned short* q = (unsigned short*)(bI + 32);
-    unsigned long long* stg = (unsigned long long*)(q + SMAX * 32);     // [2][32][SGB_PITCH] records
-    unsigned long long* bar = stg + 2 * 32 * SGB_PITCH;                 // [2] mbarriers
+    unsigned long long* stg = (unsigned long long*)(q + SMAX * 32);     // [2][SGB_CH][32] records
+    unsigned long long* bar = stg + 2 * 32 * SGB_CH;                    // [2] mbarriers
     if (STAGE == SGB_STAGE_TMA && lane == 0) {
         sgb_mbar_init(&bar[0], 1);
         sgb_mbar_init(&bar[1], 1);
@@ -228,34 +251,29 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
         const long long r = (long long)g * 32 + lane;
         int len = 0;
         long long ostart = 0;
-        const unsigned long long* prow = A.packed;
         if (r < A.plan.nseq) {
             len = A.plan.len[r];
             ostart = A.plan.ostart[r];
-            prow = A.packed + A.plan.pstart[r];
         }
-        const int Tmax = __reduce_max_sync(SGB_FULL, len);
-        const int plen = (len + 1) & ~1;    // rows are padded to an even record count (16-byte multiples)
+        const unsigned long long* gtile = A.packed + A.plan.goff[g];      // [bin][lane] records of this group
+        const int Tmax = __shfl_sync(SGB_FULL, len, 0);                   // lane 0 holds the group's longest sequence
         SgbSeqState<SMAX> st;
 #pragma unroll
         for (int i = 0; i < SMAX; i++) st.T1[i] = NEG_INF;
         st.m1 = NEG_INF; st.m2 = NEG_INF; st.i1 = 0;
         unsigned long long rec_next = 0ull;
-        // issue the bulk copies of chunk c (bins c*CH .. c*CH+CH-1 of every lane's row) into stage c&1
+        // one 1-D bulk copy moves chunk c (SGB_CH bins x 32 lanes = 2 KB, contiguous in the tile) into stage c&1
         auto issue_chunk = [&](int c) {
-            int rem = plen - c * SGB_CH;
-            rem = rem < 0 ? 0 : (rem > SGB_CH ? SGB_CH : rem);
-            const unsigned bytes = (unsigned)rem * 8u;
-            const unsigned total = __reduce_add_sync(SGB_FULL, bytes);
-            unsigned long long* b = &bar[c & 1];
-            if (lane == 0) sgb_mbar_expect_tx(b, total);
-            __syncwarp();
-            if (bytes) sgb_tma_load_1d(stg + ((c & 1) * 32 + lane) * SGB_PITCH, prow + (long long)c * SGB_CH, bytes, b);
+            if (lane == 0) {
+                unsigned long long* b = &bar[c & 1];
+                sgb_mbar_expect_tx(b, SGB_CH * 32 * 8);
+                sgb_tma_load_1d(stg + (c & 1) * 32 * SGB_CH, gtile + (long long)c * SGB_CH * 32, SGB_CH * 32 * 8, b);
+            }
         };
         if (STAGE == SGB_STAGE_TMA) {
             if (Tmax > 0) issue_chunk(0);
         } else {
-            rec_next = (len > 0) ? __ldg(prow) : 0ull;
+            rec_next = (Tmax > 0) ? __ldg(gtile + lane) : 0ull;
         }
         int back = 0;
         int Lprev = SMAX;          // states >= L hold -Inf in this lane's E column; refreshed when L shrinks
@@ -269,13 +287,13 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
                     else { sgb_mbar_wait(&bar[0], use0 & 1); use0++; }
                     if ((ci + 1) * SGB_CH < Tmax) issue_chunk(ci + 1);
                 }
-                rec = act ? stg[((ci & 1) * 32 + lane) * SGB_PITCH + w] : 0ull;
+                rec = stg[((ci & 1) * SGB_CH + w) * 32 + lane];
             } else {
                 rec = rec_next;
-                if (t + 1 < len) rec_next = __ldg(prow + t + 1);
+                if (t + 1 < Tmax) rec_next = __ldg(gtile + (long long)(t + 1) * 32 + lane);
             }
             // ---- (1) per-bin quantities of this lane's sequence
-            int L = 0, ebase = 0, fastmask = 0;
+            int L = 0, ebase = 0;
             if (act) {
                 const int n = (int)(rec & SGB_COUNT_MASK), x = (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK);
                 const int cprime = sgb_cprime(MODEL, (int)(rec >> 56));
@@ -296,8 +314,10 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
                 if (LIKBB) bG[lane] = lgs;
                 bI[lane] = cprime | (ins << 16);
                 const bool tab = cprime < SGB_CN_TABLE;
-                fastmask = (tab && ins && sp.fast_ok) ? sKM[cprime] : 0;
-                ebase = lane | ((tab ? cprime : 0) << 11);
+                const int fastmask = (tab && ins && sp.fast_ok) ? sKM[cprime] : 0;
+                const int lm = (1 << L) - 1;
+                // all live states of this bin on the lean path (the usual case) -> one flag for the lane's entries
+                ebase = lane | ((tab ? cprime : 0) << 11) | (((fastmask & lm) == lm) ? 32 : 0);
                 for (int i = L; i < Lprev; i++) myE[i * 32 + lane] = NEG_INF;      // rare: only when L shrinks
                 Lprev = L;
             }
@@ -310,8 +330,9 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, 2) k_decode(SgbDecodeArgs 
             }
             const int tot = __shfl_sync(SGB_FULL, incl, 31);
             const int qoff = incl - L;
-            for (int m = 0; m < L; m++)
-                q[qoff + m] = (unsigned short)(ebase | (m << 6) | (((fastmask >> m) & 1) << 5));
+#pragma unroll
+            for (int m = 0; m < SMAX; m++)
+                if (m < L) q[qoff + m] = (unsigned short)(ebase + (m << 6));
             __syncwarp();
             // ---- (3) emissions, two queue entries per lane per round
             for (int base = 0; base < tot; base += 64) {
@@ -379,7 +400,9 @@ static cudaError_t launch_decode(const SgbDecodeArgs& A, int sm_count, cudaStrea
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int blocks = (A.plan.ngroups + SGB_DECODE_WARPS - 1) / SGB_DECODE_WARPS;
-    int cap = sm_count * 2;
+    int occ = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, SGB_DECODE_THREADS, smem) != cudaSuccess || occ < 1) occ = 1;
+    int cap = sm_count * occ;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     kern<<<blocks, SGB_DECODE_THREADS, smem, st>>>(A);

@@ -19,8 +19,12 @@ struct SgbDevTables {
 
 // A "plan" describes the (cell, chromosome) sequences of one batch, sorted by length
 // (longest first) and grouped 32 to a warp; see DESIGN.md "HBM layout".
+// Packed buffer: group g owns a tile of roundup(T_g, SGB_CH) x 32 records starting at goff[g],
+// record (bin t, lane l) at goff[g] + t*32 + l  (bin-major, lanes interleaved: a warp reads 256
+// contiguous bytes per bin and one 1-D bulk copy moves SGB_CH bins of all 32 sequences).
+#define SGB_CH 8               // bins per staged chunk
 struct SgbPlanDev {
-    const long long* pstart;   // [nseq] first record of the sequence in the packed buffer (even => 16 B aligned)
+    const long long* goff;     // [ngroups] first record of the group's tile in the packed buffer
     const long long* ostart;   // [nseq] first row of the sequence in the caller's n/x/cn/state arrays
     const int* len;            // [nseq] number of bins
     long long nseq;
