@@ -201,6 +201,47 @@ SGB_HD double sgb_emission_fast(double kd, double nkd, double lc_x, double lc_y,
     return l;
 }
 
+// Two lean emissions at once: identical arithmetic per item (so identical bits), but written so that both
+// dependency chains sit in the same basic blocks and the scheduler can interleave them.
+template <int MODEL, int LIKBB>
+SGB_HD void sgb_emission_fast2(double kd0, double nk0, double lx0, double ly0, double gs0, double lp0, double lq0,
+                               double a0, double b0, double z0, double kd1, double nk1, double lx1, double ly1,
+                               double gs1, double lp1, double lq1, double a1, double b1, double z1,
+                               const SgbScalars& sp, const double* __restrict__ LT, const double* __restrict__ ET,
+                               double& r0, double& r1)
+{
+    double l0, l1;
+    if (!LIKBB) {
+        l0 = sgb_fma(nk0, lq0, sgb_fma(kd0, lp0, lx0));
+        l1 = sgb_fma(nk1, lq1, sgb_fma(kd1, lp1, lx1));
+    } else {
+        double t0 = sgb_add(sgb_lgamma_pos(sgb_add(a0, kd0), LT), sgb_lgamma_pos(sgb_add(b0, nk0), LT));
+        double t1 = sgb_add(sgb_lgamma_pos(sgb_add(a1, kd1), LT), sgb_lgamma_pos(sgb_add(b1, nk1), LT));
+        l0 = sgb_add(lx0, sgb_sub(sgb_sub(t0, gs0), z0));
+        l1 = sgb_add(lx1, sgb_sub(sgb_sub(t1, gs1), z1));
+    }
+    if (MODEL == SGB_MODEL_ASCN) {
+        double m0, m1;
+        if (!LIKBB) {
+            m0 = sgb_fma(kd0, lq0, sgb_fma(nk0, lp0, ly0));
+            m1 = sgb_fma(kd1, lq1, sgb_fma(nk1, lp1, ly1));
+        } else {
+            double t0 = sgb_add(sgb_lgamma_pos(sgb_add(a0, nk0), LT), sgb_lgamma_pos(sgb_add(b0, kd0), LT));
+            double t1 = sgb_add(sgb_lgamma_pos(sgb_add(a1, nk1), LT), sgb_lgamma_pos(sgb_add(b1, kd1), LT));
+            m0 = sgb_add(ly0, sgb_sub(sgb_sub(t0, gs0), z0));
+            m1 = sgb_add(ly1, sgb_sub(sgb_sub(t1, gs1), z1));
+        }
+        l0 = sgb_logspace_add_lean(l0, m0, LT, ET);
+        l1 = sgb_logspace_add_lean(l1, m1, LT, ET);
+    }
+    if (sp.use_eps) {
+        const double le = sp.log_eps;
+        l0 = sgb_logspace_add_lean(l0, le, LT, ET);
+        l1 = sgb_logspace_add_lean(l1, le, LT, ET);
+    }
+    r0 = l0; r1 = l1;
+}
+
 #if defined(__CUDA_ARCH__)
 #define SGB_NOINLINE __device__ __noinline__
 #else
@@ -363,14 +404,23 @@ SGB_HD int sgb_seq_step(SgbSeqState<SMAX>& st, const double* e, const double* ec
         const double vdia = sgb_add(sgb_add(st.T1[i], tr_self), e[i]);
         Tn[i] = (vdia > voff) ? vdia : voff;
     }
-    double m1 = Tn[0];
-    int i1 = 0;
+    // first maximum by a tournament (depth log2 SMAX instead of a chain of SMAX-1 dependent compares):
+    // the left operand always holds the lower indices, so '>' (strict) keeps the lowest index on ties
+    double tv[SMAX];
+    int ti[SMAX];
 #pragma unroll
-    for (int i = 1; i < SMAX; i++) {
-        const bool gt = Tn[i] > m1;          // strict: the first maximum keeps the lowest index
-        m1 = gt ? Tn[i] : m1;
-        i1 = gt ? i : i1;
+    for (int i = 0; i < SMAX; i++) { tv[i] = Tn[i]; ti[i] = i; }
+#pragma unroll
+    for (int stride = 1; stride < SMAX; stride *= 2) {
+#pragma unroll
+        for (int i = 0; i + stride < SMAX; i += 2 * stride) {
+            const bool gt = tv[i + stride] > tv[i];
+            tv[i] = gt ? tv[i + stride] : tv[i];
+            ti[i] = gt ? ti[i + stride] : ti[i];
+        }
     }
+    const double m1 = tv[0];
+    const int i1 = ti[0];
     int back = i1;
     const double ej = ecol[i1 * estride];
     if (m1 == sgb_add(u1, ej)) {

@@ -58,37 +58,41 @@ __global__ void __launch_bounds__(128) k_pack(const int32_t* __restrict__ n, con
 {
     __shared__ unsigned long long tile[4][32][33];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    // work item = (group, block of 32 bins); items are enumerated group-major by a per-warp walk
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     int bad = 0;
     for (long long g = warp; g < plan.ngroups; g += nwarps) {
         const long long r0 = g * 32;
-        const int nrow = (int)((plan.nseq - r0) < 32 ? (plan.nseq - r0) : 32);
-        const int Tg = plan.len[r0];
+        // lane j keeps row j's length and start; the row loop broadcasts them with shuffles
+        const bool has = r0 + lane < plan.nseq;
+        const int my_len = has ? plan.len[r0 + lane] : 0;
+        const long long my_o = has ? plan.ostart[r0 + lane] : 0;
+        const int Tg = __shfl_sync(SGB_FULL, my_len, 0);
         const int Tpad = ((Tg + SGB_CH - 1) / SGB_CH) * SGB_CH;
         const long long base = plan.goff[g];
         for (int t0 = 0; t0 < Tpad; t0 += 32) {
+            const int t = t0 + lane;
+#pragma unroll 8
             for (int j = 0; j < 32; j++) {
+                const int lenj = __shfl_sync(SGB_FULL, my_len, j);
+                const long long o = __shfl_sync(SGB_FULL, my_o, j) + t;
                 unsigned long long rec = 0ull;
-                if (j < nrow) {
-                    const int lenj = plan.len[r0 + j];
-                    const int t = t0 + lane;
-                    if (t < lenj) {
-                        const long long o = plan.ostart[r0 + j] + t;
-                        const int nv = n[o], xv = x[o];
-                        const int cv = (cn_itemsize == 1) ? (int)((const uint8_t*)cn)[o] : ((const int32_t*)cn)[o];
-                        if (nv < 0 || xv < 0) bad |= SGB_ERR_NEGATIVE_COUNT;
-                        if (nv >= (1 << SGB_COUNT_BITS) || xv >= (1 << SGB_COUNT_BITS)) bad |= SGB_ERR_COUNT_TOO_LARGE;
-                        if (cv < 0 || cv > 255) bad |= SGB_ERR_BAD_CN;
-                        rec = ((unsigned long long)(unsigned)nv & SGB_COUNT_MASK) |
-                              (((unsigned long long)(unsigned)xv & SGB_COUNT_MASK) << SGB_COUNT_BITS) |
-                              ((unsigned long long)(cv & 255) << 56);
-                    }
+                if (t < lenj) {
+                    const int nv = __ldg(n + o), xv = __ldg(x + o);
+                    const int cv = (cn_itemsize == 1) ? (int)__ldg((const uint8_t*)cn + o) : __ldg((const int32_t*)cn + o);
+                    if (nv < 0 || xv < 0) bad |= SGB_ERR_NEGATIVE_COUNT;
+                    if (nv >= (1 << SGB_COUNT_BITS) || xv >= (1 << SGB_COUNT_BITS)) bad |= SGB_ERR_COUNT_TOO_LARGE;
+                    if (cv < 0 || cv > 255) bad |= SGB_ERR_BAD_CN;
+                    rec = ((unsigned long long)(unsigned)nv & SGB_COUNT_MASK) |
+                          (((unsigned long long)(unsigned)xv & SGB_COUNT_MASK) << SGB_COUNT_BITS) |
+                          ((unsigned long long)(cv & 255) << 56);
                 }
                 tile[wid][j][lane] = rec;
             }
             __syncwarp();
             const int nb = (Tpad - t0) < 32 ? (Tpad - t0) : 32;
+#pragma unroll 8
             for (int jb = 0; jb < nb; jb++) packed[base + (long long)(t0 + jb) * 32 + lane] = tile[wid][lane][jb];
             __syncwarp();
         }
@@ -217,7 +221,15 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
             if (A.tabs->kind[threadIdx.x * SGB_MAX_STATES + s] == SGB_KIND_NORMAL) mask |= 1 << s;
         sKM[threadIdx.x] = mask;
     }
-    const SgbScalars sp = A.tabs->sp;
+    __shared__ SgbScalars s_sp;             // read-mostly scalars live in shared memory, not in 16 registers
+    __shared__ SgbTables s_TB;
+    if (threadIdx.x == 0) {
+        s_sp = A.tabs->sp;
+        s_TB.LT = sLT; s_TB.ET = sET; s_TB.LP = sLP; s_TB.LQ = sLQ; s_TB.A = sA; s_TB.B = sB; s_TB.L0 = sL0;
+        s_TB.KIND = sKind; s_TB.S = S; s_TB.lik = A.lik; s_TB.loherror = A.loherror; s_TB.rho = A.rho;
+    }
+    const SgbScalars& sp = s_sp;
+    const SgbTables& TB = s_TB;
 
     const int lane = threadIdx.x & 31;
     const int wid = threadIdx.x >> 5;
@@ -237,9 +249,6 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     }
     __syncthreads();
 
-    SgbTables TB;
-    TB.LT = sLT; TB.ET = sET; TB.LP = sLP; TB.LQ = sLQ; TB.A = sA; TB.B = sB; TB.L0 = sL0; TB.KIND = sKind;
-    TB.S = S; TB.lik = A.lik; TB.loherror = A.loherror; TB.rho = A.rho;
     const double NEG_INF = -sgb_inf();
     unsigned use0 = 0, use1 = 0;            // completed phases of the two stage barriers
 
@@ -353,10 +362,10 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 double r0, r1;
                 if (en0 & en1 & 32) {
                     // both on the lean path: one basic block, two independent dependency chains
-                    r0 = sgb_emission_fast<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
-                                                         LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, sp, sLT, sET);
-                    r1 = sgb_emission_fast<MODEL, LIKBB>(d1.x, d1.y, lx1, ly1, gs1, sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0,
-                                                         LIKBB ? sB[t1] : 0.0, LIKBB ? sL0[t1] : 0.0, sp, sLT, sET);
+                    sgb_emission_fast2<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
+                                                     LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, d1.x, d1.y, lx1, ly1, gs1,
+                                                     sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0, LIKBB ? sB[t1] : 0.0,
+                                                     LIKBB ? sL0[t1] : 0.0, sp, sLT, sET, r0, r1);
                 } else {
                     const int bi0 = bI[ol0], bi1 = bI[ol1];
                     r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);

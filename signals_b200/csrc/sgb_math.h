@@ -128,11 +128,13 @@ SGB_HD double sgb_exp_core(double x, const double* __restrict__ ET)
     int32_t j = k & (SGB_NEXP - 1);
     int64_t q = (int64_t)(k >> 6);
     double s = sgb_u2d(sgb_d2u(ET[j]) + ((uint64_t)q << 52));
-    double p = sgb_fma(r, SGB_C(EXPC6), SGB_C(EXPC5));
-    p = sgb_fma(r, p, SGB_C(EXPC4));
-    p = sgb_fma(r, p, SGB_C(EXPC3));
-    p = sgb_fma(r, p, SGB_C(EXPC2));
-    p = sgb_fma(r, p, 1.0);
+    // Estrin evaluation (3 dependent levels instead of 6): 1 + C2 r + ... + C6 r^5
+    double r2 = sgb_mul(r, r);
+    double p01 = sgb_fma(r, SGB_C(EXPC2), 1.0);
+    double p23 = sgb_fma(r, SGB_C(EXPC4), SGB_C(EXPC3));
+    double p45 = sgb_fma(r, SGB_C(EXPC6), SGB_C(EXPC5));
+    double p = sgb_fma(r2, p45, p23);
+    p = sgb_fma(r2, p, p01);
     p = sgb_mul(r, p);
     return sgb_fma(s, p, s);
 }
@@ -158,14 +160,14 @@ SGB_HD double sgb_log_core(uint64_t ix, int32_t kadj, const double* __restrict__
     if (rcp_seed) *rcp_seed = sgb_u2d(sgb_d2u(invc) - ((uint64_t)(int64_t)k << 52));
     double r = sgb_fma(w, invc, -1.0);
     double kd = (double)(k + kadj);
-    double p = sgb_fma(r, SGB_C(LOGC9), SGB_C(LOGC8));
-    p = sgb_fma(r, p, SGB_C(LOGC7));
-    p = sgb_fma(r, p, SGB_C(LOGC6));
-    p = sgb_fma(r, p, SGB_C(LOGC5));
-    p = sgb_fma(r, p, SGB_C(LOGC4));
-    p = sgb_fma(r, p, SGB_C(LOGC3));
-    p = sgb_fma(r, p, SGB_C(LOGC2));
+    // Estrin evaluation of C2 + C3 r + ... + C9 r^7 (3 dependent levels instead of 7)
     double r2 = sgb_mul(r, r);
+    double r4 = sgb_mul(r2, r2);
+    double q0 = sgb_fma(r, SGB_C(LOGC3), SGB_C(LOGC2));
+    double q1 = sgb_fma(r, SGB_C(LOGC5), SGB_C(LOGC4));
+    double q2 = sgb_fma(r, SGB_C(LOGC7), SGB_C(LOGC6));
+    double q3 = sgb_fma(r, SGB_C(LOGC9), SGB_C(LOGC8));
+    double p = sgb_fma(r4, sgb_fma(r2, q3, q2), sgb_fma(r2, q1, q0));
     double lo = sgb_fma(r2, p, sgb_mul(kd, SGB_C(LN2_LO)));
     double hi = sgb_fma(kd, SGB_C(LN2_HI), logc);
     return sgb_add(hi, sgb_add(r, lo));
@@ -224,14 +226,14 @@ SGB_HD double sgb_log1p01_core(double u, double w, const double* __restrict__ LT
     int32_t i = (int32_t)((sgb_d2u(w) - 0x3ff0000000000000ULL) >> 45);
     double invc = LT[2 * i], logc = LT[2 * i + 1];
     double r = sgb_fma(w, invc, -1.0);
-    double p = sgb_fma(r, SGB_C(LOGC9), SGB_C(LOGC8));
-    p = sgb_fma(r, p, SGB_C(LOGC7));
-    p = sgb_fma(r, p, SGB_C(LOGC6));
-    p = sgb_fma(r, p, SGB_C(LOGC5));
-    p = sgb_fma(r, p, SGB_C(LOGC4));
-    p = sgb_fma(r, p, SGB_C(LOGC3));
-    p = sgb_fma(r, p, SGB_C(LOGC2));
+    // Estrin evaluation of C2 + C3 r + ... + C9 r^7 (3 dependent levels instead of 7)
     double r2 = sgb_mul(r, r);
+    double r4 = sgb_mul(r2, r2);
+    double q0 = sgb_fma(r, SGB_C(LOGC3), SGB_C(LOGC2));
+    double q1 = sgb_fma(r, SGB_C(LOGC5), SGB_C(LOGC4));
+    double q2 = sgb_fma(r, SGB_C(LOGC7), SGB_C(LOGC6));
+    double q3 = sgb_fma(r, SGB_C(LOGC9), SGB_C(LOGC8));
+    double p = sgb_fma(r4, sgb_fma(r2, q3, q2), sgb_fma(r2, q1, q0));
     double lo = sgb_fma(r2, p, sgb_mul(c, invc));
     return sgb_add(logc, sgb_add(r, lo));
 }
@@ -306,12 +308,11 @@ SGB_HD double sgb_lgamma_pos(double z, const double* __restrict__ LT)
         t = sgb_fma(e, e, e);
         rr = sgb_fma(rr, t, rr);
         double r2 = sgb_mul(rr, rr);
-        double c = sgb_fma(r2, SGB_C(STIR7), SGB_C(STIR6));
-        c = sgb_fma(r2, c, SGB_C(STIR5));
-        c = sgb_fma(r2, c, SGB_C(STIR4));
-        c = sgb_fma(r2, c, SGB_C(STIR3));
-        c = sgb_fma(r2, c, SGB_C(STIR2));
-        c = sgb_fma(r2, c, SGB_C(STIR1));
+        double r4 = sgb_mul(r2, r2);
+        double c01 = sgb_fma(r2, SGB_C(STIR2), SGB_C(STIR1));
+        double c23 = sgb_fma(r2, SGB_C(STIR4), SGB_C(STIR3));
+        double c45 = sgb_fma(r2, SGB_C(STIR6), SGB_C(STIR5));
+        double c = sgb_fma(r4, sgb_fma(r4, sgb_fma(r4, SGB_C(STIR7), c45), c23), c01);
         corr = sgb_mul(rr, c);
         // y = fl(z+k): fold the rounding residual back in with lgamma'(y) ~ log y - 1/(2y)
         double dy = sgb_sub(z, sgb_sub(y, (double)k));

@@ -35,8 +35,24 @@ static void run(int S, int decode, double loherror, double eps, double rho, doub
         int L = sgb_live_states(MODEL, b.cprime, S);
         double e[SMAX];
         for (int i = 0; i < SMAX; i++) e[i] = -sgb_inf();
-        for (int i = 0; i < L; i++)
-            e[i] = sgb_emit_item<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, i, TB, sp);
+        // like the kernel: pairs of lean items go through the two-wide function, everything else one by one
+        auto lean = [&](int m) {
+            return b.cprime < SGB_CN_TABLE && b.in_support && sp.fast_ok && tK[b.cprime * S + m] == SGB_KIND_NORMAL;
+        };
+        for (int i = 0; i < L; i += 2) {
+            const int j = (i + 1 < L) ? i + 1 : i;
+            if (lean(i) && lean(j)) {
+                const int t0 = b.cprime * S + i, t1 = b.cprime * S + j;
+                double r0, r1;
+                sgb_emission_fast2<MODEL, LIKBB>(b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, tLP[t0], tLQ[t0], tA[t0], tB[t0], tL0[t0],
+                                                 b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, tLP[t1], tLQ[t1], tA[t1], tB[t1], tL0[t1],
+                                                 sp, LT, ET, r0, r1);
+                e[i] = r0; e[j] = r1;
+            } else {
+                e[i] = sgb_emit_item<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, i, TB, sp);
+                e[j] = sgb_emit_item<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, j, TB, sp);
+            }
+        }
         if (l_out) for (int i = 0; i < S; i++) l_out[t + T * i] = e[i];
         if (t == 0) { sgb_seq_init<SMAX>(st, e, S, sp.init); continue; }
         if (decode == SGB_DECODE_REFERENCE) {
