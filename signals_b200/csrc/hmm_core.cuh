@@ -446,6 +446,67 @@ SGB_HD int sgb_seq_step(SgbSeqState<SMAX>& st, const double* e, const double* ec
     return back;
 }
 
+// The same step with the T1 column kept in (shared) memory instead of registers: T1[i*ts], E[i*es].
+// Frees 2*SMAX registers per thread for occupancy; arithmetic and results are identical to sgb_seq_step.
+template <int SMAX>
+SGB_HD void sgb_seq_init_mem(double* T1, int ts, const double* E, int es, int S, double init, double& m1)
+{
+    double best = -sgb_inf();
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) {
+        const double v = (i < S) ? sgb_add(init, E[i * es]) : -sgb_inf();
+        T1[i * ts] = v;
+        best = (v > best) ? v : best;
+    }
+    m1 = best;
+}
+
+template <int SMAX>
+SGB_HD int sgb_seq_step_mem(double* T1, int ts, const double* E, int es, double& m1io, double tr_self, double tr_off)
+{
+    double Tn[SMAX];
+    const double u1 = sgb_add(m1io, tr_off);
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) {
+        const double e = E[i * es];
+        const double voff = sgb_add(u1, e);
+        const double vdia = sgb_add(sgb_add(T1[i * ts], tr_self), e);
+        Tn[i] = (vdia > voff) ? vdia : voff;
+    }
+    double tv[SMAX];
+    int ti[SMAX];
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) { tv[i] = Tn[i]; ti[i] = i; }
+#pragma unroll
+    for (int stride = 1; stride < SMAX; stride *= 2) {
+#pragma unroll
+        for (int i = 0; i + stride < SMAX; i += 2 * stride) {
+            const bool gt = tv[i + stride] > tv[i];
+            tv[i] = gt ? tv[i + stride] : tv[i];
+            ti[i] = gt ? ti[i + stride] : ti[i];
+        }
+    }
+    const double m1 = tv[0];
+    const int i1 = ti[0];
+    int back = i1;
+    const double ej = E[i1 * es];
+    if (m1 == sgb_add(u1, ej)) {
+        unsigned int pm = 0;
+#pragma unroll
+        for (int k = 0; k < SMAX; k++) {
+            const double val = sgb_add(sgb_add(T1[k * ts], tr_off), ej);
+            pm |= (val == m1) ? (1u << k) : 0u;
+        }
+        const double wd = sgb_add(sgb_add(T1[i1 * ts], tr_self), ej);
+        pm = (pm & ~(1u << i1)) | ((wd == m1) ? (1u << i1) : 0u);
+        back = sgb_ffs32(pm) - 1;
+    }
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) T1[i * ts] = Tn[i];
+    m1io = m1;
+    return back;
+}
+
 // Chained (textbook) mode: backpointers of ALL states for bin j, bp[i] = first argmax_k.
 template <int SMAX>
 SGB_HD void sgb_seq_step_chained(SgbSeqState<SMAX>& st, const double* e, int S, double tr_self, double tr_off,

@@ -123,8 +123,13 @@ struct SgbDecodeArgs {
     double loherror, rho;
 };
 
+#ifndef SGB_DECODE_THREADS
 #define SGB_DECODE_THREADS 256
+#endif
 #define SGB_DECODE_WARPS (SGB_DECODE_THREADS / 32)
+#ifndef SGB_LF_SMEM
+#define SGB_LF_SMEM 1024         // log-factorial entries cached in shared memory (the rest of the 2048 stay in L1/L2)
+#endif
 #ifndef SGB_DECODE_MINBLOCKS
 #define SGB_DECODE_MINBLOCKS 2   // resident CTAs per SM the register allocation is bounded for
 #endif
@@ -160,13 +165,13 @@ __device__ __forceinline__ void sgb_mbar_wait(unsigned long long* bar, unsigned 
 // per-warp shared-memory scratch, in doubles (see the pointer carving in k_decode)
 static inline size_t decode_warp_doubles(int SMAX, int model, int lik_bb, int stage)
 {
-    size_t d = (size_t)SMAX * 32 + 64 + (model == SGB_MODEL_ASCN ? 64 : 32) + (lik_bb ? 32 : 0) + 16 + (size_t)SMAX * 8;
+    size_t d = (size_t)SMAX * 64 + 64 + (model == SGB_MODEL_ASCN ? 64 : 32) + (lik_bb ? 32 : 0) + 16 + (size_t)SMAX * 8;
     if (stage == SGB_STAGE_TMA) d += 2 * 32 * SGB_CH + 2;
     return d;
 }
 static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb, int stage)
 {
-    size_t d = SGB_LOGTAB_LEN + SGB_EXPTAB_LEN + SGB_LFTAB_LEN;
+    size_t d = SGB_LOGTAB_LEN + SGB_EXPTAB_LEN + SGB_LF_SMEM;
     d += (size_t)SGB_CN_TABLE * S * (lik_bb ? 5 : 2);
     d += (size_t)SGB_DECODE_WARPS * decode_warp_doubles(SMAX, model, lik_bb, stage);
     return d * sizeof(double) + ((size_t)SGB_CN_TABLE * S + SGB_CN_TABLE) * sizeof(int);
@@ -191,12 +196,12 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     const int S = A.S;
     const int CTS = SGB_CN_TABLE * S;
     constexpr int NL = (MODEL == SGB_MODEL_ASCN) ? 64 : 32;
-    constexpr int WARP_DOUBLES = SMAX * 32 + 64 + NL + (LIKBB ? 32 : 0) + 16 + SMAX * 8 +
+    constexpr int WARP_DOUBLES = SMAX * 64 + 64 + NL + (LIKBB ? 32 : 0) + 16 + SMAX * 8 +
                                  (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_CH + 2 : 0);
     double* sLT = smem;
     double* sET = sLT + SGB_LOGTAB_LEN;
     double* sLF = sET + SGB_EXPTAB_LEN;
-    double* sLP = sLF + SGB_LFTAB_LEN;
+    double* sLP = sLF + SGB_LF_SMEM;
     double* sLQ = sLP + CTS;
     double* sA = sLQ + CTS;
     double* sB = sA + (LIKBB ? CTS : 0);
@@ -207,7 +212,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
 
     for (int i = threadIdx.x; i < SGB_LOGTAB_LEN; i += blockDim.x) sLT[i] = g_logtab[i];
     for (int i = threadIdx.x; i < SGB_EXPTAB_LEN; i += blockDim.x) sET[i] = g_exptab[i];
-    for (int i = threadIdx.x; i < SGB_LFTAB_LEN; i += blockDim.x) sLF[i] = g_lftab[i];
+    for (int i = threadIdx.x; i < SGB_LF_SMEM; i += blockDim.x) sLF[i] = g_lftab[i];
     for (int i = threadIdx.x; i < CTS; i += blockDim.x) {
         int c = i / S, s = i - c * S, src = c * SGB_MAX_STATES + s;
         sLP[i] = A.tabs->lp[src];
@@ -233,8 +238,9 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
 
     const int lane = threadIdx.x & 31;
     const int wid = threadIdx.x >> 5;
-    double* myE = sW + wid * WARP_DOUBLES;
-    double2* bD = (double2*)(myE + SMAX * 32);                // {x, n-x}
+    double* myE = sW + wid * WARP_DOUBLES;                    // E[state][lane]
+    double* myT = myE + SMAX * 32;                            // T1[state][lane] (forward column of every lane's sequence)
+    double2* bD = (double2*)(myT + SMAX * 32);                // {x, n-x}
     double* bL = (double*)(bD + 32);                          // HSCN: lcx[32]; ASCN: {lcx, lcy}[32]
     double* bG = bL + NL;                                     // beta-binomial: lgamma(s+n)[32]
     int* bI = (int*)(bG + (LIKBB ? 32 : 0));                  // cprime | in_support << 16
@@ -266,10 +272,9 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
         }
         const unsigned long long* gtile = A.packed + A.plan.goff[g];      // [bin][lane] records of this group
         const int Tmax = __shfl_sync(SGB_FULL, len, 0);                   // lane 0 holds the group's longest sequence
-        SgbSeqState<SMAX> st;
-#pragma unroll
-        for (int i = 0; i < SMAX; i++) st.T1[i] = NEG_INF;
-        st.m1 = NEG_INF; st.m2 = NEG_INF; st.i1 = 0;
+        double m1 = NEG_INF;            // running column maximum of this lane's sequence
+        double m2 = NEG_INF;            // second maximum / argmax: only the general and chained variants use them
+        int i1 = 0;
         unsigned long long rec_next = 0ull;
         // one 1-D bulk copy moves chunk c (SGB_CH bins x 32 lanes = 2 KB, contiguous in the tile) into stage c&1
         auto issue_chunk = [&](int c) {
@@ -311,7 +316,8 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 double lcx = 0.0, lcy = 0.0, lgs = 0.0;
                 if (ins) {
                     double fn, fx, fy;
-                    if (n < SGB_NLF) { fn = sLF[n]; fx = sLF[x]; fy = sLF[n - x]; }
+                    if (n < SGB_LF_SMEM) { fn = sLF[n]; fx = sLF[x]; fy = sLF[n - x]; }
+                    else if (n < SGB_NLF) { fn = g_lftab[n]; fx = g_lftab[x]; fy = g_lftab[n - x]; }
                     else { fn = sgb_logfact(n, sLF, sLT); fx = sgb_logfact(x, sLF, sLT); fy = sgb_logfact(n - x, sLF, sLT); }
                     lcx = sgb_sub(sgb_sub(fn, fx), fy);
                     if (MODEL == SGB_MODEL_ASCN) lcy = sgb_sub(sgb_sub(fn, fy), fx);
@@ -375,29 +381,46 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 if (v1) myE[m1 * 32 + ol1] = r1;
             }
             __syncwarp();
-            // ---- (4) forward recursion + decode of this lane's sequence
+            // ---- (4) forward recursion + decode of this lane's sequence (T1 column lives in shared memory)
             if (act) {
-                double e[SMAX];
-#pragma unroll
-                for (int i = 0; i < SMAX; i++) e[i] = myE[i * 32 + lane];
-                if (t == 0) {
-                    sgb_seq_init<SMAX>(st, e, S, sp.init);
-                    if (CHAINED == 0 && len == 1) A.state_out[ostart] = 0;
-                } else if (CHAINED == 0) {
-                    back = sgb_seq_step<SMAX>(st, e, myE + lane, 32, S, sp.tr_self, sp.tr_off, sp.diag_dominant);
-                    A.state_out[ostart + t - 1] = (uint8_t)back;
-                    if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
+                if (CHAINED == 0 && sp.diag_dominant) {
+                    if (t == 0) {
+                        sgb_seq_init_mem<SMAX>(myT + lane, 32, myE + lane, 32, S, sp.init, m1);
+                        if (len == 1) A.state_out[ostart] = 0;
+                    } else {
+                        back = sgb_seq_step_mem<SMAX>(myT + lane, 32, myE + lane, 32, m1, sp.tr_self, sp.tr_off);
+                        A.state_out[ostart + t - 1] = (uint8_t)back;
+                        if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
+                    }
                 } else {
-                    unsigned char bpv[SMAX];
-                    sgb_seq_step_chained<SMAX>(st, e, S, sp.tr_self, sp.tr_off, bpv);
-                    uint8_t* dst = A.bp + (ostart + t) * (long long)S;
+                    // general transition (selftransitionprob < 1/S) or chained decode: register-resident step
+                    SgbSeqState<SMAX> st;
+                    double e[SMAX];
 #pragma unroll
-                    for (int i = 0; i < SMAX; i++) if (i < S) dst[i] = bpv[i];
+                    for (int i = 0; i < SMAX; i++) { e[i] = myE[i * 32 + lane]; st.T1[i] = myT[i * 32 + lane]; }
+                    st.m1 = m1; st.m2 = m2; st.i1 = i1;
+                    if (t == 0) {
+                        sgb_seq_init<SMAX>(st, e, S, sp.init);
+                        if (CHAINED == 0 && len == 1) A.state_out[ostart] = 0;
+                    } else if (CHAINED == 0) {
+                        back = sgb_seq_step<SMAX>(st, e, myE + lane, 32, S, sp.tr_self, sp.tr_off, 0);
+                        A.state_out[ostart + t - 1] = (uint8_t)back;
+                        if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
+                    } else {
+                        unsigned char bpv[SMAX];
+                        sgb_seq_step_chained<SMAX>(st, e, S, sp.tr_self, sp.tr_off, bpv);
+                        uint8_t* dst = A.bp + (ostart + t) * (long long)S;
+#pragma unroll
+                        for (int i = 0; i < SMAX; i++) if (i < S) dst[i] = bpv[i];
+                    }
+#pragma unroll
+                    for (int i = 0; i < SMAX; i++) myT[i * 32 + lane] = st.T1[i];
+                    m1 = st.m1; m2 = st.m2; i1 = st.i1;
                 }
             }
             __syncwarp();
         }
-        if (CHAINED && r < A.plan.nseq) A.last_state[r] = st.i1;
+        if (CHAINED && r < A.plan.nseq) A.last_state[r] = i1;
     }
 }
 
@@ -407,7 +430,11 @@ static cudaError_t launch_decode(const SgbDecodeArgs& A, int sm_count, cudaStrea
     size_t smem = decode_smem_bytes(SMAX, A.S, MODEL, LIKBB, STAGE);
     auto kern = k_decode<SMAX, MODEL, LIKBB, CHAINED, STAGE>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        if (STAGE == SGB_STAGE_TMA) return launch_decode<SMAX, MODEL, LIKBB, CHAINED, SGB_STAGE_LDG>(A, sm_count, st);
+        return e;
+    }
     int blocks = (A.plan.ngroups + SGB_DECODE_WARPS - 1) / SGB_DECODE_WARPS;
     int occ = 1;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, SGB_DECODE_THREADS, smem) != cudaSuccess || occ < 1) occ = 1;

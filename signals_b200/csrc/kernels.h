@@ -22,7 +22,9 @@ struct SgbDevTables {
 // Packed buffer: group g owns a tile of roundup(T_g, SGB_CH) x 32 records starting at goff[g],
 // record (bin t, lane l) at goff[g] + t*32 + l  (bin-major, lanes interleaved: a warp reads 256
 // contiguous bytes per bin and one 1-D bulk copy moves SGB_CH bins of all 32 sequences).
+#ifndef SGB_CH
 #define SGB_CH 8               // bins per staged chunk
+#endif
 struct SgbPlanDev {
     const long long* goff;     // [ngroups] first record of the group's tile in the packed buffer
     const long long* ostart;   // [nseq] first row of the sequence in the caller's n/x/cn/state arrays

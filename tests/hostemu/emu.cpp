@@ -29,6 +29,7 @@ static void run(int S, int decode, double loherror, double eps, double rho, doub
     TB.LT = LT; TB.ET = ET; TB.LP = tLP.data(); TB.LQ = tLQ.data(); TB.A = tA.data(); TB.B = tB.data();
     TB.L0 = tL0.data(); TB.KIND = tK.data(); TB.S = S; TB.lik = lik; TB.loherror = loherror; TB.rho = rho;
     SgbSeqState<SMAX> st;
+    double T1m[SMAX], m1m = 0.0;
     std::vector<unsigned char> bp((size_t)T * S);
     for (long t = 0; t < T; t++) {
         SgbBin b = sgb_bin_prepare(MODEL, LIKBB, n[t], x[t], cn[t], sp.bb_s, LF, LT);
@@ -54,8 +55,15 @@ static void run(int S, int decode, double loherror, double eps, double rho, doub
             }
         }
         if (l_out) for (int i = 0; i < S; i++) l_out[t + T * i] = e[i];
-        if (t == 0) { sgb_seq_init<SMAX>(st, e, S, sp.init); continue; }
-        if (decode == SGB_DECODE_REFERENCE) {
+        const bool mem = (decode == SGB_DECODE_REFERENCE) && sp.diag_dominant;      // the kernel's fast path
+        if (t == 0) {
+            if (mem) sgb_seq_init_mem<SMAX>(T1m, 1, e, 1, S, sp.init, m1m);
+            else sgb_seq_init<SMAX>(st, e, S, sp.init);
+            continue;
+        }
+        if (mem) {
+            out[t - 1] = (unsigned char)sgb_seq_step_mem<SMAX>(T1m, 1, e, 1, m1m, sp.tr_self, sp.tr_off);
+        } else if (decode == SGB_DECODE_REFERENCE) {
             int back = sgb_seq_step<SMAX>(st, e, e, 1, S, sp.tr_self, sp.tr_off, sp.diag_dominant);
             out[t - 1] = (unsigned char)back;
         } else {
