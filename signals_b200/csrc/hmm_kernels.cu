@@ -163,11 +163,21 @@ __device__ __forceinline__ void sgb_mbar_wait(unsigned long long* bar, unsigned 
 }
 
 // per-warp shared-memory scratch, in doubles (see the pointer carving in k_decode)
+//   E  [32][P]  emissions of the current bin, lane-major with odd pitch P = SMAX+1 (conflict-free columns)
+//   T1 [32][P]  forward column of every lane's sequence
+//   E2 [32][P]  second density (ASCN binomial only)
+//   bD/bL/bG    per-lane bin fields for the item queue (beta-binomial only)
+//   bI [32]     cprime | in_support << 16
+//   q           work queue, SMAX*32 uint16 entries
+//   stage       2 x SGB_CH x 32 records + 2 mbarriers (TMA staging only)
 static inline size_t decode_warp_doubles(int SMAX, int model, int lik_bb, int stage)
 {
-    size_t d = (size_t)SMAX * 64 + 64 + (model == SGB_MODEL_ASCN ? 64 : 32) + (lik_bb ? 32 : 0) + 16 + (size_t)SMAX * 8;
+    const size_t P = (size_t)SMAX + 1;
+    size_t d = 2 * 32 * P + 16 + (size_t)SMAX * 8;
+    if (!lik_bb && model == SGB_MODEL_ASCN) d += 32 * P;
+    if (lik_bb) d += 64 + (model == SGB_MODEL_ASCN ? 64 : 32) + 32;
     if (stage == SGB_STAGE_TMA) d += 2 * 32 * SGB_CH + 2;
-    return d;
+    return (d + 1) & ~(size_t)1;
 }
 static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb, int stage)
 {
@@ -179,25 +189,28 @@ static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb, i
 
 // Fused emission + forward recursion + decode.  One lane per (cell, chromosome) sequence, 32 sequences
 // of similar length per warp, warps fetch groups from a global counter (longest first).
-// Per bin step a warp
-//  (0) takes its 32 packed records from a shared-memory stage that 1-D TMA bulk copies filled one chunk
-//      (8 bins per sequence) ahead, completion tracked by an mbarrier per stage,
-//  (1) unpacks them and looks the log-factorials up in shared memory,
-//  (2) compacts the LIVE (lane, state) pairs of all 32 lanes into a queue (prefix sum of the live-state
-//      counts) -- lanes with copy number 2 do not idle while a lane with copy number 9 works,
-//  (3) evaluates the queue two entries per lane per round (two independent FP64 chains per thread),
-//      writing E[state][lane],
-//  (4) runs the O(S) max-plus step of its own sequence from registers and stores the decoded state of
-//      the previous bin.
+// The kernel is bound by shared-memory bandwidth and FP64 issue, so per bin step a warp
+//  (0) takes its 32 packed records from a shared-memory stage that a 1-D TMA bulk copy filled one chunk
+//      (SGB_CH bins x 32 sequences, 2 KB contiguous) ahead, completion tracked by an mbarrier per stage;
+//  (1) unpacks them, looks the log-factorials up;
+//  (2) binomial: every lane evaluates the (2-fma) log densities of its own live states; states whose density
+//      is provably floored by eps get log(eps) without any transcendental (sp.lsa_skip, exact), the others
+//      are queued.  beta-binomial: all live (lane, state) pairs are queued;
+//  (3) the queue -- compacted across the 32 lanes by a prefix sum, so a lane with copy number 2 does not
+//      idle while a lane with copy number 9 works -- is evaluated two entries per lane per round;
+//  (4) each lane runs the O(S) max-plus step of its sequence over the live states only and stores the
+//      decoded state of the previous bin.
 template <int SMAX, int MODEL, int LIKBB, int CHAINED, int STAGE>
 __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_decode(SgbDecodeArgs A)
 {
     extern __shared__ __align__(16) double smem[];
     const int S = A.S;
     const int CTS = SGB_CN_TABLE * S;
+    constexpr int P = SMAX + 1;
     constexpr int NL = (MODEL == SGB_MODEL_ASCN) ? 64 : 32;
-    constexpr int WARP_DOUBLES = SMAX * 64 + 64 + NL + (LIKBB ? 32 : 0) + 16 + SMAX * 8 +
-                                 (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_CH + 2 : 0);
+    constexpr int WD0 = 2 * 32 * P + 16 + SMAX * 8 + ((!LIKBB && MODEL == SGB_MODEL_ASCN) ? 32 * P : 0) +
+                        (LIKBB ? 64 + NL + 32 : 0) + (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_CH + 2 : 0);
+    constexpr int WARP_DOUBLES = (WD0 + 1) & ~1;
     double* sLT = smem;
     double* sET = sLT + SGB_LOGTAB_LEN;
     double* sLF = sET + SGB_EXPTAB_LEN;
@@ -226,7 +239,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
             if (A.tabs->kind[threadIdx.x * SGB_MAX_STATES + s] == SGB_KIND_NORMAL) mask |= 1 << s;
         sKM[threadIdx.x] = mask;
     }
-    __shared__ SgbScalars s_sp;             // read-mostly scalars live in shared memory, not in 16 registers
+    __shared__ SgbScalars s_sp;             // read-mostly scalars live in shared memory, not in registers
     __shared__ SgbTables s_TB;
     if (threadIdx.x == 0) {
         s_sp = A.tabs->sp;
@@ -238,11 +251,13 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
 
     const int lane = threadIdx.x & 31;
     const int wid = threadIdx.x >> 5;
-    double* myE = sW + wid * WARP_DOUBLES;                    // E[state][lane]
-    double* myT = myE + SMAX * 32;                            // T1[state][lane] (forward column of every lane's sequence)
-    double2* bD = (double2*)(myT + SMAX * 32);                // {x, n-x}
-    double* bL = (double*)(bD + 32);                          // HSCN: lcx[32]; ASCN: {lcx, lcy}[32]
-    double* bG = bL + NL;                                     // beta-binomial: lgamma(s+n)[32]
+    double* myE = sW + wid * WARP_DOUBLES;                    // E [lane][P]
+    double* myT = myE + 32 * P;                               // T1[lane][P]
+    double* myE2 = myT + 32 * P;                              // ASCN binomial: second density [lane][P]
+    double* pq = myE2 + ((!LIKBB && MODEL == SGB_MODEL_ASCN) ? 32 * P : 0);
+    double2* bD = (double2*)pq;                               // beta-binomial: {x, n-x}
+    double* bL = pq + (LIKBB ? 64 : 0);                       //   HSCN lcx[32]; ASCN {lcx, lcy}[32]
+    double* bG = bL + (LIKBB ? NL : 0);                       //   lgamma(s+n)[32]
     int* bI = (int*)(bG + (LIKBB ? 32 : 0));                  // cprime | in_support << 16
     unsigned short* q = (unsigned short*)(bI + 32);
     unsigned long long* stg = (unsigned long long*)(q + SMAX * 32);     // [2][SGB_CH][32] records
@@ -256,6 +271,9 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     __syncthreads();
 
     const double NEG_INF = -sgb_inf();
+    double* colE = myE + lane * P;          // this lane's own columns
+    double* colT = myT + lane * P;
+    double* colE2 = myE2 + lane * P;
     unsigned use0 = 0, use1 = 0;            // completed phases of the two stage barriers
 
     for (;;) {
@@ -276,7 +294,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
         double m2 = NEG_INF;            // second maximum / argmax: only the general and chained variants use them
         int i1 = 0;
         unsigned long long rec_next = 0ull;
-        // one 1-D bulk copy moves chunk c (SGB_CH bins x 32 lanes = 2 KB, contiguous in the tile) into stage c&1
+        // one 1-D bulk copy moves chunk c (SGB_CH bins x 32 lanes, contiguous in the tile) into stage c&1
         auto issue_chunk = [&](int c) {
             if (lane == 0) {
                 unsigned long long* b = &bar[c & 1];
@@ -291,6 +309,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
         }
         int back = 0;
         int Lprev = SMAX;          // states >= L hold -Inf in this lane's E column; refreshed when L shrinks
+        int Lw_prev = SMAX;        // warp-wide maximum live-state count of the previous bin
         for (int t = 0; t < Tmax; t++) {
             const bool act = t < len;
             unsigned long long rec;
@@ -307,13 +326,13 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 if (t + 1 < Tmax) rec_next = __ldg(gtile + (long long)(t + 1) * 32 + lane);
             }
             // ---- (1) per-bin quantities of this lane's sequence
-            int L = 0, ebase = 0;
+            int L = 0, cprime = 0, ins = 0, fastmask = 0;
+            double kd = 0.0, nkd = 0.0, lcx = 0.0, lcy = 0.0, lgs = 0.0;
             if (act) {
                 const int n = (int)(rec & SGB_COUNT_MASK), x = (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK);
-                const int cprime = sgb_cprime(MODEL, (int)(rec >> 56));
-                const int ins = x <= n;
+                cprime = sgb_cprime(MODEL, (int)(rec >> 56));
+                ins = x <= n;
                 L = sgb_live_states(MODEL, cprime, S);
-                double lcx = 0.0, lcy = 0.0, lgs = 0.0;
                 if (ins) {
                     double fn, fx, fy;
                     if (n < SGB_LF_SMEM) { fn = sLF[n]; fx = sLF[x]; fy = sLF[n - x]; }
@@ -323,72 +342,113 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     if (MODEL == SGB_MODEL_ASCN) lcy = sgb_sub(sgb_sub(fn, fy), fx);
                     if (LIKBB) lgs = sgb_lgamma_pos(sgb_add(sp.bb_s, (double)n), sLT);
                 }
-                bD[lane] = make_double2((double)x, (double)(n - x));
-                if (MODEL == SGB_MODEL_ASCN) ((double2*)bL)[lane] = make_double2(lcx, lcy);
-                else bL[lane] = lcx;
-                if (LIKBB) bG[lane] = lgs;
-                bI[lane] = cprime | (ins << 16);
+                kd = (double)x; nkd = (double)(n - x);
                 const bool tab = cprime < SGB_CN_TABLE;
-                const int fastmask = (tab && ins && sp.fast_ok) ? sKM[cprime] : 0;
-                const int lm = (1 << L) - 1;
-                // all live states of this bin on the lean path (the usual case) -> one flag for the lane's entries
-                ebase = lane | ((tab ? cprime : 0) << 11) | (((fastmask & lm) == lm) ? 32 : 0);
-                for (int i = L; i < Lprev; i++) myE[i * 32 + lane] = NEG_INF;      // rare: only when L shrinks
+                fastmask = (tab && ins && sp.fast_ok) ? sKM[cprime] : 0;
+                for (int i = L; i < Lprev; i++) colE[i] = NEG_INF;      // rare: only when L shrinks
                 Lprev = L;
             }
-            // ---- (2) queue of live (lane, state) pairs: lane | lean << 5 | state << 6 | cprime << 11
-            int incl = L;
+            const int Lw = __reduce_max_sync(SGB_FULL, L);
+            // ---- (2) what has to go through the queue
+            unsigned need = 0;          // bit m: state m of this lane's bin is queued
+            if (LIKBB) {
+                if (act) {
+                    bD[lane] = make_double2(kd, nkd);
+                    if (MODEL == SGB_MODEL_ASCN) ((double2*)bL)[lane] = make_double2(lcx, lcy);
+                    else bL[lane] = lcx;
+                    bG[lane] = lgs;
+                    bI[lane] = cprime | (ins << 16);
+                    need = (1u << L) - 1u;
+                }
+            } else {
+                // binomial: densities by the owner lane; the exact eps-floor shortcut settles most wrong states here
+                for (int m = 0; m < Lw; m++) {
+                    if (m < L) {
+                        if ((fastmask >> m) & 1) {
+                            const int ti = cprime * S + m;
+                            double l1, l2, out;
+                            if (sgb_binom_stage<MODEL>(kd, nkd, lcx, lcy, sLP[ti], sLQ[ti], sp, l1, l2, out)) {
+                                colE[m] = l1;
+                                if (MODEL == SGB_MODEL_ASCN) colE2[m] = l2;
+                                need |= 1u << m;
+                            } else {
+                                colE[m] = out;
+                            }
+                        } else {
+                            colE[m] = sgb_emit_item_slow<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, m, TB, sp);
+                        }
+                    }
+                }
+            }
+            int cnt = __popc(need);
+            int incl = cnt;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 int v = __shfl_up_sync(SGB_FULL, incl, d);
                 if (lane >= d) incl += v;
             }
             const int tot = __shfl_sync(SGB_FULL, incl, 31);
-            const int qoff = incl - L;
-#pragma unroll
-            for (int m = 0; m < SMAX; m++)
-                if (m < L) q[qoff + m] = (unsigned short)(ebase + (m << 6));
+            {
+                int qpos = incl - cnt;
+                unsigned rem = need;
+                const int allfast = LIKBB ? (((fastmask & need) == need) ? 32 : 0) : 0;
+                const int ebase = lane | allfast | (((cprime < SGB_CN_TABLE) ? cprime : 0) << 11);
+                while (rem) {
+                    const int m = __ffs((int)rem) - 1;
+                    rem &= rem - 1;
+                    q[qpos++] = (unsigned short)(ebase | (m << 6));
+                }
+            }
             __syncwarp();
-            // ---- (3) emissions, two queue entries per lane per round
+            // ---- (3) the queue, two entries per lane per round
             for (int base = 0; base < tot; base += 64) {
                 const int j0 = base + lane, j1 = j0 + 32;
                 const bool v0 = j0 < tot, v1 = j1 < tot;
                 const int en0 = q[v0 ? j0 : 0], en1 = q[v1 ? j1 : (v0 ? j0 : 0)];
-                const int ol0 = en0 & 31, m0 = (en0 >> 6) & 31, ol1 = en1 & 31, m1 = (en1 >> 6) & 31;
-                const int t0 = (en0 >> 11) * S + m0, t1 = (en1 >> 11) * S + m1;
-                const double2 d0 = bD[ol0], d1 = bD[ol1];
-                double lx0, ly0 = 0.0, lx1, ly1 = 0.0;
-                if (MODEL == SGB_MODEL_ASCN) {
-                    const double2 a0 = ((const double2*)bL)[ol0], a1 = ((const double2*)bL)[ol1];
-                    lx0 = a0.x; ly0 = a0.y; lx1 = a1.x; ly1 = a1.y;
-                } else {
-                    lx0 = bL[ol0]; lx1 = bL[ol1];
-                }
-                const double gs0 = LIKBB ? bG[ol0] : 0.0, gs1 = LIKBB ? bG[ol1] : 0.0;
+                const int ol0 = en0 & 31, m0 = (en0 >> 6) & 31, ol1 = en1 & 31, mm1 = (en1 >> 6) & 31;
                 double r0, r1;
-                if (en0 & en1 & 32) {
-                    // both on the lean path: one basic block, two independent dependency chains
-                    sgb_emission_fast2<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
-                                                     LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, d1.x, d1.y, lx1, ly1, gs1,
-                                                     sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0, LIKBB ? sB[t1] : 0.0,
-                                                     LIKBB ? sL0[t1] : 0.0, sp, sLT, sET, r0, r1);
+                if (!LIKBB) {
+                    const double a0 = myE[ol0 * P + m0], a1 = myE[ol1 * P + mm1];
+                    const double b0 = (MODEL == SGB_MODEL_ASCN) ? myE2[ol0 * P + m0] : 0.0;
+                    const double b1 = (MODEL == SGB_MODEL_ASCN) ? myE2[ol1 * P + mm1] : 0.0;
+                    if (MODEL == SGB_MODEL_ASCN) __syncwarp();      // (reads of a round precede its writes: entries are distinct)
+                    r0 = sgb_binom_finish<MODEL>(a0, b0, sp, sLT, sET);
+                    r1 = sgb_binom_finish<MODEL>(a1, b1, sp, sLT, sET);
                 } else {
-                    const int bi0 = bI[ol0], bi1 = bI[ol1];
-                    r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
-                    r1 = v1 ? sgb_emit_item<MODEL, LIKBB>(bi1 & 0xffff, bi1 >> 16, d1.x, d1.y, lx1, ly1, gs1, m1, TB, sp) : 0.0;
+                    const int t0 = (en0 >> 11) * S + m0, t1 = (en1 >> 11) * S + mm1;
+                    const double2 d0 = bD[ol0], d1 = bD[ol1];
+                    double lx0, ly0 = 0.0, lx1, ly1 = 0.0;
+                    if (MODEL == SGB_MODEL_ASCN) {
+                        const double2 c0 = ((const double2*)bL)[ol0], c1 = ((const double2*)bL)[ol1];
+                        lx0 = c0.x; ly0 = c0.y; lx1 = c1.x; ly1 = c1.y;
+                    } else {
+                        lx0 = bL[ol0]; lx1 = bL[ol1];
+                    }
+                    const double gs0 = bG[ol0], gs1 = bG[ol1];
+                    if (en0 & en1 & 32) {
+                        sgb_emission_fast2<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], sA[t0], sB[t0], sL0[t0],
+                                                         d1.x, d1.y, lx1, ly1, gs1, sLP[t1], sLQ[t1], sA[t1], sB[t1], sL0[t1],
+                                                         sp, sLT, sET, r0, r1);
+                    } else {
+                        const int bi0 = bI[ol0], bi1 = bI[ol1];
+                        r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
+                        r1 = v1 ? sgb_emit_item<MODEL, LIKBB>(bi1 & 0xffff, bi1 >> 16, d1.x, d1.y, lx1, ly1, gs1, mm1, TB, sp) : 0.0;
+                    }
                 }
-                if (v0) myE[m0 * 32 + ol0] = r0;
-                if (v1) myE[m1 * 32 + ol1] = r1;
+                if (v0) myE[ol0 * P + m0] = r0;
+                if (v1) myE[ol1 * P + mm1] = r1;
             }
             __syncwarp();
             // ---- (4) forward recursion + decode of this lane's sequence (T1 column lives in shared memory)
+            const int nlive = (t == 0) ? SMAX : (Lw > Lw_prev ? Lw : Lw_prev);
+            Lw_prev = Lw;
             if (act) {
                 if (CHAINED == 0 && sp.diag_dominant) {
                     if (t == 0) {
-                        sgb_seq_init_mem<SMAX>(myT + lane, 32, myE + lane, 32, S, sp.init, m1);
+                        sgb_seq_init_mem<SMAX>(colT, 1, colE, 1, S, sp.init, m1);
                         if (len == 1) A.state_out[ostart] = 0;
                     } else {
-                        back = sgb_seq_step_mem<SMAX>(myT + lane, 32, myE + lane, 32, m1, sp.tr_self, sp.tr_off);
+                        back = sgb_seq_step_mem<SMAX>(colT, 1, colE, 1, m1, sp.tr_self, sp.tr_off, nlive);
                         A.state_out[ostart + t - 1] = (uint8_t)back;
                         if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
                     }
@@ -397,13 +457,13 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     SgbSeqState<SMAX> st;
                     double e[SMAX];
 #pragma unroll
-                    for (int i = 0; i < SMAX; i++) { e[i] = myE[i * 32 + lane]; st.T1[i] = myT[i * 32 + lane]; }
+                    for (int i = 0; i < SMAX; i++) { e[i] = colE[i]; st.T1[i] = colT[i]; }
                     st.m1 = m1; st.m2 = m2; st.i1 = i1;
                     if (t == 0) {
                         sgb_seq_init<SMAX>(st, e, S, sp.init);
                         if (CHAINED == 0 && len == 1) A.state_out[ostart] = 0;
                     } else if (CHAINED == 0) {
-                        back = sgb_seq_step<SMAX>(st, e, myE + lane, 32, S, sp.tr_self, sp.tr_off, 0);
+                        back = sgb_seq_step<SMAX>(st, e, colE, 1, S, sp.tr_self, sp.tr_off, 0);
                         A.state_out[ostart + t - 1] = (uint8_t)back;
                         if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
                     } else {
@@ -414,7 +474,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                         for (int i = 0; i < SMAX; i++) if (i < S) dst[i] = bpv[i];
                     }
 #pragma unroll
-                    for (int i = 0; i < SMAX; i++) myT[i * 32 + lane] = st.T1[i];
+                    for (int i = 0; i < SMAX; i++) colT[i] = st.T1[i];
                     m1 = st.m1; m2 = st.m2; i1 = st.i1;
                 }
             }

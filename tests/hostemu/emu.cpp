@@ -30,31 +30,48 @@ static void run(int S, int decode, double loherror, double eps, double rho, doub
     TB.L0 = tL0.data(); TB.KIND = tK.data(); TB.S = S; TB.lik = lik; TB.loherror = loherror; TB.rho = rho;
     SgbSeqState<SMAX> st;
     double T1m[SMAX], m1m = 0.0;
+    int Lkeep = SMAX;
     std::vector<unsigned char> bp((size_t)T * S);
     for (long t = 0; t < T; t++) {
         SgbBin b = sgb_bin_prepare(MODEL, LIKBB, n[t], x[t], cn[t], sp.bb_s, LF, LT);
         int L = sgb_live_states(MODEL, b.cprime, S);
         double e[SMAX];
         for (int i = 0; i < SMAX; i++) e[i] = -sgb_inf();
-        // like the kernel: pairs of lean items go through the two-wide function, everything else one by one
         auto lean = [&](int m) {
             return b.cprime < SGB_CN_TABLE && b.in_support && sp.fast_ok && tK[b.cprime * S + m] == SGB_KIND_NORMAL;
         };
-        for (int i = 0; i < L; i += 2) {
-            const int j = (i + 1 < L) ? i + 1 : i;
-            if (lean(i) && lean(j)) {
-                const int t0 = b.cprime * S + i, t1 = b.cprime * S + j;
-                double r0, r1;
-                sgb_emission_fast2<MODEL, LIKBB>(b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, tLP[t0], tLQ[t0], tA[t0], tB[t0], tL0[t0],
-                                                 b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, tLP[t1], tLQ[t1], tA[t1], tB[t1], tL0[t1],
-                                                 sp, LT, ET, r0, r1);
-                e[i] = r0; e[j] = r1;
-            } else {
-                e[i] = sgb_emit_item<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, i, TB, sp);
-                e[j] = sgb_emit_item<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, j, TB, sp);
+        if (!LIKBB) {
+            // binomial kernels: owner-lane density stage (with the exact eps-floor shortcut), then the finish stage
+            for (int i = 0; i < L; i++) {
+                if (lean(i)) {
+                    const int ti = b.cprime * S + i;
+                    double l1, l2, out;
+                    if (sgb_binom_stage<MODEL>(b.kd, b.nkd, b.lc_x, b.lc_y, tLP[ti], tLQ[ti], sp, l1, l2, out))
+                        out = sgb_binom_finish<MODEL>(l1, l2, sp, LT, ET);
+                    e[i] = out;
+                } else {
+                    e[i] = sgb_emit_item_slow<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, i, TB, sp);
+                }
+            }
+        } else {
+            // beta-binomial kernels: pairs of lean items go through the two-wide function, the rest one by one
+            for (int i = 0; i < L; i += 2) {
+                const int j = (i + 1 < L) ? i + 1 : i;
+                if (lean(i) && lean(j)) {
+                    const int t0 = b.cprime * S + i, t1 = b.cprime * S + j;
+                    double r0, r1;
+                    sgb_emission_fast2<MODEL, LIKBB>(b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, tLP[t0], tLQ[t0], tA[t0], tB[t0], tL0[t0],
+                                                     b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, tLP[t1], tLQ[t1], tA[t1], tB[t1], tL0[t1],
+                                                     sp, LT, ET, r0, r1);
+                    e[i] = r0; e[j] = r1;
+                } else {
+                    e[i] = sgb_emit_item<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, i, TB, sp);
+                    e[j] = sgb_emit_item<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, j, TB, sp);
+                }
             }
         }
         if (l_out) for (int i = 0; i < S; i++) l_out[t + T * i] = e[i];
+        const int Lprev = Lkeep; Lkeep = L;
         const bool mem = (decode == SGB_DECODE_REFERENCE) && sp.diag_dominant;      // the kernel's fast path
         if (t == 0) {
             if (mem) sgb_seq_init_mem<SMAX>(T1m, 1, e, 1, S, sp.init, m1m);
@@ -62,7 +79,8 @@ static void run(int S, int decode, double loherror, double eps, double rho, doub
             continue;
         }
         if (mem) {
-            out[t - 1] = (unsigned char)sgb_seq_step_mem<SMAX>(T1m, 1, e, 1, m1m, sp.tr_self, sp.tr_off);
+            const int nlive = (L > Lprev) ? L : Lprev;       // the kernel uses the warp-wide maxima of the same two counts
+            out[t - 1] = (unsigned char)sgb_seq_step_mem<SMAX>(T1m, 1, e, 1, m1m, sp.tr_self, sp.tr_off, nlive);
         } else if (decode == SGB_DECODE_REFERENCE) {
             int back = sgb_seq_step<SMAX>(st, e, e, 1, S, sp.tr_self, sp.tr_off, sp.diag_dominant);
             out[t - 1] = (unsigned char)back;
@@ -99,4 +117,28 @@ extern "C" int emu_decode_sequence(int model, int lik, int S, int decode, double
     else if (S <= 32) run_s<32>(model, lik_bb, S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
     else return -1;
     return 0;
+}
+
+// Exactness of the eps-floor shortcut (SgbScalars::lsa_skip): for every l below the threshold the full
+// logspace_add(l, log eps) must return log eps bit-for-bit.  Returns the number of violations.
+extern "C" long emu_lsa_skip_violations(double eps, long n_samples, double* skip_out)
+{
+    SgbScalars sp = sgb_scalars(12, eps, 0.0, 0.95, 0.0, LT);
+    if (skip_out) *skip_out = sp.lsa_skip;
+    if (!(sp.lsa_skip > -sgb_inf())) return 0;
+    long bad = 0;
+    unsigned long long st = 88172645463325252ull;
+    for (long i = 0; i < n_samples; i++) {
+        st ^= st << 13; st ^= st >> 7; st ^= st << 17;
+        double u = (double)(st >> 11) * 0x1p-53;
+        // dense just below the threshold, sparse far below it
+        double l = (i & 1) ? sp.lsa_skip - u * 2.0 - 1e-300 : sp.lsa_skip - u * 800.0 - 1e-300;
+        if (!(l < sp.lsa_skip)) continue;
+        double r = sgb_logspace_add(l, sp.log_eps, LT, ET);
+        if (sgb_d2u(r) != sgb_d2u(sp.log_eps)) bad++;
+    }
+    // the largest double below the threshold, too
+    double l = sgb_u2d(sgb_d2u(sp.lsa_skip) + 1);      // lsa_skip is negative: +1 ulp in magnitude = next below
+    if (sgb_d2u(sgb_logspace_add(l, sp.log_eps, LT, ET)) != sgb_d2u(sp.log_eps)) bad++;
+    return bad;
 }
