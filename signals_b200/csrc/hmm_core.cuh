@@ -51,7 +51,6 @@ struct SgbScalars {
     double bb_s;        // (1-rho)/rho
     int use_eps;
     int use_abias;
-    double lsa_skip;    // l < lsa_skip  =>  logspace_add(l, log_eps) == log_eps exactly (see sgb_scalars)
     int fast_ok;        // the lean emission path is valid (no Abias, log(eps) finite)
     int diag_dominant;  // tr_self >= tr_off: the O(S) recursion needs only the column maximum
 };
@@ -111,16 +110,6 @@ SGB_HD SgbScalars sgb_scalars(int S, double eps, double Abias, double stp, doubl
     s.bb_s = (rho > 0.0) ? sgb_div(sgb_sub(1.0, rho), rho) : 0.0;
     s.fast_ok = !s.use_abias && (!s.use_eps || (s.log_eps == s.log_eps && sgb_fabs(s.log_eps) != sgb_inf()));
     s.diag_dominant = (s.tr_self >= s.tr_off) ? 1 : 0;
-    // Exact shortcut for the eps floor.  For l < log_eps with u = exp(l - log_eps) < 2^-53, 1+u rounds to 1 and
-    // the log1p kernel returns exactly u; if also u < 2^-54 |log_eps| (under half an ulp of log_eps) the sum
-    // log_eps + u rounds back to log_eps.  lsa_skip sits one e-fold below that bound, so every l < lsa_skip
-    // yields log_eps bit-for-bit without evaluating exp / log1p.  -Inf disables the shortcut.
-    s.lsa_skip = -sgb_inf();
-    if (s.use_eps && s.fast_ok) {
-        const double a = sgb_mul(0x1p-54, sgb_fabs(s.log_eps));
-        const double bound = (a < 0x1p-53) ? a : 0x1p-53;
-        if (bound > 0x1p-1000) s.lsa_skip = sgb_add(s.log_eps, sgb_sub(sgb_log(bound, LT), 1.0));
-    }
     return s;
 }
 
@@ -251,41 +240,6 @@ SGB_HD void sgb_emission_fast2(double kd0, double nk0, double lx0, double ly0, d
         l1 = sgb_logspace_add_lean(l1, le, LT, ET);
     }
     r0 = l0; r1 = l1;
-}
-
-// ---- binomial likelihood, split in two stages --------------------------------------------------------
-// Stage 1 (cheap, run by the lane that owns the bin): the log densities, 2 fmas each.  Returns 1 when the
-// emission still needs the logspace_add stage (l1 [, l2] to be finished by sgb_binom_finish), 0 when
-// *out already is the final emission: either eps == 0 (HSCN: the density itself) or the density is so far
-// below log(eps) that logspace_add returns log(eps) exactly (sp.lsa_skip).
-template <int MODEL>
-SGB_HD int sgb_binom_stage(double kd, double nkd, double lc_x, double lc_y, double lp, double lq,
-                           const SgbScalars& sp, double& l1, double& l2, double& out)
-{
-    l1 = sgb_fma(nkd, lq, sgb_fma(kd, lp, lc_x));
-    l2 = 0.0;
-    if (MODEL == SGB_MODEL_ASCN) {
-        l2 = sgb_fma(kd, lq, sgb_fma(nkd, lp, lc_y));
-        if (!sp.use_eps) return 1;                                   // still needs logspace_add(l1, l2)
-        const double mx = (l1 > l2) ? l1 : l2;
-        // logspace_add(l1,l2) <= max + ln 2 (< max + 0.7): still below the exact-floor threshold
-        if (sgb_add(mx, 0.7) < sp.lsa_skip) { out = sp.log_eps; return 0; }
-        return 1;
-    }
-    if (!sp.use_eps) { out = l1; return 0; }
-    if (l1 < sp.lsa_skip) { out = sp.log_eps; return 0; }
-    return 1;
-}
-
-// Stage 2: the logspace_add chain of one emission (R/callASCN.R:64 and R/callHSCN.R:67-71)
-template <int MODEL>
-SGB_HD double sgb_binom_finish(double l1, double l2, const SgbScalars& sp, const double* __restrict__ LT,
-                               const double* __restrict__ ET)
-{
-    double l = l1;
-    if (MODEL == SGB_MODEL_ASCN) l = sgb_logspace_add_lean(l1, l2, LT, ET);
-    if (sp.use_eps) l = sgb_logspace_add_lean(l, sp.log_eps, LT, ET);
-    return l;
 }
 
 #if defined(__CUDA_ARCH__)

@@ -73,22 +73,28 @@ __global__ void __launch_bounds__(128) k_pack(const int32_t* __restrict__ n, con
         const long long base = plan.goff[g];
         for (int t0 = 0; t0 < Tpad; t0 += 32) {
             const int t = t0 + lane;
-#pragma unroll 8
+            // all 96 loads of the block are issued before any is consumed (the kernel is latency-, not issue-bound)
+            int nv[32], xv[32], cv[32];
+            unsigned okmask = 0;
+#pragma unroll
             for (int j = 0; j < 32; j++) {
                 const int lenj = __shfl_sync(SGB_FULL, my_len, j);
                 const long long o = __shfl_sync(SGB_FULL, my_o, j) + t;
-                unsigned long long rec = 0ull;
-                if (t < lenj) {
-                    const int nv = __ldg(n + o), xv = __ldg(x + o);
-                    const int cv = (cn_itemsize == 1) ? (int)__ldg((const uint8_t*)cn + o) : __ldg((const int32_t*)cn + o);
-                    if (nv < 0 || xv < 0) bad |= SGB_ERR_NEGATIVE_COUNT;
-                    if (nv >= (1 << SGB_COUNT_BITS) || xv >= (1 << SGB_COUNT_BITS)) bad |= SGB_ERR_COUNT_TOO_LARGE;
-                    if (cv < 0 || cv > 255) bad |= SGB_ERR_BAD_CN;
-                    rec = ((unsigned long long)(unsigned)nv & SGB_COUNT_MASK) |
-                          (((unsigned long long)(unsigned)xv & SGB_COUNT_MASK) << SGB_COUNT_BITS) |
-                          ((unsigned long long)(cv & 255) << 56);
-                }
-                tile[wid][j][lane] = rec;
+                const bool ok = t < lenj;
+                okmask |= ok ? (1u << j) : 0u;
+                nv[j] = ok ? __ldg(n + o) : 0;
+                xv[j] = ok ? __ldg(x + o) : 0;
+                cv[j] = ok ? ((cn_itemsize == 1) ? (int)__ldg((const uint8_t*)cn + o) : __ldg((const int32_t*)cn + o)) : 0;
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+                if (nv[j] < 0 || xv[j] < 0) bad |= SGB_ERR_NEGATIVE_COUNT;
+                if (nv[j] >= (1 << SGB_COUNT_BITS) || xv[j] >= (1 << SGB_COUNT_BITS)) bad |= SGB_ERR_COUNT_TOO_LARGE;
+                if (cv[j] < 0 || cv[j] > 255) bad |= SGB_ERR_BAD_CN;
+                const unsigned long long rec = ((unsigned long long)(unsigned)nv[j] & SGB_COUNT_MASK) |
+                                               (((unsigned long long)(unsigned)xv[j] & SGB_COUNT_MASK) << SGB_COUNT_BITS) |
+                                               ((unsigned long long)(cv[j] & 255) << 56);
+                tile[wid][j][lane] = ((okmask >> j) & 1u) ? rec : 0ull;
             }
             __syncwarp();
             const int nb = (Tpad - t0) < 32 ? (Tpad - t0) : 32;
@@ -165,8 +171,7 @@ __device__ __forceinline__ void sgb_mbar_wait(unsigned long long* bar, unsigned 
 // per-warp shared-memory scratch, in doubles (see the pointer carving in k_decode)
 //   E  [32][P]  emissions of the current bin, lane-major with odd pitch P = SMAX+1 (conflict-free columns)
 //   T1 [32][P]  forward column of every lane's sequence
-//   E2 [32][P]  second density (ASCN binomial only)
-//   bD/bL/bG    per-lane bin fields for the item queue (beta-binomial only)
+//   bD/bL/bG    per-lane bin fields for the item queue ({x, n-x}, log-choose terms, lgamma(s+n))
 //   bI [32]     cprime | in_support << 16
 //   q           work queue, SMAX*32 uint16 entries
 //   stage       2 x SGB_CH x 32 records + 2 mbarriers (TMA staging only)
@@ -174,8 +179,7 @@ static inline size_t decode_warp_doubles(int SMAX, int model, int lik_bb, int st
 {
     const size_t P = (size_t)SMAX + 1;
     size_t d = 2 * 32 * P + 16 + (size_t)SMAX * 8;
-    if (!lik_bb && model == SGB_MODEL_ASCN) d += 32 * P;
-    if (lik_bb) d += 64 + (model == SGB_MODEL_ASCN ? 64 : 32) + 32;
+    d += 64 + (model == SGB_MODEL_ASCN ? 64 : 32) + (lik_bb ? 32 : 0);
     if (stage == SGB_STAGE_TMA) d += 2 * 32 * SGB_CH + 2;
     return (d + 1) & ~(size_t)1;
 }
@@ -208,8 +212,8 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     const int CTS = SGB_CN_TABLE * S;
     constexpr int P = SMAX + 1;
     constexpr int NL = (MODEL == SGB_MODEL_ASCN) ? 64 : 32;
-    constexpr int WD0 = 2 * 32 * P + 16 + SMAX * 8 + ((!LIKBB && MODEL == SGB_MODEL_ASCN) ? 32 * P : 0) +
-                        (LIKBB ? 64 + NL + 32 : 0) + (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_CH + 2 : 0);
+    constexpr int WD0 = 2 * 32 * P + 16 + SMAX * 8 + 64 + NL + (LIKBB ? 32 : 0) +
+                        (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_CH + 2 : 0);
     constexpr int WARP_DOUBLES = (WD0 + 1) & ~1;
     double* sLT = smem;
     double* sET = sLT + SGB_LOGTAB_LEN;
@@ -253,11 +257,9 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     const int wid = threadIdx.x >> 5;
     double* myE = sW + wid * WARP_DOUBLES;                    // E [lane][P]
     double* myT = myE + 32 * P;                               // T1[lane][P]
-    double* myE2 = myT + 32 * P;                              // ASCN binomial: second density [lane][P]
-    double* pq = myE2 + ((!LIKBB && MODEL == SGB_MODEL_ASCN) ? 32 * P : 0);
-    double2* bD = (double2*)pq;                               // beta-binomial: {x, n-x}
-    double* bL = pq + (LIKBB ? 64 : 0);                       //   HSCN lcx[32]; ASCN {lcx, lcy}[32]
-    double* bG = bL + (LIKBB ? NL : 0);                       //   lgamma(s+n)[32]
+    double2* bD = (double2*)(myT + 32 * P);                   // {x, n-x}
+    double* bL = (double*)(bD + 32);                          // HSCN lcx[32]; ASCN {lcx, lcy}[32]
+    double* bG = bL + NL;                                     // beta-binomial: lgamma(s+n)[32]
     int* bI = (int*)(bG + (LIKBB ? 32 : 0));                  // cprime | in_support << 16
     unsigned short* q = (unsigned short*)(bI + 32);
     unsigned long long* stg = (unsigned long long*)(q + SMAX * 32);     // [2][SGB_CH][32] records
@@ -273,7 +275,6 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     const double NEG_INF = -sgb_inf();
     double* colE = myE + lane * P;          // this lane's own columns
     double* colT = myT + lane * P;
-    double* colE2 = myE2 + lane * P;
     unsigned use0 = 0, use1 = 0;            // completed phases of the two stage barriers
 
     for (;;) {
@@ -337,7 +338,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     double fn, fx, fy;
                     if (n < SGB_LF_SMEM) { fn = sLF[n]; fx = sLF[x]; fy = sLF[n - x]; }
                     else if (n < SGB_NLF) { fn = g_lftab[n]; fx = g_lftab[x]; fy = g_lftab[n - x]; }
-                    else { fn = sgb_logfact(n, sLF, sLT); fx = sgb_logfact(x, sLF, sLT); fy = sgb_logfact(n - x, sLF, sLT); }
+                    else { fn = sgb_logfact(n, g_lftab, sLT); fx = sgb_logfact(x, g_lftab, sLT); fy = sgb_logfact(n - x, g_lftab, sLT); }
                     lcx = sgb_sub(sgb_sub(fn, fx), fy);
                     if (MODEL == SGB_MODEL_ASCN) lcy = sgb_sub(sgb_sub(fn, fy), fx);
                     if (LIKBB) lgs = sgb_lgamma_pos(sgb_add(sp.bb_s, (double)n), sLT);
@@ -349,36 +350,15 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 Lprev = L;
             }
             const int Lw = __reduce_max_sync(SGB_FULL, L);
-            // ---- (2) what has to go through the queue
+            // ---- (2) queue of live (lane, state) pairs: lane | lean << 5 | state << 6 | cprime << 11
             unsigned need = 0;          // bit m: state m of this lane's bin is queued
-            if (LIKBB) {
-                if (act) {
-                    bD[lane] = make_double2(kd, nkd);
-                    if (MODEL == SGB_MODEL_ASCN) ((double2*)bL)[lane] = make_double2(lcx, lcy);
-                    else bL[lane] = lcx;
-                    bG[lane] = lgs;
-                    bI[lane] = cprime | (ins << 16);
-                    need = (1u << L) - 1u;
-                }
-            } else {
-                // binomial: densities by the owner lane; the exact eps-floor shortcut settles most wrong states here
-                for (int m = 0; m < Lw; m++) {
-                    if (m < L) {
-                        if ((fastmask >> m) & 1) {
-                            const int ti = cprime * S + m;
-                            double l1, l2, out;
-                            if (sgb_binom_stage<MODEL>(kd, nkd, lcx, lcy, sLP[ti], sLQ[ti], sp, l1, l2, out)) {
-                                colE[m] = l1;
-                                if (MODEL == SGB_MODEL_ASCN) colE2[m] = l2;
-                                need |= 1u << m;
-                            } else {
-                                colE[m] = out;
-                            }
-                        } else {
-                            colE[m] = sgb_emit_item_slow<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, m, TB, sp);
-                        }
-                    }
-                }
+            if (act) {
+                bD[lane] = make_double2(kd, nkd);
+                if (MODEL == SGB_MODEL_ASCN) ((double2*)bL)[lane] = make_double2(lcx, lcy);
+                else bL[lane] = lcx;
+                if (LIKBB) bG[lane] = lgs;
+                bI[lane] = cprime | (ins << 16);
+                need = (1u << L) - 1u;
             }
             int cnt = __popc(need);
             int incl = cnt;
@@ -390,14 +370,11 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
             const int tot = __shfl_sync(SGB_FULL, incl, 31);
             {
                 int qpos = incl - cnt;
-                unsigned rem = need;
-                const int allfast = LIKBB ? (((fastmask & need) == need) ? 32 : 0) : 0;
+                const int allfast = ((fastmask & need) == need) ? 32 : 0;
                 const int ebase = lane | allfast | (((cprime < SGB_CN_TABLE) ? cprime : 0) << 11);
-                while (rem) {
-                    const int m = __ffs((int)rem) - 1;
-                    rem &= rem - 1;
-                    q[qpos++] = (unsigned short)(ebase | (m << 6));
-                }
+#pragma unroll
+                for (int m = 0; m < SMAX; m++)
+                    if (m < L) q[qpos + m] = (unsigned short)(ebase + (m << 6));
             }
             __syncwarp();
             // ---- (3) the queue, two entries per lane per round
@@ -407,14 +384,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 const int en0 = q[v0 ? j0 : 0], en1 = q[v1 ? j1 : (v0 ? j0 : 0)];
                 const int ol0 = en0 & 31, m0 = (en0 >> 6) & 31, ol1 = en1 & 31, mm1 = (en1 >> 6) & 31;
                 double r0, r1;
-                if (!LIKBB) {
-                    const double a0 = myE[ol0 * P + m0], a1 = myE[ol1 * P + mm1];
-                    const double b0 = (MODEL == SGB_MODEL_ASCN) ? myE2[ol0 * P + m0] : 0.0;
-                    const double b1 = (MODEL == SGB_MODEL_ASCN) ? myE2[ol1 * P + mm1] : 0.0;
-                    if (MODEL == SGB_MODEL_ASCN) __syncwarp();      // (reads of a round precede its writes: entries are distinct)
-                    r0 = sgb_binom_finish<MODEL>(a0, b0, sp, sLT, sET);
-                    r1 = sgb_binom_finish<MODEL>(a1, b1, sp, sLT, sET);
-                } else {
+                {
                     const int t0 = (en0 >> 11) * S + m0, t1 = (en1 >> 11) * S + mm1;
                     const double2 d0 = bD[ol0], d1 = bD[ol1];
                     double lx0, ly0 = 0.0, lx1, ly1 = 0.0;
@@ -424,11 +394,12 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     } else {
                         lx0 = bL[ol0]; lx1 = bL[ol1];
                     }
-                    const double gs0 = bG[ol0], gs1 = bG[ol1];
+                    const double gs0 = LIKBB ? bG[ol0] : 0.0, gs1 = LIKBB ? bG[ol1] : 0.0;
                     if (en0 & en1 & 32) {
-                        sgb_emission_fast2<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], sA[t0], sB[t0], sL0[t0],
-                                                         d1.x, d1.y, lx1, ly1, gs1, sLP[t1], sLQ[t1], sA[t1], sB[t1], sL0[t1],
-                                                         sp, sLT, sET, r0, r1);
+                        sgb_emission_fast2<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
+                                                         LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, d1.x, d1.y, lx1, ly1, gs1,
+                                                         sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0, LIKBB ? sB[t1] : 0.0,
+                                                         LIKBB ? sL0[t1] : 0.0, sp, sLT, sET, r0, r1);
                     } else {
                         const int bi0 = bI[ol0], bi1 = bI[ol1];
                         r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);

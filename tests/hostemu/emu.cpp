@@ -40,21 +40,8 @@ static void run(int S, int decode, double loherror, double eps, double rho, doub
         auto lean = [&](int m) {
             return b.cprime < SGB_CN_TABLE && b.in_support && sp.fast_ok && tK[b.cprime * S + m] == SGB_KIND_NORMAL;
         };
-        if (!LIKBB) {
-            // binomial kernels: owner-lane density stage (with the exact eps-floor shortcut), then the finish stage
-            for (int i = 0; i < L; i++) {
-                if (lean(i)) {
-                    const int ti = b.cprime * S + i;
-                    double l1, l2, out;
-                    if (sgb_binom_stage<MODEL>(b.kd, b.nkd, b.lc_x, b.lc_y, tLP[ti], tLQ[ti], sp, l1, l2, out))
-                        out = sgb_binom_finish<MODEL>(l1, l2, sp, LT, ET);
-                    e[i] = out;
-                } else {
-                    e[i] = sgb_emit_item_slow<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, i, TB, sp);
-                }
-            }
-        } else {
-            // beta-binomial kernels: pairs of lean items go through the two-wide function, the rest one by one
+        {
+            // like the kernel: pairs of lean items go through the two-wide function, the rest one by one
             for (int i = 0; i < L; i += 2) {
                 const int j = (i + 1 < L) ? i + 1 : i;
                 if (lean(i) && lean(j)) {
@@ -119,26 +106,3 @@ extern "C" int emu_decode_sequence(int model, int lik, int S, int decode, double
     return 0;
 }
 
-// Exactness of the eps-floor shortcut (SgbScalars::lsa_skip): for every l below the threshold the full
-// logspace_add(l, log eps) must return log eps bit-for-bit.  Returns the number of violations.
-extern "C" long emu_lsa_skip_violations(double eps, long n_samples, double* skip_out)
-{
-    SgbScalars sp = sgb_scalars(12, eps, 0.0, 0.95, 0.0, LT);
-    if (skip_out) *skip_out = sp.lsa_skip;
-    if (!(sp.lsa_skip > -sgb_inf())) return 0;
-    long bad = 0;
-    unsigned long long st = 88172645463325252ull;
-    for (long i = 0; i < n_samples; i++) {
-        st ^= st << 13; st ^= st >> 7; st ^= st << 17;
-        double u = (double)(st >> 11) * 0x1p-53;
-        // dense just below the threshold, sparse far below it
-        double l = (i & 1) ? sp.lsa_skip - u * 2.0 - 1e-300 : sp.lsa_skip - u * 800.0 - 1e-300;
-        if (!(l < sp.lsa_skip)) continue;
-        double r = sgb_logspace_add(l, sp.log_eps, LT, ET);
-        if (sgb_d2u(r) != sgb_d2u(sp.log_eps)) bad++;
-    }
-    // the largest double below the threshold, too
-    double l = sgb_u2d(sgb_d2u(sp.lsa_skip) + 1);      // lsa_skip is negative: +1 ulp in magnitude = next below
-    if (sgb_d2u(sgb_logspace_add(l, sp.log_eps, LT, ET)) != sgb_d2u(sp.log_eps)) bad++;
-    return bad;
-}
