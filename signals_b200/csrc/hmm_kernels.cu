@@ -455,20 +455,45 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     }
 }
 
+// resident CTAs per SM of one instantiation (0 if it does not fit in shared memory at all)
+template <int SMAX, int MODEL, int LIKBB, int CHAINED, int STAGE>
+static int decode_occupancy(int S)
+{
+    static int cached_S[2] = {-1, -1}, cached_occ[2] = {0, 0};      // per instantiation; the answer depends on S only
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const int slot = dev & 1;
+    if (cached_S[slot] == S + 1000 * dev) return cached_occ[slot];
+    size_t smem = decode_smem_bytes(SMAX, S, MODEL, LIKBB, STAGE);
+    auto kern = k_decode<SMAX, MODEL, LIKBB, CHAINED, STAGE>;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, SGB_DECODE_THREADS, smem) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    cached_occ[slot] = occ;
+    cached_S[slot] = S + 1000 * dev;
+    return occ;
+}
+
 template <int SMAX, int MODEL, int LIKBB, int CHAINED, int STAGE>
 static cudaError_t launch_decode(const SgbDecodeArgs& A, int sm_count, cudaStream_t st)
 {
+    int occ = decode_occupancy<SMAX, MODEL, LIKBB, CHAINED, STAGE>(A.S);
+    if (STAGE == SGB_STAGE_TMA) {
+        // the staging buffers cost shared memory: if they would lower the number of resident CTAs, stream the
+        // records with plain coalesced loads instead (same arithmetic, same results)
+        int occ_ldg = decode_occupancy<SMAX, MODEL, LIKBB, CHAINED, SGB_STAGE_LDG>(A.S);
+        if (occ_ldg > occ) return launch_decode<SMAX, MODEL, LIKBB, CHAINED, SGB_STAGE_LDG>(A, sm_count, st);
+    }
+    if (occ < 1) return cudaErrorInvalidConfiguration;
     size_t smem = decode_smem_bytes(SMAX, A.S, MODEL, LIKBB, STAGE);
     auto kern = k_decode<SMAX, MODEL, LIKBB, CHAINED, STAGE>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) {
-        cudaGetLastError();
-        if (STAGE == SGB_STAGE_TMA) return launch_decode<SMAX, MODEL, LIKBB, CHAINED, SGB_STAGE_LDG>(A, sm_count, st);
-        return e;
-    }
     int blocks = (A.plan.ngroups + SGB_DECODE_WARPS - 1) / SGB_DECODE_WARPS;
-    int occ = 1;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, SGB_DECODE_THREADS, smem) != cudaSuccess || occ < 1) occ = 1;
     int cap = sm_count * occ;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;

@@ -23,7 +23,7 @@ struct SgbDevTables {
 // record (bin t, lane l) at goff[g] + t*32 + l  (bin-major, lanes interleaved: a warp reads 256
 // contiguous bytes per bin and one 1-D bulk copy moves SGB_CH bins of all 32 sequences).
 #ifndef SGB_CH
-#define SGB_CH 8               // bins per staged chunk
+#define SGB_CH 4               // bins per staged chunk
 #endif
 struct SgbPlanDev {
     const long long* goff;     // [ngroups] first record of the group's tile in the packed buffer
