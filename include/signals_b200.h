@@ -116,6 +116,18 @@ SGB_API int64_t sgb_plan_scratch_bytes(const sgb_plan* plan);
 SGB_API int sgb_viterbi(const double* emission, int64_t nrow_e, const double* transition, const int32_t* observations,
                 int64_t T, int32_t S, int32_t init_mode, int32_t decode, int32_t* path_out);
 
+/* Chained-decode viterbi for callers that must not allocate device memory (host callbacks, fixed-arena
+ * services, latency-critical loops -- see signals_b200/csrc/noalloc.cu).  This entry point has no counterpart
+ * in the reference.  Same arithmetic as sgb_viterbi(..., decode = SGB_DECODE_CHAINED) but every pointer is a
+ * DEVICE pointer on the current device, the work is only enqueued on `stream`, and the uint8 backpointers live in
+ * a 4 MiB array built into the library instead of a library-allocated buffer: T * S must not exceed 4,194,304
+ * (larger problems return an error).  It calls no cudaMalloc / cudaFree.  The first call on a device resolves the
+ * array's address: make it before any stream capture.  Calls that overlap on one GPU race on the shared array.
+ * Observations must already be valid 1-based row indices (they cannot be checked on the host). */
+SGB_API int sgb_viterbi_chained_noalloc(const double* d_emission, int64_t nrow_e, const double* d_transition,
+                                        const int32_t* d_observations, int64_t T, int32_t S, int32_t init_mode,
+                                        int32_t* d_path_out, void* stream);
+
 /* logspace_addcpp(logx, logy)  src/code.cpp:5-8, R/RcppExports.R:4-6 ; and its vectorised R twin
  * logspace_add (R/callASCN.R:9-11).  Evaluated on the device with the same deterministic math as the
  * emission kernel (a scalar call is a 1-element launch). */

@@ -44,6 +44,7 @@ SIGNATURES = {
     "sgb_plan_enable_timing": (ctypes.c_int, [_vp, _i32]),
     "sgb_plan_read_timing": (ctypes.c_int, [_vp, _i32, _vp, _vp, ctypes.POINTER(_i32)]),
     "sgb_viterbi": (ctypes.c_int, [_vp, _i64, _vp, _vp, _i64, _i32, _i32, _i32, _vp]),
+    "sgb_viterbi_chained_noalloc": (ctypes.c_int, [_vp, _i64, _vp, _vp, _i64, _i32, _i32, _vp, _vp]),
     "sgb_logspace_add": (ctypes.c_int, [_dbl, _dbl, ctypes.POINTER(_dbl)]),
     "sgb_logspace_add_vec": (ctypes.c_int, [_vp, _vp, _i64, _vp]),
     "sgb_postprocess": (ctypes.c_int, [_i64, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libsignals_b200.so")
-SOURCES = ["hmm_kernels.cu", "capi.cu"]
+SOURCES = ["hmm_kernels.cu", "capi.cu", "noalloc.cu"]
 HEADERS = ["sgb_math.h", "sgb_tables.h", "hmm_core.cuh", "kernels.h", os.path.join("..", "..", "include", "signals_b200.h")]
 
 NVCC_FLAGS = [

@@ -15,9 +15,9 @@
 #include <thread>
 #include <vector>
 
-namespace {
-
 thread_local std::string t_err;
+
+namespace {
 
 int fail(const std::string& msg)
 {
@@ -323,6 +323,8 @@ int check_batch_args(int64_t N, const int32_t* n, const int32_t* x, const void* 
 }
 
 }  // namespace
+
+void sgb_internal_set_error(const char* msg) { t_err = msg ? msg : ""; }
 
 // ====================================================================== C ABI
 extern "C" {
