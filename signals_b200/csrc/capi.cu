@@ -59,6 +59,32 @@ struct DevBuf {
     }
 };
 
+// grow-only pinned host buffer: plan arrays are uploaded from page-locked memory so that the copies are truly
+// asynchronous (a cudaMemcpyAsync from pageable memory first synchronises the stream with the host, which
+// would stall the chunk pipeline once per chunk)
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes)
+    {
+        if (bytes <= cap) return 0;
+        if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 4 + 4096;
+        cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocDefault);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            return fail(std::string("cudaHostAlloc of ") + std::to_string(want) + " bytes failed: " + cudaGetErrorString(e));
+        }
+        cap = want;
+        return 0;
+    }
+    void release()
+    {
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+    }
+};
+
 // host-side description of a batch of sequences, sorted by length (longest first)
 struct HostPlan {
     std::vector<long long> goff, ostart;       // goff: per group of 32 sequences, ostart: per sequence
@@ -127,6 +153,7 @@ struct Slot {
     DevBuf n, x, cn, out, packed, bp, last_state, goff, ostart, len, loglik;
     unsigned int* counter = nullptr;
     HostPlan hp;
+    PinBuf pin;                 // page-locked copy of hp's arrays for the upload
     // pending device->host copy bookkeeping is implicit: copies are enqueued on st
 };
 
@@ -218,9 +245,15 @@ int upload_plan(Slot& S, cudaStream_t st, SgbPlanDev& pd)
     if (S.ostart.reserve(ns * sizeof(long long) + 16)) return 1;
     if (S.len.reserve(ns * sizeof(int) + 16)) return 1;
     if (ns) {
-        SGB_CUDA(cudaMemcpyAsync(S.goff.p, hp.goff.data(), ng * sizeof(long long), cudaMemcpyHostToDevice, st));
-        SGB_CUDA(cudaMemcpyAsync(S.ostart.p, hp.ostart.data(), ns * sizeof(long long), cudaMemcpyHostToDevice, st));
-        SGB_CUDA(cudaMemcpyAsync(S.len.p, hp.len.data(), ns * sizeof(int), cudaMemcpyHostToDevice, st));
+        const size_t b_goff = ng * sizeof(long long), b_ost = ns * sizeof(long long), b_len = ns * sizeof(int);
+        if (S.pin.reserve(b_goff + b_ost + b_len)) return 1;
+        char* h = (char*)S.pin.p;
+        memcpy(h, hp.goff.data(), b_goff);
+        memcpy(h + b_goff, hp.ostart.data(), b_ost);
+        memcpy(h + b_goff + b_ost, hp.len.data(), b_len);
+        SGB_CUDA(cudaMemcpyAsync(S.goff.p, h, b_goff, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(S.ostart.p, h + b_goff, b_ost, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(S.len.p, h + b_goff + b_ost, b_len, cudaMemcpyHostToDevice, st));
     }
     pd.goff = (const long long*)S.goff.p;
     pd.ostart = (const long long*)S.ostart.p;
@@ -275,12 +308,12 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
                 (SL.bp.reserve((size_t)rows * S) || SL.last_state.reserve((size_t)SL.hp.nseq * 4 + 16)))
                 return 1;
             if (loglik_out && SL.loglik.reserve((size_t)rows * S * 8)) return 1;
+            SgbPlanDev pd;
+            if (upload_plan(SL, st, pd)) return 1;
             SGB_CUDA(cudaMemcpyAsync(SL.n.p, n + r0, (size_t)rows * 4, cudaMemcpyHostToDevice, st));
             SGB_CUDA(cudaMemcpyAsync(SL.x.p, x + r0, (size_t)rows * 4, cudaMemcpyHostToDevice, st));
             SGB_CUDA(cudaMemcpyAsync(SL.cn.p, (const char*)cn + (size_t)r0 * cn_itemsize, (size_t)rows * cn_itemsize,
                                      cudaMemcpyHostToDevice, st));
-            SgbPlanDev pd;
-            if (upload_plan(SL, st, pd)) return 1;
             SGB_CUDA(cudaStreamWaitEvent(st, C->ev_setup, 0));
             SGB_CUDA(sgbk_pack((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, pd,
                                (unsigned long long*)SL.packed.p, C->d_err, st));
@@ -362,7 +395,7 @@ int sgb_shutdown(void)
             Slot& s = c->slot[i];
             if (s.st) { cudaStreamSynchronize(s.st); cudaStreamDestroy(s.st); }
             s.n.release(); s.x.release(); s.cn.release(); s.out.release(); s.packed.release(); s.bp.release();
-            s.last_state.release(); s.goff.release(); s.ostart.release(); s.len.release(); s.loglik.release();
+            s.last_state.release(); s.pin.release(); s.goff.release(); s.ostart.release(); s.len.release(); s.loglik.release();
             if (s.counter) cudaFree(s.counter);
         }
         c->scratch_a.release(); c->scratch_b.release(); c->scratch_c.release(); c->scratch_d.release();
