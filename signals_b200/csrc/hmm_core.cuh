@@ -461,32 +461,30 @@ SGB_HD void sgb_seq_init_mem(double* T1, int ts, const double* E, int es, int S,
     m1 = best;
 }
 
-// nlive (uniform across the warp): states >= nlive are -Inf both in the previous column and in this bin's
-// emissions, so they are neither loaded, computed nor stored (they stay -Inf in memory).
-template <int SMAX>
-SGB_HD int sgb_seq_step_mem(double* T1, int ts, const double* E, int es, double& m1io, double tr_self, double tr_off,
-                            int nlive)
+// NL (compile time) bounds the states that can be alive: states >= NL are -Inf both in the previous column and
+// in this bin's emissions, so they are neither loaded, computed nor stored (they stay -Inf in memory).
+template <int NL>
+SGB_HD int sgb_seq_step_mem_nl(double* T1, int ts, const double* E, int es, double& m1io, double tr_self, double tr_off)
 {
-    double Tn[SMAX];
+    double Tn[NL];
     const double u1 = sgb_add(m1io, tr_off);
 #pragma unroll
-    for (int i = 0; i < SMAX; i++) {
-        Tn[i] = -sgb_inf();
-        if (i < nlive) {
-            const double e = E[i * es];
-            const double voff = sgb_add(u1, e);
-            const double vdia = sgb_add(sgb_add(T1[i * ts], tr_self), e);
-            Tn[i] = (vdia > voff) ? vdia : voff;
-        }
+    for (int i = 0; i < NL; i++) {
+        const double e = E[i * es];
+        const double voff = sgb_add(u1, e);
+        const double vdia = sgb_add(sgb_add(T1[i * ts], tr_self), e);
+        Tn[i] = (vdia > voff) ? vdia : voff;
     }
-    double tv[SMAX];
-    int ti[SMAX];
+    // first maximum by a tournament: the left operand always holds the lower indices, so a strict '>' keeps
+    // the lowest index on ties (what which_max does)
+    double tv[NL];
+    int ti[NL];
 #pragma unroll
-    for (int i = 0; i < SMAX; i++) { tv[i] = Tn[i]; ti[i] = i; }
+    for (int i = 0; i < NL; i++) { tv[i] = Tn[i]; ti[i] = i; }
 #pragma unroll
-    for (int stride = 1; stride < SMAX; stride *= 2) {
+    for (int stride = 1; stride < NL; stride *= 2) {
 #pragma unroll
-        for (int i = 0; i + stride < SMAX; i += 2 * stride) {
+        for (int i = 0; i + stride < NL; i += 2 * stride) {
             const bool gt = tv[i + stride] > tv[i];
             tv[i] = gt ? tv[i + stride] : tv[i];
             ti[i] = gt ? ti[i + stride] : ti[i];
@@ -497,23 +495,44 @@ SGB_HD int sgb_seq_step_mem(double* T1, int ts, const double* E, int es, double&
     int back = i1;
     const double ej = E[i1 * es];
     if (m1 == sgb_add(u1, ej)) {
+        // The winner's value equals its off-diagonal candidate (its diagonal one is not strictly larger), so a
+        // predecessor other than i1 may hold the first maximum: find the first k with
+        // (T1[k] + tr[k,i1]) + e[i1] == m1 -- the reference's own expression (src/code.cpp:29-31).
+        // (everything -Inf: every predecessor "matches" and the first one is state 0, as in the full scan)
         unsigned int pm = 0;
 #pragma unroll
-        for (int k = 0; k < SMAX; k++) {
-            if (k < nlive) {
-                const double val = sgb_add(sgb_add(T1[k * ts], tr_off), ej);
-                pm |= (val == m1) ? (1u << k) : 0u;
-            }
+        for (int k = 0; k < NL; k++) {
+            const double val = sgb_add(sgb_add(T1[k * ts], tr_off), ej);
+            pm |= (val == m1) ? (1u << k) : 0u;
         }
         const double wd = sgb_add(sgb_add(T1[i1 * ts], tr_self), ej);
         pm = (pm & ~(1u << i1)) | ((wd == m1) ? (1u << i1) : 0u);
-        // everything -Inf: every predecessor "matches"; the first one is state 0 (as in the full scan)
         back = sgb_ffs32(pm) - 1;
     }
 #pragma unroll
-    for (int i = 0; i < SMAX; i++) if (i < nlive) T1[i * ts] = Tn[i];
+    for (int i = 0; i < NL; i++) T1[i * ts] = Tn[i];
     m1io = m1;
     return back;
+}
+
+// run-time nlive (uniform across a warp) -> the smallest compiled bound that covers it
+template <int SMAX>
+SGB_HD int sgb_seq_step_mem(double* T1, int ts, const double* E, int es, double& m1io, double tr_self, double tr_off,
+                            int nlive)
+{
+    if (SMAX <= 12) {
+        if (nlive <= 2) return sgb_seq_step_mem_nl<(SMAX < 2 ? SMAX : 2)>(T1, ts, E, es, m1io, tr_self, tr_off);
+        if (nlive <= 4) return sgb_seq_step_mem_nl<(SMAX < 4 ? SMAX : 4)>(T1, ts, E, es, m1io, tr_self, tr_off);
+        if (nlive <= 6) return sgb_seq_step_mem_nl<(SMAX < 6 ? SMAX : 6)>(T1, ts, E, es, m1io, tr_self, tr_off);
+        if (nlive <= 8) return sgb_seq_step_mem_nl<(SMAX < 8 ? SMAX : 8)>(T1, ts, E, es, m1io, tr_self, tr_off);
+        if (nlive <= 10) return sgb_seq_step_mem_nl<(SMAX < 10 ? SMAX : 10)>(T1, ts, E, es, m1io, tr_self, tr_off);
+        return sgb_seq_step_mem_nl<SMAX>(T1, ts, E, es, m1io, tr_self, tr_off);
+    } else {
+        if (nlive <= 8) return sgb_seq_step_mem_nl<8>(T1, ts, E, es, m1io, tr_self, tr_off);
+        if (nlive <= 16) return sgb_seq_step_mem_nl<(SMAX < 16 ? SMAX : 16)>(T1, ts, E, es, m1io, tr_self, tr_off);
+        if (nlive <= 24) return sgb_seq_step_mem_nl<(SMAX < 24 ? SMAX : 24)>(T1, ts, E, es, m1io, tr_self, tr_off);
+        return sgb_seq_step_mem_nl<SMAX>(T1, ts, E, es, m1io, tr_self, tr_off);
+    }
 }
 
 // Chained (textbook) mode: backpointers of ALL states for bin j, bp[i] = first argmax_k.
