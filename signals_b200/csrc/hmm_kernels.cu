@@ -377,14 +377,14 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     if (m < L) q[qpos + m] = (unsigned short)(ebase + (m << 6));
             }
             __syncwarp();
-            // ---- (3) the queue, two entries per lane per round
-            for (int base = 0; base < tot; base += 64) {
-                const int j0 = base + lane, j1 = j0 + 32;
-                const bool v0 = j0 < tot, v1 = j1 < tot;
-                const int en0 = q[v0 ? j0 : 0], en1 = q[v1 ? j1 : (v0 ? j0 : 0)];
-                const int ol0 = en0 & 31, m0 = (en0 >> 6) & 31, ol1 = en1 & 31, mm1 = (en1 >> 6) & 31;
-                double r0, r1;
-                {
+            // ---- (3) the queue: two entries per lane per round while more than 32 remain, else one
+            for (int base = 0; base < tot;) {
+                const int remaining = tot - base;
+                if (remaining > 32) {
+                    const int j0 = base + lane, j1 = j0 + 32;
+                    const bool v1 = j1 < tot;
+                    const int en0 = q[j0], en1 = q[v1 ? j1 : j0];
+                    const int ol0 = en0 & 31, m0 = (en0 >> 6) & 31, ol1 = en1 & 31, mm1 = (en1 >> 6) & 31;
                     const int t0 = (en0 >> 11) * S + m0, t1 = (en1 >> 11) * S + mm1;
                     const double2 d0 = bD[ol0], d1 = bD[ol1];
                     double lx0, ly0 = 0.0, lx1, ly1 = 0.0;
@@ -395,6 +395,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                         lx0 = bL[ol0]; lx1 = bL[ol1];
                     }
                     const double gs0 = LIKBB ? bG[ol0] : 0.0, gs1 = LIKBB ? bG[ol1] : 0.0;
+                    double r0, r1;
                     if (en0 & en1 & 32) {
                         sgb_emission_fast2<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
                                                          LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, d1.x, d1.y, lx1, ly1, gs1,
@@ -405,9 +406,34 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                         r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
                         r1 = v1 ? sgb_emit_item<MODEL, LIKBB>(bi1 & 0xffff, bi1 >> 16, d1.x, d1.y, lx1, ly1, gs1, mm1, TB, sp) : 0.0;
                     }
+                    myE[ol0 * P + m0] = r0;
+                    if (v1) myE[ol1 * P + mm1] = r1;
+                    base += 64;
+                } else {
+                    const bool v0 = lane < remaining;
+                    const int en0 = q[v0 ? base + lane : base];
+                    const int ol0 = en0 & 31, m0 = (en0 >> 6) & 31;
+                    const int t0 = (en0 >> 11) * S + m0;
+                    const double2 d0 = bD[ol0];
+                    double lx0, ly0 = 0.0;
+                    if (MODEL == SGB_MODEL_ASCN) {
+                        const double2 c0 = ((const double2*)bL)[ol0];
+                        lx0 = c0.x; ly0 = c0.y;
+                    } else {
+                        lx0 = bL[ol0];
+                    }
+                    const double gs0 = LIKBB ? bG[ol0] : 0.0;
+                    double r0;
+                    if (en0 & 32) {
+                        r0 = sgb_emission_fast<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
+                                                             LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, sp, sLT, sET);
+                    } else {
+                        const int bi0 = bI[ol0];
+                        r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
+                    }
+                    if (v0) myE[ol0 * P + m0] = r0;
+                    base += 32;
                 }
-                if (v0) myE[ol0 * P + m0] = r0;
-                if (v1) myE[ol1 * P + mm1] = r1;
             }
             __syncwarp();
             // ---- (4) forward recursion + decode of this lane's sequence (T1 column lives in shared memory)

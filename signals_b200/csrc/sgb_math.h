@@ -20,7 +20,7 @@
 //   sgb_log       <= 1 ulp            all positive normals (near-1 branch is fdlibm-style)
 //   sgb_log_tab   <= 2e-16 absolute near 1, <= 1.5 ulp elsewhere
 //   sgb_log1p_01  <= 1.5 ulp          on [0, 1]
-//   sgb_lgamma    <= 4e-16*max(1,|lgamma|) + 3e-15 absolute,  z > 0
+//   sgb_lgamma    <= 6e-16*|lgamma| + 2e-14 absolute,  z > 0
 #pragma once
 #include <stdint.h>
 #include <string.h>
@@ -287,40 +287,50 @@ SGB_HD double sgb_logspace_add(double a, double b, const double* __restrict__ LT
 // z < 10 is shifted up with the recurrence (P = z(z+1)...(z+k-1)), then
 // Stirling with 7 correction terms; 1/y by two cubic Newton steps from the
 // table seed (no division instruction on the hot path).
-// core: finite z > 0, no special-value handling
+// core: finite z > 0, no special-value handling.  Branch-free on purpose (several calls sit in one basic
+// block of the emission kernel and are interleaved by the scheduler): arguments below 10 are shifted up by
+// exactly 10 with the recurrence lgamma(z) = lgamma(z+10) - log(z (z+1) ... (z+9)); larger ones use P = 1,
+// whose logarithm the table kernel returns as an exact 0.
 SGB_HD double sgb_lgamma_pos(double z, const double* __restrict__ LT)
 {
-    double P = 1.0, y = z;
-    int k = 0;
-    while (y < 10.0) {
-        P = sgb_mul(P, y);
-        ++k;
-        y = sgb_add(z, (double)k);
-    }
+    const int sm = z < 10.0;
+    double P = z;
+    P = sgb_mul(P, sgb_add(z, 1.0));
+    P = sgb_mul(P, sgb_add(z, 2.0));
+    P = sgb_mul(P, sgb_add(z, 3.0));
+    P = sgb_mul(P, sgb_add(z, 4.0));
+    P = sgb_mul(P, sgb_add(z, 5.0));
+    P = sgb_mul(P, sgb_add(z, 6.0));
+    P = sgb_mul(P, sgb_add(z, 7.0));
+    P = sgb_mul(P, sgb_add(z, 8.0));
+    P = sgb_mul(P, sgb_add(z, 9.0));
+    P = sm ? P : 1.0;
+    const double sh = sm ? 10.0 : 0.0;
+    const double y = sgb_add(z, sh);
     double seed;
-    double ly = sgb_log_core(sgb_d2u(y), 0, LT, &seed);
-    double corr = 0.0;
-    if (y < 0x1p500) {
-        double e = sgb_fma(-y, seed, 1.0);
-        double t = sgb_fma(e, e, e);
-        double rr = sgb_fma(seed, t, seed);
-        e = sgb_fma(-y, rr, 1.0);
-        t = sgb_fma(e, e, e);
-        rr = sgb_fma(rr, t, rr);
-        double r2 = sgb_mul(rr, rr);
-        double r4 = sgb_mul(r2, r2);
-        double c01 = sgb_fma(r2, SGB_C(STIR2), SGB_C(STIR1));
-        double c23 = sgb_fma(r2, SGB_C(STIR4), SGB_C(STIR3));
-        double c45 = sgb_fma(r2, SGB_C(STIR6), SGB_C(STIR5));
-        double c = sgb_fma(r4, sgb_fma(r4, sgb_fma(r4, SGB_C(STIR7), c45), c23), c01);
-        corr = sgb_mul(rr, c);
-        // y = fl(z+k): fold the rounding residual back in with lgamma'(y) ~ log y - 1/(2y)
-        double dy = sgb_sub(z, sgb_sub(y, (double)k));
-        corr = sgb_fma(dy, sgb_fma(-0.5, rr, ly), corr);
-    }
-    double res = sgb_add(sgb_fma(sgb_sub(y, 0.5), ly, -y), sgb_add(SGB_C(HALF_LN_2PI), corr));
-    if (k > 0) res = sgb_sub(res, sgb_log_tab(P, LT));
-    return res;
+    const double ly = sgb_log_core(sgb_d2u(y), 0, LT, &seed);
+    const double lP = sgb_log_core(sgb_d2u(P), 0, LT, 0);
+    // 1/y by two cubic Newton steps from the 8-bit table seed (for y beyond 2^500 the series vanishes anyway:
+    // the seed's exponent arithmetic is then meaningless but every term below is multiplied by rr ~ 0 or NaN-free)
+    double e = sgb_fma(-y, seed, 1.0);
+    double t = sgb_fma(e, e, e);
+    double rr = sgb_fma(seed, t, seed);
+    e = sgb_fma(-y, rr, 1.0);
+    t = sgb_fma(e, e, e);
+    rr = sgb_fma(rr, t, rr);
+    rr = (y < 0x1p500) ? rr : 0.0;
+    const double r2 = sgb_mul(rr, rr);
+    const double r4 = sgb_mul(r2, r2);
+    const double c01 = sgb_fma(r2, SGB_C(STIR2), SGB_C(STIR1));
+    const double c23 = sgb_fma(r2, SGB_C(STIR4), SGB_C(STIR3));
+    const double c45 = sgb_fma(r2, SGB_C(STIR6), SGB_C(STIR5));
+    const double c = sgb_fma(r4, sgb_fma(r4, sgb_fma(r4, SGB_C(STIR7), c45), c23), c01);
+    double corr = sgb_mul(rr, c);
+    // y = fl(z + shift): fold the rounding residual back in with lgamma'(y) ~ log y - 1/(2y)
+    const double dy = sgb_sub(z, sgb_sub(y, sh));
+    corr = sgb_fma(dy, sgb_fma(-0.5, rr, ly), corr);
+    const double res = sgb_add(sgb_fma(sgb_sub(y, 0.5), ly, -y), sgb_add(SGB_C(HALF_LN_2PI), corr));
+    return sgb_sub(res, lP);
 }
 
 SGB_HD double sgb_lgamma(double z, const double* __restrict__ LT)
