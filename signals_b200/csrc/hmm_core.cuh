@@ -24,6 +24,7 @@
 #define SGB_MAX_STATES 32      // S = maxCN+1 supported by the fused kernels
 #define SGB_CN_TABLE 16        // total-CN values 0..15 have their per-state constants tabulated
 #define SGB_COUNT_BITS 28      // read counts must be < 2^28 (packed record n:28 | x:28 | cn:8)
+#define SGB_LGK 10             // beta-binomial: lgamma(shape + k) is tabulated per (total CN, state) for k < SGB_LGK
 
 // kind of a (total CN, state) pair
 #define SGB_KIND_NORMAL 0      // 0 < p < 1, use the density formula
@@ -170,19 +171,31 @@ SGB_HD double sgb_emission(int model, int lik_bb, const SgbBin& b, int m, const 
     return l;
 }
 
+// lgamma(shape + k) on the lean beta-binomial path.  Counts below SGB_LGK come from the per-call table (a cache
+// of sgb_lgamma_pos(shape + k), filled by the same function); larger ones have shape + k >= 10, where the
+// Stirling part alone gives the same bits.  Branch-free: both are evaluated and one is selected.
+SGB_HD double sgb_lg_shape(double shape, double kd, const double* __restrict__ lgk, const double* __restrict__ LT)
+{
+    const int small = kd < (double)SGB_LGK;
+    const double zs = small ? 16.0 : sgb_add(shape, kd);         // any harmless argument for the discarded lane
+    const double st = sgb_lgamma_ge10(zs, LT);
+    const double tb = lgk[small ? (int)kd : 0];
+    return small ? tb : st;
+}
+
 // Lean emission for the common case: tabulated total CN, 0 < p < 1 (kind NORMAL), 0 <= x <= n, no Abias,
 // finite log(eps).  Same operations in the same order as sgb_density / sgb_emission, minus the branches
 // that cannot be taken under these conditions -- so the bits are identical (tests/test_hostemu.py).
 template <int MODEL, int LIKBB>
 SGB_HD double sgb_emission_fast(double kd, double nkd, double lc_x, double lc_y, double lg_sn, double lp, double lq,
-                                double a, double b, double l0, const SgbScalars& sp,
+                                double a, double b, double l0, const double* __restrict__ lgk, const SgbScalars& sp,
                                 const double* __restrict__ LT, const double* __restrict__ ET)
 {
     double l;
     if (!LIKBB) {
         l = sgb_fma(nkd, lq, sgb_fma(kd, lp, lc_x));
     } else {
-        double t1 = sgb_add(sgb_lgamma_pos(sgb_add(a, kd), LT), sgb_lgamma_pos(sgb_add(b, nkd), LT));
+        double t1 = sgb_add(sgb_lg_shape(a, kd, lgk, LT), sgb_lg_shape(b, nkd, lgk + SGB_LGK, LT));
         t1 = sgb_sub(t1, lg_sn);
         l = sgb_add(lc_x, sgb_sub(t1, l0));
     }
@@ -191,7 +204,7 @@ SGB_HD double sgb_emission_fast(double kd, double nkd, double lc_x, double lc_y,
         if (!LIKBB) {
             l2 = sgb_fma(kd, lq, sgb_fma(nkd, lp, lc_y));
         } else {
-            double t1 = sgb_add(sgb_lgamma_pos(sgb_add(a, nkd), LT), sgb_lgamma_pos(sgb_add(b, kd), LT));
+            double t1 = sgb_add(sgb_lg_shape(a, nkd, lgk, LT), sgb_lg_shape(b, kd, lgk + SGB_LGK, LT));
             t1 = sgb_sub(t1, lg_sn);
             l2 = sgb_add(lc_y, sgb_sub(t1, l0));
         }
@@ -207,7 +220,7 @@ template <int MODEL, int LIKBB>
 SGB_HD void sgb_emission_fast2(double kd0, double nk0, double lx0, double ly0, double gs0, double lp0, double lq0,
                                double a0, double b0, double z0, double kd1, double nk1, double lx1, double ly1,
                                double gs1, double lp1, double lq1, double a1, double b1, double z1,
-                               const SgbScalars& sp, const double* __restrict__ LT, const double* __restrict__ ET,
+                               const double* __restrict__ g0, const double* __restrict__ g1, const SgbScalars& sp, const double* __restrict__ LT, const double* __restrict__ ET,
                                double& r0, double& r1)
 {
     double l0, l1;
@@ -215,8 +228,8 @@ SGB_HD void sgb_emission_fast2(double kd0, double nk0, double lx0, double ly0, d
         l0 = sgb_fma(nk0, lq0, sgb_fma(kd0, lp0, lx0));
         l1 = sgb_fma(nk1, lq1, sgb_fma(kd1, lp1, lx1));
     } else {
-        double t0 = sgb_add(sgb_lgamma_pos(sgb_add(a0, kd0), LT), sgb_lgamma_pos(sgb_add(b0, nk0), LT));
-        double t1 = sgb_add(sgb_lgamma_pos(sgb_add(a1, kd1), LT), sgb_lgamma_pos(sgb_add(b1, nk1), LT));
+        double t0 = sgb_add(sgb_lg_shape(a0, kd0, g0, LT), sgb_lg_shape(b0, nk0, g0 + SGB_LGK, LT));
+        double t1 = sgb_add(sgb_lg_shape(a1, kd1, g1, LT), sgb_lg_shape(b1, nk1, g1 + SGB_LGK, LT));
         l0 = sgb_add(lx0, sgb_sub(sgb_sub(t0, gs0), z0));
         l1 = sgb_add(lx1, sgb_sub(sgb_sub(t1, gs1), z1));
     }
@@ -226,8 +239,8 @@ SGB_HD void sgb_emission_fast2(double kd0, double nk0, double lx0, double ly0, d
             m0 = sgb_fma(kd0, lq0, sgb_fma(nk0, lp0, ly0));
             m1 = sgb_fma(kd1, lq1, sgb_fma(nk1, lp1, ly1));
         } else {
-            double t0 = sgb_add(sgb_lgamma_pos(sgb_add(a0, nk0), LT), sgb_lgamma_pos(sgb_add(b0, kd0), LT));
-            double t1 = sgb_add(sgb_lgamma_pos(sgb_add(a1, nk1), LT), sgb_lgamma_pos(sgb_add(b1, kd1), LT));
+            double t0 = sgb_add(sgb_lg_shape(a0, nk0, g0, LT), sgb_lg_shape(b0, kd0, g0 + SGB_LGK, LT));
+            double t1 = sgb_add(sgb_lg_shape(a1, nk1, g1, LT), sgb_lg_shape(b1, kd1, g1 + SGB_LGK, LT));
             m0 = sgb_add(ly0, sgb_sub(sgb_sub(t0, gs0), z0));
             m1 = sgb_add(ly1, sgb_sub(sgb_sub(t1, gs1), z1));
         }
@@ -253,6 +266,7 @@ SGB_HD void sgb_emission_fast2(double kd0, double nk0, double lx0, double ly0, d
 // untabulated path needs to recompute an entry on the fly.
 struct SgbTables {
     const double *LT, *ET, *LP, *LQ, *A, *B, *L0;
+    const double* LGK;    // [entry][2][SGB_LGK]: lgamma(a + k), lgamma(b + k) for k < SGB_LGK (beta-binomial; same bits as sgb_lgamma_pos)
     const int* KIND;
     int S, lik;
     double loherror, rho;
@@ -286,7 +300,8 @@ SGB_HD double sgb_emit_item(int cprime, int in_support, double kd, double nkd, d
     const bool fast = (cprime < SGB_CN_TABLE) && in_support && sp.fast_ok && (T.KIND[ti] == SGB_KIND_NORMAL);
     if (fast)
         return sgb_emission_fast<MODEL, LIKBB>(kd, nkd, lc_x, lc_y, lg_sn, T.LP[ti], T.LQ[ti], LIKBB ? T.A[ti] : 0.0,
-                                               LIKBB ? T.B[ti] : 0.0, LIKBB ? T.L0[ti] : 0.0, sp, T.LT, T.ET);
+                                               LIKBB ? T.B[ti] : 0.0, LIKBB ? T.L0[ti] : 0.0,
+                                               LIKBB ? T.LGK + (long)ti * 2 * SGB_LGK : T.LT, sp, T.LT, T.ET);
     return sgb_emit_item_slow<MODEL, LIKBB>(cprime, in_support, kd, nkd, lc_x, lc_y, lg_sn, m, T, sp);
 }
 

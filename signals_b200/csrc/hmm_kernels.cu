@@ -36,6 +36,13 @@ __global__ void k_setup(SgbDevTables* T, SgbModelArgs m, double eps, double Abia
                                            m.rho, s_bb, g_logtab);
         T->lp[idx] = sc.lp; T->lq[idx] = sc.lq; T->a[idx] = sc.a; T->b[idx] = sc.b; T->l0[idx] = sc.l0;
         T->kind[idx] = sc.kind;
+        if (m.lik_bb && s < m.S && sc.kind == SGB_KIND_NORMAL) {
+            double* row = T->lgk + (size_t)(c * m.S + s) * 2 * SGB_LGK;
+            for (int k = 0; k < SGB_LGK; k++) {
+                row[k] = sgb_lgamma_pos(sgb_add(sc.a, (double)k), g_logtab);
+                row[SGB_LGK + k] = sgb_lgamma_pos(sgb_add(sc.b, (double)k), g_logtab);
+            }
+        }
     }
 }
 
@@ -248,7 +255,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     if (threadIdx.x == 0) {
         s_sp = A.tabs->sp;
         s_TB.LT = sLT; s_TB.ET = sET; s_TB.LP = sLP; s_TB.LQ = sLQ; s_TB.A = sA; s_TB.B = sB; s_TB.L0 = sL0;
-        s_TB.KIND = sKind; s_TB.S = S; s_TB.lik = A.lik; s_TB.loherror = A.loherror; s_TB.rho = A.rho;
+        s_TB.LGK = A.tabs->lgk; s_TB.KIND = sKind; s_TB.S = S; s_TB.lik = A.lik; s_TB.loherror = A.loherror; s_TB.rho = A.rho;
     }
     const SgbScalars& sp = s_sp;
     const SgbTables& TB = s_TB;
@@ -273,6 +280,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     __syncthreads();
 
     const double NEG_INF = -sgb_inf();
+    const double* gLGK = A.tabs->lgk;       // small-count lgamma cache (global memory, L1-resident: ~12 KB live)
     double* colE = myE + lane * P;          // this lane's own columns
     double* colT = myT + lane * P;
     unsigned use0 = 0, use1 = 0;            // completed phases of the two stage barriers
@@ -400,7 +408,8 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                         sgb_emission_fast2<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
                                                          LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, d1.x, d1.y, lx1, ly1, gs1,
                                                          sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0, LIKBB ? sB[t1] : 0.0,
-                                                         LIKBB ? sL0[t1] : 0.0, sp, sLT, sET, r0, r1);
+                                                         LIKBB ? sL0[t1] : 0.0, LIKBB ? gLGK + (long)t0 * 2 * SGB_LGK : sLT,
+                                                         LIKBB ? gLGK + (long)t1 * 2 * SGB_LGK : sLT, sp, sLT, sET, r0, r1);
                     } else {
                         const int bi0 = bI[ol0], bi1 = bI[ol1];
                         r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
@@ -426,7 +435,8 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     double r0;
                     if (en0 & 32) {
                         r0 = sgb_emission_fast<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
-                                                             LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, sp, sLT, sET);
+                                                             LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0,
+                                                             LIKBB ? gLGK + (long)t0 * 2 * SGB_LGK : sLT, sp, sLT, sET);
                     } else {
                         const int bi0 = bI[ol0];
                         r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);

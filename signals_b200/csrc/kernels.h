@@ -15,6 +15,8 @@ struct SgbDevTables {
     double b[SGB_CN_TABLE * SGB_MAX_STATES];
     double l0[SGB_CN_TABLE * SGB_MAX_STATES];
     int kind[SGB_CN_TABLE * SGB_MAX_STATES];
+    // beta-binomial only: lgamma(a + k), lgamma(b + k), k < SGB_LGK, row index = cn * S + state (the call's S)
+    double lgk[SGB_CN_TABLE * SGB_MAX_STATES * 2 * SGB_LGK];
 };
 
 // A "plan" describes the (cell, chromosome) sequences of one batch, sorted by length

@@ -333,6 +333,29 @@ SGB_HD double sgb_lgamma_pos(double z, const double* __restrict__ LT)
     return sgb_sub(res, lP);
 }
 
+// Stirling part alone: for z >= 10 this performs exactly the operations sgb_lgamma_pos performs there
+// (P = 1 -> log P = +0, shift 0 -> residual 0), hence the same bits, without the product and the second log.
+SGB_HD double sgb_lgamma_ge10(double z, const double* __restrict__ LT)
+{
+    double seed;
+    const double ly = sgb_log_core(sgb_d2u(z), 0, LT, &seed);
+    double e = sgb_fma(-z, seed, 1.0);
+    double t = sgb_fma(e, e, e);
+    double rr = sgb_fma(seed, t, seed);
+    e = sgb_fma(-z, rr, 1.0);
+    t = sgb_fma(e, e, e);
+    rr = sgb_fma(rr, t, rr);
+    rr = (z < 0x1p500) ? rr : 0.0;
+    const double r2 = sgb_mul(rr, rr);
+    const double r4 = sgb_mul(r2, r2);
+    const double c01 = sgb_fma(r2, SGB_C(STIR2), SGB_C(STIR1));
+    const double c23 = sgb_fma(r2, SGB_C(STIR4), SGB_C(STIR3));
+    const double c45 = sgb_fma(r2, SGB_C(STIR6), SGB_C(STIR5));
+    const double c = sgb_fma(r4, sgb_fma(r4, sgb_fma(r4, SGB_C(STIR7), c45), c23), c01);
+    const double corr = sgb_mul(rr, c);      // (the residual term is fma(0, finite, corr) = corr there, and log 1 = +0)
+    return sgb_add(sgb_fma(sgb_sub(z, 0.5), ly, -z), sgb_add(SGB_C(HALF_LN_2PI), corr));
+}
+
 SGB_HD double sgb_lgamma(double z, const double* __restrict__ LT)
 {
     if (z != z) return z;

@@ -19,15 +19,21 @@ static void run(int S, int decode, double loherror, double eps, double rho, doub
     std::vector<double> tLP(SGB_CN_TABLE * S), tLQ(SGB_CN_TABLE * S), tA(SGB_CN_TABLE * S), tB(SGB_CN_TABLE * S),
         tL0(SGB_CN_TABLE * S);
     std::vector<int> tK(SGB_CN_TABLE * S);
+    std::vector<double> tG((size_t)SGB_CN_TABLE * S * 2 * SGB_LGK, 0.0);
     for (int c = 0; c < SGB_CN_TABLE; c++)
         for (int m = 0; m < S; m++) {
             SgbStateConst sc = sgb_state_const(c, m, loherror, lik, rho, sp.bb_s, LT);
             int i = c * S + m;
             tLP[i] = sc.lp; tLQ[i] = sc.lq; tA[i] = sc.a; tB[i] = sc.b; tL0[i] = sc.l0; tK[i] = sc.kind;
+            if (LIKBB && sc.kind == SGB_KIND_NORMAL)
+                for (int k = 0; k < SGB_LGK; k++) {
+                    tG[(size_t)i * 2 * SGB_LGK + k] = sgb_lgamma_pos(sgb_add(sc.a, (double)k), LT);
+                    tG[(size_t)i * 2 * SGB_LGK + SGB_LGK + k] = sgb_lgamma_pos(sgb_add(sc.b, (double)k), LT);
+                }
         }
     SgbTables TB;
     TB.LT = LT; TB.ET = ET; TB.LP = tLP.data(); TB.LQ = tLQ.data(); TB.A = tA.data(); TB.B = tB.data();
-    TB.L0 = tL0.data(); TB.KIND = tK.data(); TB.S = S; TB.lik = lik; TB.loherror = loherror; TB.rho = rho;
+    TB.L0 = tL0.data(); TB.LGK = tG.data(); TB.KIND = tK.data(); TB.S = S; TB.lik = lik; TB.loherror = loherror; TB.rho = rho;
     SgbSeqState<SMAX> st;
     double T1m[SMAX], m1m = 0.0;
     int Lkeep = SMAX;
@@ -49,6 +55,7 @@ static void run(int S, int decode, double loherror, double eps, double rho, doub
                     double r0, r1;
                     sgb_emission_fast2<MODEL, LIKBB>(b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, tLP[t0], tLQ[t0], tA[t0], tB[t0], tL0[t0],
                                                      b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, tLP[t1], tLQ[t1], tA[t1], tB[t1], tL0[t1],
+                                                     tG.data() + (size_t)t0 * 2 * SGB_LGK, tG.data() + (size_t)t1 * 2 * SGB_LGK,
                                                      sp, LT, ET, r0, r1);
                     e[i] = r0; e[j] = r1;
                 } else {
