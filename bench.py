@@ -310,10 +310,17 @@ def main():
         hbm_peak, hbm_src = float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     except Exception:
         hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_k_decode_traffic.json")))
+        traffic = tj[a.workload]["traffic_bytes_per_launch"] if a.workload in tj else None
+    except Exception:
+        traffic = None
     dec_s = main_res["decode_ms"] * 1e-3
     achieved_tf = fe / dec_s / 1e12
     roofline = {"bound": "fp64", "kernel": "k_decode", "achieved": achieved_tf, "peak": peak.value, "unit": "TFLOP/s",
-                "frac": achieved_tf / peak.value if peak.value > 0 else None, "traffic": None,
+                "frac": achieved_tf / peak.value if peak.value > 0 else None, "traffic": traffic,
+                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one k_decode launch from the committed ncu --set full capture (profiles/r01_k_decode_traffic.json); algorithmic bytes = 10 B x cell-bins",
                 "peak_source": "DFMA micro-kernel measured in this process (sgb_fp64_peak); nominal 37.2 at 1965 MHz",
                 "flop_eq_per_cell_bin": fe / main_res["N"], "flop_eq_convention": "SURVEY 8(d): FMA=2, exp=40, log=log1p=50, lgamma=100, live states only",
                 "kernel_ms": main_res["decode_ms"], "pack_ms": main_res["pack_ms"],
