@@ -162,24 +162,85 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
     hc = torch.from_numpy(d["cn"]).pin_memory()
     hout = torch.zeros(N, dtype=torch.uint8).pin_memory()
     tn, tx, tc = hn.to(dev), hx.to(dev), hc.to(dev)
-    out = torch.zeros(N, dtype=torch.uint8, device=dev)
-    gathered = torch.empty(N * world, dtype=torch.uint8, device=dev) if world > 1 else None
-    plan = hmm.DevicePlan(N, d["seg_off"], n_states=PARAMS["n_states"])
-    plan.enable_timing(True)
     stream = torch.cuda.current_stream().cuda_stream
+    so = d["seg_off"]
+    gather_mode = "none"
+    if world == 1:
+        out = torch.zeros(N, dtype=torch.uint8, device=dev)
+        plan = hmm.DevicePlan(N, so, n_states=PARAMS["n_states"])
+        plan.enable_timing(True)
+        plans = [plan]
 
-    def step():
-        plan.decode(P, tn, tx, tc, out, stream=stream)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, out)
+        def step():
+            plan.decode(P, tn, tx, tc, out, stream=stream)
+    else:
+        # Cells are independent: each rank decodes its own shard; the only exchange is the gather of the uint8
+        # paths.  Preferred: every rank PUSHES its slice into all peers' gather buffers with copy-engine (DMA)
+        # copies over NVLink -- no SMs involved -- issued per half of the shard so the first half's transfer
+        # overlaps the second half's decode; one barrier at the end of the step.  Fallback: NCCL all-gather.
+        half = (so.size - 1) // 2
+        NA = int(so[half])
+        planA = hmm.DevicePlan(NA, so[: half + 1], n_states=PARAMS["n_states"])
+        planB = hmm.DevicePlan(N - NA, so[half:] - so[half], n_states=PARAMS["n_states"])
+        planB.enable_timing(True); planA.enable_timing(True)
+        plans = [planA, planB]
+        plan = planB
+        side = torch.cuda.Stream(device=dev)
+        hdl = None
+        if os.environ.get("BENCH_GATHER", "p2p") == "p2p":
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+                if hasattr(symm_mem, "enable_symm_mem_for_group"):
+                    try:
+                        symm_mem.enable_symm_mem_for_group(dist.group.WORLD.group_name)
+                    except Exception:
+                        pass
+                gathered = symm_mem.empty(N * world, dtype=torch.uint8, device=dev)
+                hdl = symm_mem.rendezvous(gathered, dist.group.WORLD)
+                peers = [hdl.get_buffer(r, (N * world,), torch.uint8) for r in range(world)]
+                gather_mode = "p2p_dma_push_overlapped"
+            except Exception as ex:          # symmetric memory unavailable: NCCL path below
+                hdl = None
+                sys.stderr.write("symmetric memory unavailable (%s); using NCCL all_gather\n" % ex)
+        if hdl is None:
+            gathered = torch.empty(N * world, dtype=torch.uint8, device=dev)
+            gather_mode = "nccl_all_gather"
+        out = gathered[rank * N: (rank + 1) * N] if hdl is not None else torch.zeros(N, dtype=torch.uint8, device=dev)
+        main = torch.cuda.current_stream()
+        evA, evB = torch.cuda.Event(), torch.cuda.Event()
+
+        def push(lo, hi):
+            for k in range(1, world):
+                r = (rank + k) % world
+                peers[r][rank * N + lo: rank * N + hi].copy_(out[lo:hi], non_blocking=True)
+
+        def step():
+            planA.decode(P, tn[:NA], tx[:NA], tc[:NA], out[:NA], stream=stream)
+            if hdl is not None:
+                evA.record(main)
+                with torch.cuda.stream(side):
+                    side.wait_event(evA)
+                    push(0, NA)
+            planB.decode(P, tn[NA:], tx[NA:], tc[NA:], out[NA:], stream=stream)
+            if hdl is not None:
+                evB.record(main)
+                with torch.cuda.stream(side):
+                    side.wait_event(evB)
+                    push(NA, N)
+                main.wait_stream(side)
+                hdl.barrier()
+            else:
+                dist.all_gather_into_tensor(gathered, out)
 
     for _ in range(max(warmup, 3)):
         step()
-    plan.check(stream)
+    for pl in plans:
+        pl.check(stream)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    plan.enable_timing(True)            # restart the ring so it only holds timed steps
+    for pl in plans:
+        pl.enable_timing(True)          # restart the rings so they only hold timed steps
     small = N * 9 < 200e6               # inputs fit in the 126 MB L2: flush it between (individually timed) steps
     sampler.active = True
     if not small:
@@ -207,11 +268,20 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     total_ms = float(ms.item())
-    plan.check(stream)
-    pack_ms, decode_ms = plan.read_timing(64)
+    for pl in plans:
+        pl.check(stream)
+    pack_ms = sum(float(pl.read_timing(64)[0].mean()) for pl in plans)
+    decode_ms = sum(float(pl.read_timing(64)[1].mean()) for pl in plans)      # one launch per plan per step
     res = dict(ms_per_step=total_ms / steps, value=N * world * steps / (total_ms * 1e-3),
-               decode_ms=float(decode_ms.mean()), pack_ms=float(pack_ms.mean()), N=N,
-               scratch_bytes=plan.scratch_bytes(), checksum=int(out.to(torch.int64).sum().item()))
+               decode_ms=decode_ms, pack_ms=pack_ms, N=N, gather=gather_mode, launches_per_step=3 * len(plans),
+               scratch_bytes=sum(pl.scratch_bytes() for pl in plans), checksum=int(out.to(torch.int64).sum().item()))
+    if world > 1:
+        # every rank must hold every rank's paths: compare checksums of the gathered slices with their owners'
+        sums = torch.stack([gathered[r * N: (r + 1) * N].to(torch.int64).sum() for r in range(world)])
+        ref = torch.zeros(world, dtype=torch.int64, device=dev)
+        ref[rank] = res["checksum"]
+        dist.all_reduce(ref)
+        assert torch.equal(sums, ref), "gathered paths differ from the owners' results"
 
     if want_e2e:
         lib = _lib.load()
@@ -242,7 +312,8 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                           h2d_bytes_per_step=int(N * 9 + nseq * 20), d2h_bytes_per_step=int(N), steps=e2e_steps,
                           api="sgb_hmm_decode (host buffers, pinned, chunked copy/compute overlap)")
         assert int(hout.to(torch.int64).sum().item()) == res["checksum"], "host-API and device-API results differ"
-    plan.close()
+    for pl in plans:
+        pl.close()
     del tn, tx, tc, out, hn, hx, hc, hout
     torch.cuda.empty_cache()
     return res
@@ -330,7 +401,7 @@ def main():
     line = {"metric": "cell_bins_per_sec", "value": main_res["value"], "unit": "cell-bins/s", "n_gpus": world,
             "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": main_res["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
-            "clocks": clocks, "e2e": main_res.get("e2e"), "gpu_launches": 3 * a.steps,
+            "clocks": clocks, "e2e": main_res.get("e2e"), "gpu_launches": main_res["launches_per_step"] * a.steps, "gather": main_res["gather"],
             "gpu_kernels_per_step": ["k_setup", "k_pack", "k_decode"], "roofline": roofline,
             "scratch_bytes": main_res["scratch_bytes"]}
 
