@@ -176,16 +176,12 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
     else:
         # Cells are independent: each rank decodes its own shard; the only exchange is the gather of the uint8
         # paths.  Preferred: every rank PUSHES its slice into all peers' gather buffers with copy-engine (DMA)
-        # copies over NVLink -- no SMs involved -- issued per half of the shard so the first half's transfer
-        # overlaps the second half's decode; one barrier at the end of the step.  Fallback: NCCL all-gather.
-        half = (so.size - 1) // 2
-        NA = int(so[half])
-        planA = hmm.DevicePlan(NA, so[: half + 1], n_states=PARAMS["n_states"])
-        planB = hmm.DevicePlan(N - NA, so[half:] - so[half], n_states=PARAMS["n_states"])
-        planB.enable_timing(True); planA.enable_timing(True)
-        plans = [planA, planB]
-        plan = planB
-        side = torch.cuda.Stream(device=dev)
+        # copies over NVLink (symmetric memory, no SMs involved) and one barrier closes the step.  (Splitting the
+        # shard in halves to overlap the first half's transfer with the second half's decode was measured and
+        # lost more to the second kernel tail than it hid.)  Fallback: NCCL all-gather.
+        plan = hmm.DevicePlan(N, so, n_states=PARAMS["n_states"])
+        plan.enable_timing(True)
+        plans = [plan]
         hdl = None
         if os.environ.get("BENCH_GATHER", "p2p") == "p2p":
             try:
@@ -198,7 +194,7 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                 gathered = symm_mem.empty(N * world, dtype=torch.uint8, device=dev)
                 hdl = symm_mem.rendezvous(gathered, dist.group.WORLD)
                 peers = [hdl.get_buffer(r, (N * world,), torch.uint8) for r in range(world)]
-                gather_mode = "p2p_dma_push_overlapped"
+                gather_mode = "p2p_dma_push"
             except Exception as ex:          # symmetric memory unavailable: NCCL path below
                 hdl = None
                 sys.stderr.write("symmetric memory unavailable (%s); using NCCL all_gather\n" % ex)
@@ -206,28 +202,13 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
             gathered = torch.empty(N * world, dtype=torch.uint8, device=dev)
             gather_mode = "nccl_all_gather"
         out = gathered[rank * N: (rank + 1) * N] if hdl is not None else torch.zeros(N, dtype=torch.uint8, device=dev)
-        main = torch.cuda.current_stream()
-        evA, evB = torch.cuda.Event(), torch.cuda.Event()
-
-        def push(lo, hi):
-            for k in range(1, world):
-                r = (rank + k) % world
-                peers[r][rank * N + lo: rank * N + hi].copy_(out[lo:hi], non_blocking=True)
 
         def step():
-            planA.decode(P, tn[:NA], tx[:NA], tc[:NA], out[:NA], stream=stream)
+            plan.decode(P, tn, tx, tc, out, stream=stream)
             if hdl is not None:
-                evA.record(main)
-                with torch.cuda.stream(side):
-                    side.wait_event(evA)
-                    push(0, NA)
-            planB.decode(P, tn[NA:], tx[NA:], tc[NA:], out[NA:], stream=stream)
-            if hdl is not None:
-                evB.record(main)
-                with torch.cuda.stream(side):
-                    side.wait_event(evB)
-                    push(NA, N)
-                main.wait_stream(side)
+                for k in range(1, world):
+                    r = (rank + k) % world
+                    peers[r][rank * N: (rank + 1) * N].copy_(out, non_blocking=True)
                 hdl.barrier()
             else:
                 dist.all_gather_into_tensor(gathered, out)
