@@ -24,9 +24,6 @@
 #define SGB_MAX_STATES 32      // S = maxCN+1 supported by the fused kernels
 #define SGB_CN_TABLE 16        // total-CN values 0..15 have their per-state constants tabulated
 #define SGB_COUNT_BITS 28      // read counts must be < 2^28 (packed record n:28 | x:28 | cn:8)
-#ifndef SGB_ET_STRIDE
-#define SGB_ET_STRIDE 1           // spacing of exp-table entries seen by the lean emission path (see sgb_exp_core_s)
-#endif
 #define SGB_LGK 10             // beta-binomial: lgamma(shape + k) is tabulated per (total CN, state) for k < SGB_LGK
 
 // kind of a (total CN, state) pair
@@ -211,9 +208,9 @@ SGB_HD double sgb_emission_fast(double kd, double nkd, double lc_x, double lc_y,
             t1 = sgb_sub(t1, lg_sn);
             l2 = sgb_add(lc_y, sgb_sub(t1, l0));
         }
-        l = sgb_logspace_add_lean_s(l, l2, LT, ET, SGB_ET_STRIDE);
+        l = sgb_logspace_add_lean(l, l2, LT, ET);
     }
-    if (sp.use_eps) l = sgb_logspace_add_lean_s(l, sp.log_eps, LT, ET, SGB_ET_STRIDE);
+    if (sp.use_eps) l = sgb_logspace_add_lean(l, sp.log_eps, LT, ET);
     return l;
 }
 
@@ -247,13 +244,13 @@ SGB_HD void sgb_emission_fast2(double kd0, double nk0, double lx0, double ly0, d
             m0 = sgb_add(ly0, sgb_sub(sgb_sub(t0, gs0), z0));
             m1 = sgb_add(ly1, sgb_sub(sgb_sub(t1, gs1), z1));
         }
-        l0 = sgb_logspace_add_lean_s(l0, m0, LT, ET, SGB_ET_STRIDE);
-        l1 = sgb_logspace_add_lean_s(l1, m1, LT, ET, SGB_ET_STRIDE);
+        l0 = sgb_logspace_add_lean(l0, m0, LT, ET);
+        l1 = sgb_logspace_add_lean(l1, m1, LT, ET);
     }
     if (sp.use_eps) {
         const double le = sp.log_eps;
-        l0 = sgb_logspace_add_lean_s(l0, le, LT, ET, SGB_ET_STRIDE);
-        l1 = sgb_logspace_add_lean_s(l1, le, LT, ET, SGB_ET_STRIDE);
+        l0 = sgb_logspace_add_lean(l0, le, LT, ET);
+        l1 = sgb_logspace_add_lean(l1, le, LT, ET);
     }
     r0 = l0; r1 = l1;
 }
@@ -269,7 +266,6 @@ SGB_HD void sgb_emission_fast2(double kd0, double nk0, double lx0, double ly0, d
 // untabulated path needs to recompute an entry on the fly.
 struct SgbTables {
     const double *LT, *ET, *LP, *LQ, *A, *B, *L0;
-    const double* ETR;    // exp table with entry spacing SGB_ET_STRIDE for the lean path (== ET when the stride is 1)
     const double* LGK;    // [entry][2][SGB_LGK]: lgamma(a + k), lgamma(b + k) for k < SGB_LGK (beta-binomial; same bits as sgb_lgamma_pos)
     const int* KIND;
     int S, lik;
@@ -305,7 +301,7 @@ SGB_HD double sgb_emit_item(int cprime, int in_support, double kd, double nkd, d
     if (fast)
         return sgb_emission_fast<MODEL, LIKBB>(kd, nkd, lc_x, lc_y, lg_sn, T.LP[ti], T.LQ[ti], LIKBB ? T.A[ti] : 0.0,
                                                LIKBB ? T.B[ti] : 0.0, LIKBB ? T.L0[ti] : 0.0,
-                                               LIKBB ? T.LGK + (long)ti * 2 * SGB_LGK : T.LT, sp, T.LT, T.ETR);
+                                               LIKBB ? T.LGK + (long)ti * 2 * SGB_LGK : T.LT, sp, T.LT, T.ET);
     return sgb_emit_item_slow<MODEL, LIKBB>(cprime, in_support, kd, nkd, lc_x, lc_y, lg_sn, m, T, sp);
 }
 

@@ -11,7 +11,6 @@
 //
 // Reference functions replaced: src/code.cpp:5-45, R/callHSCN.R:36-108,135-172,217-295,
 // R/callASCN.R:41-103,128-161 (see hmm_core.cuh for the arithmetic and DESIGN.md for the design).
-#define SGB_ET_STRIDE 16          // the decode kernel reads a 16x bank-spread replica of the exp table
 #include "kernels.h"
 
 __device__ const double g_logtab[SGB_LOGTAB_LEN] = SGB_LOGTAB_INIT;
@@ -193,7 +192,7 @@ static inline size_t decode_warp_doubles(int SMAX, int model, int lik_bb, int st
 }
 static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb, int stage)
 {
-    size_t d = SGB_LOGTAB_LEN + SGB_EXPTAB_LEN * (1 + SGB_ET_STRIDE) + SGB_LF_SMEM;
+    size_t d = SGB_LOGTAB_LEN + SGB_EXPTAB_LEN + SGB_LF_SMEM;
     d += (size_t)SGB_CN_TABLE * S * (lik_bb ? 5 : 2);
     d += (size_t)SGB_DECODE_WARPS * decode_warp_doubles(SMAX, model, lik_bb, stage);
     return d * sizeof(double) + ((size_t)SGB_CN_TABLE * S + SGB_CN_TABLE) * sizeof(int);
@@ -225,8 +224,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     constexpr int WARP_DOUBLES = (WD0 + 1) & ~1;
     double* sLT = smem;
     double* sET = sLT + SGB_LOGTAB_LEN;
-    double* sETR = sET + SGB_EXPTAB_LEN;        // [entry][16 replicas]
-    double* sLF = sETR + SGB_EXPTAB_LEN * SGB_ET_STRIDE;
+    double* sLF = sET + SGB_EXPTAB_LEN;
     double* sLP = sLF + SGB_LF_SMEM;
     double* sLQ = sLP + CTS;
     double* sA = sLQ + CTS;
@@ -238,7 +236,6 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
 
     for (int i = threadIdx.x; i < SGB_LOGTAB_LEN; i += blockDim.x) sLT[i] = g_logtab[i];
     for (int i = threadIdx.x; i < SGB_EXPTAB_LEN; i += blockDim.x) sET[i] = g_exptab[i];
-    for (int i = threadIdx.x; i < SGB_EXPTAB_LEN * SGB_ET_STRIDE; i += blockDim.x) sETR[i] = g_exptab[i / SGB_ET_STRIDE];
     for (int i = threadIdx.x; i < SGB_LF_SMEM; i += blockDim.x) sLF[i] = g_lftab[i];
     for (int i = threadIdx.x; i < CTS; i += blockDim.x) {
         int c = i / S, s = i - c * S, src = c * SGB_MAX_STATES + s;
@@ -257,7 +254,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     __shared__ SgbTables s_TB;
     if (threadIdx.x == 0) {
         s_sp = A.tabs->sp;
-        s_TB.LT = sLT; s_TB.ET = sET; s_TB.ETR = sETR; s_TB.LP = sLP; s_TB.LQ = sLQ; s_TB.A = sA; s_TB.B = sB; s_TB.L0 = sL0;
+        s_TB.LT = sLT; s_TB.ET = sET; s_TB.LP = sLP; s_TB.LQ = sLQ; s_TB.A = sA; s_TB.B = sB; s_TB.L0 = sL0;
         s_TB.LGK = A.tabs->lgk; s_TB.KIND = sKind; s_TB.S = S; s_TB.lik = A.lik; s_TB.loherror = A.loherror; s_TB.rho = A.rho;
     }
     const SgbScalars& sp = s_sp;
@@ -283,7 +280,6 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     __syncthreads();
 
     const double NEG_INF = -sgb_inf();
-    const double* myET = sETR + (lane & (SGB_ET_STRIDE - 1));      // this lane's replica of the exp table
     const double* gLGK = A.tabs->lgk;       // small-count lgamma cache (global memory, L1-resident: ~12 KB live)
     double* colE = myE + lane * P;          // this lane's own columns
     double* colT = myT + lane * P;
@@ -413,7 +409,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                                                          LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, d1.x, d1.y, lx1, ly1, gs1,
                                                          sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0, LIKBB ? sB[t1] : 0.0,
                                                          LIKBB ? sL0[t1] : 0.0, LIKBB ? gLGK + (long)t0 * 2 * SGB_LGK : sLT,
-                                                         LIKBB ? gLGK + (long)t1 * 2 * SGB_LGK : sLT, sp, sLT, myET, r0, r1);
+                                                         LIKBB ? gLGK + (long)t1 * 2 * SGB_LGK : sLT, sp, sLT, sET, r0, r1);
                     } else {
                         const int bi0 = bI[ol0], bi1 = bI[ol1];
                         r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
@@ -440,7 +436,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     if (en0 & 32) {
                         r0 = sgb_emission_fast<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
                                                              LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0,
-                                                             LIKBB ? gLGK + (long)t0 * 2 * SGB_LGK : sLT, sp, sLT, myET);
+                                                             LIKBB ? gLGK + (long)t0 * 2 * SGB_LGK : sLT, sp, sLT, sET);
                     } else {
                         const int bi0 = bI[ol0];
                         r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);

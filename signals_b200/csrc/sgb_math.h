@@ -117,12 +117,8 @@ SGB_HD double sgb_fmax(double a, double b)
 // exp(x) = 2^q * T[j] * (1 + p(r)),  x = (64 q + j) ln2/64 + r,  |r| <= ln2/128.
 // Results below 2^-1022 are flushed to +0 (x <= -708): the only caller that can
 // get there is logspace_add, where exp(d) is added to 1 -- irrelevant there.
-// core: valid for x in [-708, 709], no special-value handling.
-// ET_STRIDE (a compile-time constant at every call site): spacing of consecutive table entries in doubles.
-// 1 = the plain 64-entry table; the kernels pass a
-// copy replicated 16x (entry j of replica c at ET[16 j + c], ET pre-offset by the lane's replica) so that the
-// 32 lanes of a warp always hit 16 distinct bank pairs whatever their j -- same values, fewer conflicts.
-SGB_HD double sgb_exp_core_s(double x, const double* __restrict__ ET, const int ET_STRIDE)
+// core: valid for x in [-708, 709], no special-value handling
+SGB_HD double sgb_exp_core(double x, const double* __restrict__ ET)
 {
     double t  = sgb_fma(x, SGB_C(INVLN2_N), SGB_SHIFT);
     double kd = sgb_sub(t, SGB_SHIFT);
@@ -131,7 +127,7 @@ SGB_HD double sgb_exp_core_s(double x, const double* __restrict__ ET, const int 
     r = sgb_fma(kd, -SGB_C(LN2N_LO), r);
     int32_t j = k & (SGB_NEXP - 1);
     int64_t q = (int64_t)(k >> 6);
-    double s = sgb_u2d(sgb_d2u(ET[j * ET_STRIDE]) + ((uint64_t)q << 52));
+    double s = sgb_u2d(sgb_d2u(ET[j]) + ((uint64_t)q << 52));
     // Estrin evaluation (3 dependent levels instead of 6): 1 + C2 r + ... + C6 r^5
     double r2 = sgb_mul(r, r);
     double p01 = sgb_fma(r, SGB_C(EXPC2), 1.0);
@@ -142,8 +138,6 @@ SGB_HD double sgb_exp_core_s(double x, const double* __restrict__ ET, const int 
     p = sgb_mul(r, p);
     return sgb_fma(s, p, s);
 }
-
-SGB_HD double sgb_exp_core(double x, const double* __restrict__ ET) { return sgb_exp_core_s(x, ET, 1); }
 
 SGB_HD double sgb_exp(double x, const double* __restrict__ ET)
 {
@@ -274,17 +268,12 @@ SGB_HD double sgb_max(double a, double b)            // operands are never NaN h
 // Branch-free body, valid when neither operand is NaN and they are not the same infinity.
 // The exponent is clamped at -708 (exp(-708) ~ 3e-308 instead of an underflowing value: it vanishes
 // against any max(a,b) that is not itself below 1e-290 in magnitude).
-SGB_HD double sgb_logspace_add_lean_s(double a, double b, const double* __restrict__ LT, const double* __restrict__ ET,
-                                      const int ET_STRIDE)
+SGB_HD double sgb_logspace_add_lean(double a, double b, const double* __restrict__ LT, const double* __restrict__ ET)
 {
     double mx = sgb_max(a, b);
     double d = sgb_u2d(sgb_d2u(sgb_sub(a, b)) | 0x8000000000000000ULL);      // -fabs(a-b)
-    double u = sgb_exp_core_s(sgb_max(d, -708.0), ET, ET_STRIDE);
+    double u = sgb_exp_core(sgb_max(d, -708.0), ET);
     return sgb_add(mx, sgb_log1p01_core(u, sgb_add(1.0, u), LT));
-}
-SGB_HD double sgb_logspace_add_lean(double a, double b, const double* __restrict__ LT, const double* __restrict__ ET)
-{
-    return sgb_logspace_add_lean_s(a, b, LT, ET, 1);
 }
 
 SGB_HD double sgb_logspace_add(double a, double b, const double* __restrict__ LT, const double* __restrict__ ET)
