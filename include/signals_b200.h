@@ -141,6 +141,15 @@ SGB_API int sgb_logspace_add_vec(const double* logx, const double* logy, int64_t
 SGB_API int sgb_postprocess(int64_t N, const void* cn, int32_t cn_itemsize, const uint8_t* path, int32_t* A, int32_t* B,
                     int32_t* state_min, uint8_t* loh, uint8_t* phase, uint8_t* state_phase, double* state_baf);
 
+/* ---- between-pass statistics ------------------------------------------------ */
+/* The whole-table reductions the drivers make between the two HMM passes, as exact integer sums computed on
+ * the device from the decoded paths: sums_out[0..2] = sum(alleleB), sum(totalcounts), row count over the
+ * "A-Hom" rows (B == 0 < A after the clamp block) so that infloherror = weighted.mean(BAF, totalcounts) =
+ * sums_out[0] / sums_out[1]  (R/callHSCN.R:898-902, R/callASCN.R:334-343); ab_hist_out[A*n_states + B] = number
+ * of rows in state A|B with B > 0, from which fitBB picks its modal state (R/callHSCN.R:620-621). */
+SGB_API int sgb_pass_stats(int64_t N, const int32_t* n, const int32_t* x, const void* cn, int32_t cn_itemsize,
+                           const uint8_t* path, int32_t n_states, int64_t* sums_out, int64_t* ab_hist_out);
+
 /* ---- diagnostics -------------------------------------------------------------------------- */
 /* Evaluate one deterministic math primitive on the device (tests pin device bits == host bits).
  * fn: 0 exp, 1 log, 2 log1p on [0,1], 3 log1p, 4 lgamma, 5 logspace_add(in, in2), 6 log(in!) */

@@ -48,6 +48,7 @@ SIGNATURES = {
     "sgb_logspace_add": (ctypes.c_int, [_dbl, _dbl, ctypes.POINTER(_dbl)]),
     "sgb_logspace_add_vec": (ctypes.c_int, [_vp, _vp, _i64, _vp]),
     "sgb_postprocess": (ctypes.c_int, [_i64, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "sgb_pass_stats": (ctypes.c_int, [_i64, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _vp]),
     "sgb_math_eval": (ctypes.c_int, [_i32, _vp, _vp, _i64, _vp]),
     "sgb_fp64_peak": (ctypes.c_int, [_i32, ctypes.POINTER(_dbl)]),
 }

@@ -755,6 +755,49 @@ int sgb_postprocess(int64_t N, const void* cn, int32_t cn_itemsize, const uint8_
     return 0;
 }
 
+int sgb_pass_stats(int64_t N, const int32_t* n, const int32_t* x, const void* cn, int32_t cn_itemsize,
+                   const uint8_t* path, int32_t n_states, int64_t* sums_out, int64_t* ab_hist_out)
+{
+    if (N < 0) return fail("negative size");
+    if (cn_itemsize != 1 && cn_itemsize != 4) return fail("cn_itemsize must be 1 (uint8) or 4 (int32)");
+    if (n_states < 1 || n_states > SGB_MAX_STATES) return fail("n_states (maxCN+1) must be in 1..32");
+    if (!sums_out || !ab_hist_out) return fail("NULL pointer");
+    const int S = n_states;
+    const size_t nout = 3 + (size_t)S * S;
+    for (int i = 0; i < 3; i++) sums_out[i] = 0;
+    for (size_t i = 0; i < (size_t)S * S; i++) ab_hist_out[i] = 0;
+    if (N == 0) return 0;
+    if (!n || !x || !cn || !path) return fail("NULL pointer");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    cudaStream_t st = C->main;
+    const int64_t chunk = 16ll << 20;
+    const int64_t m0 = std::min(N, chunk);
+    if (C->scratch_a.reserve((size_t)m0 * 8 + 64) || C->scratch_b.reserve((size_t)m0 * (cn_itemsize + 1) + 64) ||
+        C->scratch_c.reserve(nout * 8 + 64))
+        return 1;
+    unsigned long long* d_out = (unsigned long long*)C->scratch_c.p;
+    SGB_CUDA(cudaMemsetAsync(d_out, 0, nout * 8, st));
+    for (int64_t o = 0; o < N; o += chunk) {
+        const int64_t m = std::min(chunk, N - o);
+        int32_t* d_n = (int32_t*)C->scratch_a.p;
+        int32_t* d_x = d_n + m;
+        char* d_cn = (char*)C->scratch_b.p;
+        uint8_t* d_path = (uint8_t*)d_cn + (size_t)m * cn_itemsize;
+        SGB_CUDA(cudaMemcpyAsync(d_n, n + o, (size_t)m * 4, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(d_x, x + o, (size_t)m * 4, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(d_cn, (const char*)cn + (size_t)o * cn_itemsize, (size_t)m * cn_itemsize, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(d_path, path + o, (size_t)m, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(sgbk_pass_stats(d_n, d_x, d_cn, cn_itemsize, d_path, m, S, d_out, st));
+        SGB_CUDA(cudaStreamSynchronize(st));
+    }
+    std::vector<unsigned long long> h(nout);
+    SGB_CUDA(cudaMemcpy(h.data(), d_out, nout * 8, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 3; i++) sums_out[i] = (int64_t)h[(size_t)i];
+    for (size_t i = 0; i < (size_t)S * S; i++) ab_hist_out[i] = (int64_t)h[3 + i];
+    return 0;
+}
+
 int sgb_fp64_peak(int32_t iters, double* tflops_out)
 {
     if (!tflops_out) return fail("NULL pointer");

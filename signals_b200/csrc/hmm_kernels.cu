@@ -564,6 +564,7 @@ cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_pack
     A.lik = m.lik_bb ? SGB_LIK_BETABINOMIAL : SGB_LIK_BINOMIAL;
     A.loherror = m.loherror; A.rho = m.rho;
     if (m.S <= 12) return dispatch_decode<12>(A, m, stage, sm_count, st);
+    if (m.S <= 16) return dispatch_decode<16>(A, m, stage, sm_count, st);
     if (m.S <= SGB_MAX_STATES) return dispatch_decode<SGB_MAX_STATES>(A, m, stage, sm_count, st);
     return cudaErrorInvalidValue;
 }
@@ -836,6 +837,58 @@ cudaError_t sgbk_postprocess(const void* d_cn, int cn_itemsize, const uint8_t* d
     if (blocks > 148 * 16) blocks = 148 * 16;
     k_postprocess<<<(unsigned)blocks, 256, 0, st>>>(d_cn, cn_itemsize, d_path, N, d_A, d_B, d_state_min, d_loh,
                                                     d_phase, d_state_phase, d_state_baf);
+    return cudaGetLastError();
+}
+
+// Between-pass statistics: everything the drivers reduce over the whole decoded table before
+// the second HMM pass, as exact integer sums.
+//   out[0], out[1], out[2] : sum(alleleB), sum(totalcounts), row count over the "A-Hom" rows (B == 0 < A after
+//                            the clamp block) -> infloherror = weighted.mean(BAF, totalcounts) = out[0] / out[1]
+//                            (R/callHSCN.R:898-902, R/callASCN.R:334-343)
+//   out[3 + A*S + B]       : number of rows with that (A, B), B > 0 -> the modal state fitBB starts from
+//                            (R/callHSCN.R:620-621)
+__global__ void __launch_bounds__(256) k_pass_stats(const int32_t* __restrict__ n, const int32_t* __restrict__ x,
+                                                    const void* __restrict__ cn, int cn_itemsize,
+                                                    const uint8_t* __restrict__ path, long long N, int S,
+                                                    unsigned long long* __restrict__ out)
+{
+    __shared__ unsigned int hist[SGB_MAX_STATES * SGB_MAX_STATES];
+    for (int i = threadIdx.x; i < S * S; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    unsigned long long sx = 0, sn = 0, cnt = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (long long)gridDim.x * blockDim.x) {
+        int st = (cn_itemsize == 1) ? (int)((const uint8_t*)cn)[i] : ((const int32_t*)cn)[i];
+        int sm = path[i];
+        int a = st - sm, b = sm;
+        if (a < 0) a = 0;
+        if (b > st) b = st;
+        if (a > st) a = st;
+        if (b == 0 && a > 0) { sx += (unsigned long long)x[i]; sn += (unsigned long long)n[i]; cnt++; }
+        if (b > 0 && a < S && b < S) atomicAdd(&hist[a * S + b], 1u);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        sx += __shfl_xor_sync(SGB_FULL, sx, off);
+        sn += __shfl_xor_sync(SGB_FULL, sn, off);
+        cnt += __shfl_xor_sync(SGB_FULL, cnt, off);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (sx) atomicAdd(&out[0], sx);
+        if (sn) atomicAdd(&out[1], sn);
+        if (cnt) atomicAdd(&out[2], cnt);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < S * S; i += blockDim.x)
+        if (hist[i]) atomicAdd(&out[3 + i], (unsigned long long)hist[i]);
+}
+
+cudaError_t sgbk_pass_stats(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,
+                            const uint8_t* d_path, long long N, int S, unsigned long long* d_out, cudaStream_t st)
+{
+    if (N <= 0) return cudaSuccess;
+    long long blocks = (N + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_pass_stats<<<(unsigned)blocks, 256, 0, st>>>(d_n, d_x, d_cn, cn_itemsize, d_path, N, S, d_out);
     return cudaGetLastError();
 }
 

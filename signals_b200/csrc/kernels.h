@@ -66,6 +66,8 @@ cudaError_t sgbk_math_eval(int fn, const double* d_in, const double* d_in2, long
 cudaError_t sgbk_postprocess(const void* d_cn, int cn_itemsize, const uint8_t* d_path, long long N, int32_t* d_A,
                              int32_t* d_B, int32_t* d_state_min, uint8_t* d_loh, uint8_t* d_phase,
                              uint8_t* d_state_phase, double* d_state_baf, cudaStream_t st);
+cudaError_t sgbk_pass_stats(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,
+                            const uint8_t* d_path, long long N, int S, unsigned long long* d_out, cudaStream_t st);
 size_t sgbk_viterbi_bp_bytes(long long T, int S);
 void sgb_internal_set_error(const char* msg);      // sets the calling thread's sgb_last_error() text (capi.cu)
 cudaError_t sgbk_fp64_peak(int iters, int sm_count, cudaStream_t st, double* tflops);

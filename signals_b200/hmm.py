@@ -138,6 +138,30 @@ def postprocess_arrays(cn, path):
     return dict(A=A, B=B, state_min=smin, LOH=loh, phase=phase, state_phase=sp, state_BAF=baf)
 
 
+def pass_stats_arrays(n, x, cn, path, n_states=12):
+    """exact whole-table sums the drivers need between the two HMM passes (computed on the device):
+    returns (sum_alleleB, sum_totalcounts, n_rows) over the A-Hom rows and the A x B histogram of rows with B > 0"""
+    n = _as_counts(n, "totalcounts"); x = _as_counts(x, "alleleB")
+    cn = np.asarray(cn)
+    if cn.dtype != np.uint8:
+        cn = _as_counts(cn, "state")
+    cn = np.ascontiguousarray(cn)
+    path = np.ascontiguousarray(path, dtype=np.uint8)
+    sums = np.zeros(3, np.int64); hist = np.zeros(int(n_states) * int(n_states), np.int64)
+    check(_lib.load().sgb_pass_stats(n.size, _ptr(n), _ptr(x), _ptr(cn), cn.dtype.itemsize, _ptr(path), int(n_states),
+                                     _ptr(sums), _ptr(hist)))
+    return sums, hist.reshape(int(n_states), int(n_states))
+
+
+def infer_loherror(n, x, cn, path, maxloherror=0.035, n_states=12):
+    """infloherror of callHaplotypeSpecificCN (R/callHSCN.R:898-902): weighted.mean(BAF, w = totalcounts) over the
+    A-Hom bins, capped at maxloherror"""
+    sums, _ = pass_stats_arrays(n, x, cn, path, n_states)
+    if sums[1] == 0:
+        return float("nan")
+    return min(float(sums[0]) / float(sums[1]), float(maxloherror))
+
+
 class DevicePlan:
     """Device-resident decode: inputs/outputs are torch CUDA tensors (or anything with data_ptr())."""
 

@@ -22,6 +22,8 @@ PARAM_SETS = [
     ("hscn_bb_bigloh", "hscn", "betabinomial", 12, 0.6, 1e-12, 0.3, 0.0, 0.5),
     ("hscn_stp_below_uniform", "hscn", "binomial", 12, 0.02, 1e-12, 0.0, 0.0, 0.01),
     ("ascn_stp_below_uniform", "ascn", "betabinomial", 12, 0.02, 1e-12, 0.05, 0.0, 0.03),
+    ("hscn_maxcn14", "hscn", "binomial", 15, 0.02, 1e-12, 0.0, 0.0, 0.95),
+    ("ascn_bb_maxcn15", "ascn", "betabinomial", 16, 0.02, 1e-12, 0.02, 0.0, 0.95),
 ]
 
 

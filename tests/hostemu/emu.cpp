@@ -108,6 +108,7 @@ extern "C" int emu_decode_sequence(int model, int lik, int S, int decode, double
     if (T <= 0) return 0;
     const int lik_bb = (lik == SGB_LIK_BETABINOMIAL) && rho > 0.0;
     if (S <= 12) run_s<12>(model, lik_bb, S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
+    else if (S <= 16) run_s<16>(model, lik_bb, S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
     else if (S <= 32) run_s<32>(model, lik_bb, S, decode, loherror, eps, rho, Abias, stp, T, n, x, cn, out, l_out);
     else return -1;
     return 0;

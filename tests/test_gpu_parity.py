@@ -198,6 +198,27 @@ def test_postprocess_codes(oracle):
             assert np.array_equal(got[k], ref[k]), k
 
 
+def test_between_pass_statistics(oracle):
+    """infloherror = weighted.mean(BAF, totalcounts) over A-Hom bins (R/callHSCN.R:898-902) and the A|B histogram"""
+    d = cases.small_cohort("binomial", n_cells=40, seed=21)
+    ps = cases.PARAM_SETS[0]
+    path = hmm.decode_arrays(d["n"], d["x"], d["cn"], d["seg_off"], **_kw(ps))
+    sums, hist = hmm.pass_stats_arrays(d["n"], d["x"], d["cn"], path, n_states=12)
+    ref = oracle.postprocess(d["cn"].astype(np.int32), path)
+    ahom = (ref["B"] == 0) & (ref["A"] > 0)
+    assert sums.tolist() == [int(d["x"][ahom].sum()), int(d["n"][ahom].sum()), int(ahom.sum())]
+    h = np.zeros((12, 12), np.int64)
+    sel = ref["B"] > 0
+    np.add.at(h, (ref["A"][sel], ref["B"][sel]), 1)
+    assert np.array_equal(hist, h)
+    # the R expression: weighted.mean(x = BAF, w = totalcounts)
+    baf = d["x"][ahom] / d["n"][ahom]
+    wm = float((baf * d["n"][ahom]).sum() / d["n"][ahom].sum())
+    got = hmm.infer_loherror(d["n"], d["x"], d["cn"], path, maxloherror=1.0)
+    assert abs(got - wm) < 1e-12 and 0.01 < got < 0.04          # the cohort was simulated with loherror = 0.02
+    assert hmm.infer_loherror(d["n"], d["x"], d["cn"], path, maxloherror=0.015) == 0.015
+
+
 def test_r_level_mirror_end_to_end(oracle):
     """.callHaplotypeSpecificCN_ / ASCN twin on a long table, against the oracle's table-level restatement"""
     d = synth.make_cohort(6, lens=synth.LENS_DLPBINS, seed=31, ragged_drop=0.05)
