@@ -36,7 +36,13 @@ WORKLOADS = {
              "synthetic 1,000 cells x 5,700 500kb bins HSCN, maxCN=11, binomial (BASELINE configs[1])"),
     "cfg3": (10000, "5700", "ascn", "betabinomial", 0.02, 20260003,
              "synthetic 10,000 cells x 5,700 bins ASCN beta-binomial rho=0.02 (BASELINE configs[2])"),
+    # the two large configs are generated as 2,000 distinct cells tiled up to size (same value distributions)
+    "cfg4": (50000, "5700", "hscn", "binomial", 0.0, 20260004,
+             "synthetic 50,000 cells x 5,700 bins HSCN binomial, cells split over the ranks (BASELINE configs[3])"),
+    "cfg5": (20000, "30000", "hscn", "binomial", 0.0, 20260005,
+             "synthetic 20,000 cells x 30,000 100kb bins HSCN binomial, cells split over the ranks (BASELINE configs[4])"),
 }
+BIG = {"cfg4", "cfg5"}
 PARAMS = dict(n_states=12, loherror=0.02, eps=1e-12, Abias=0.0, selftransitionprob=0.95)
 F_BIN = {("hscn", "binomial"): 303, ("hscn", "betabinomial"): 404, ("ascn", "binomial"): 303, ("ascn", "betabinomial"): 404}
 F_STATE = {("hscn", "binomial"): 99, ("hscn", "betabinomial"): 300, ("ascn", "binomial"): 198, ("ascn", "betabinomial"): 600}
@@ -46,7 +52,19 @@ def make_data(name, rank=0):
     from signals_b200 import synth
     n_cells, lens, model, lik, rho, seed, desc = WORKLOADS[name]
     lens = synth.LENS_5700 if lens == "5700" else synth.LENS_30000
-    d = synth.make_cohort(n_cells, lens=lens, seed=seed + 1000 * rank, likelihood=lik)
+    if name not in BIG:
+        return synth.make_cohort(n_cells, lens=lens, seed=seed + 1000 * rank, likelihood=lik)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    mine = n_cells // world                       # these two configs fix the TOTAL number of cells
+    base = min(2000, mine)
+    reps = max(1, mine // base)
+    b = synth.make_cohort(base, lens=lens, seed=seed + 1000 * rank, likelihood=lik)
+    d = dict(b)
+    for k in ("n", "x", "cn", "truth_b"):
+        d[k] = np.tile(b[k], reps)
+    per = int(b["seg_off"][-1])
+    d["seg_off"] = np.concatenate([b["seg_off"][:-1] + r * per for r in range(reps)] + [np.array([reps * per])]).astype(np.int64)
+    d["n_cells"] = base * reps
     return d
 
 
@@ -313,11 +331,14 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     n_cells, lens, model, lik, rho, seed, desc = WORKLOADS[a.workload]
-    config = {"workload": desc, "cells_per_gpu": n_cells, "bins_per_cell": 5700, "sequences_per_cell": 23,
+    if a.workload in BIG:
+        n_cells = n_cells // max(world, 1)
+    bins_per_cell = 5700 if lens == "5700" else 30000
+    config = {"workload": desc, "cells_per_gpu": n_cells, "bins_per_cell": bins_per_cell, "sequences_per_cell": 23,
               "maxCN": 11, "n_states": 12, "likelihood": lik, "model": model.upper(), "selftransitionprob": 0.95,
               "loherror": 0.02, "eps": 1e-12, "rho": rho, "sharding": "cells, %d rank(s), 1 GPU each" % max(world, 1),
-              "l2": "inputs (%d MB per GPU) %s" % (n_cells * 5700 * 9 // 1000000,
-                                                   "larger than L2; no explicit flush" if n_cells * 5700 * 9 > 200e6
+              "l2": "inputs (%d MB per GPU) %s" % (n_cells * bins_per_cell * 9 // 1000000,
+                                                   "larger than L2; no explicit flush" if n_cells * bins_per_cell * 9 > 200e6
                                                    else "fit in L2: 256 MB flush write between individually timed steps")}
 
     if a.impl == "reference":
@@ -381,15 +402,15 @@ def main():
                         "algorithmic_bytes_per_cell_bin": 10}}
     line = {"metric": "cell_bins_per_sec", "value": main_res["value"], "unit": "cell-bins/s", "n_gpus": world,
             "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": main_res["ms_per_step"], "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
-            "clocks": clocks, "e2e": main_res.get("e2e"), "gpu_launches": main_res["launches_per_step"] * a.steps, "gather": main_res["gather"],
+            "scaling": "strong" if a.workload in BIG else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config, "clocks": clocks, "e2e": main_res.get("e2e"), "gpu_launches": main_res["launches_per_step"] * a.steps, "gather": main_res["gather"],
             "gpu_kernels_per_step": ["k_setup", "k_pack", "k_decode"], "roofline": roofline,
-            "scratch_bytes": main_res["scratch_bytes"]}
+            "scratch_bytes": main_res["scratch_bytes"], "torch_peak_device_bytes": int(torch.cuda.max_memory_allocated())}
 
     if rank == 0 and world == 1 and not a.no_extras:
         others = {}
         for nm in sorted(WORKLOADS):
-            if nm == a.workload:
+            if nm == a.workload or nm in BIG:
                 continue
             dd = make_data(nm)
             r = gpu_measure(nm, dd, max(5, a.steps // 2), 3, 0, 1, None, sampler, want_e2e=True)
