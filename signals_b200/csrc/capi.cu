@@ -299,14 +299,22 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
     SGB_CUDA(sgbk_setup(C->d_tabs, m, P->eps, P->Abias, P->selftransitionprob, C->main));
     SGB_CUDA(cudaEventRecord(C->ev_setup, C->main));
     const long long target = chunk_bins_target();
+    const bool explicit_chunk = getenv("SGB_CHUNK_BINS") != nullptr;      // tests pin the chunk size exactly
     const int S = m.S;
     int k = 0;
     int64_t s0 = s_begin;
     while (s0 < s_end) {
         int64_t s1 = s0;
         long long bins = 0;
-        while (s1 < s_end && (bins == 0 || bins + (seg_off[s1 + 1] - seg_off[s1]) <= target)) {
-            bins += seg_off[s1 + 1] - seg_off[s1];
+        // a chunk should (a) be big enough to amortise launches and (b) hold enough sequences to give every
+        // resident warp of the device a group (long sequences need more bins for that), within a memory cap
+        const long long seq_target = explicit_chunk ? 0 : (long long)C->sm_count * 16 * 32;
+        const long long bins_cap = explicit_chunk ? target : (128ll << 20);
+        while (s1 < s_end) {
+            const long long L = seg_off[s1 + 1] - seg_off[s1];
+            if (bins > 0 && bins + L > bins_cap) break;
+            if (bins > 0 && bins + L > target && (s1 - s0) >= seq_target) break;
+            bins += L;
             s1++;
         }
         Slot& SL = C->slot[k & 1];
