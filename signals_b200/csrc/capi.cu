@@ -308,7 +308,7 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
         long long bins = 0;
         // a chunk should (a) be big enough to amortise launches and (b) hold enough sequences to give every
         // resident warp of the device a group (long sequences need more bins for that), within a memory cap
-        const long long seq_target = explicit_chunk ? 0 : (long long)C->sm_count * 16 * 32;
+        const long long seq_target = explicit_chunk ? 0 : (long long)C->sm_count * 8 * 32;      // half a wave of warps
         const long long bins_cap = explicit_chunk ? target : (128ll << 20);
         while (s1 < s_end) {
             const long long L = seg_off[s1 + 1] - seg_off[s1];
