@@ -198,6 +198,28 @@ static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb, i
     return d * sizeof(double) + ((size_t)SGB_CN_TABLE * S + SGB_CN_TABLE) * sizeof(int);
 }
 
+// Rare variant of the recursion (selftransitionprob below 1/S, so tr_self < tr_off), kept out of line so it
+// does not sit in the hot loop's instruction footprint.  Returns the decoded state of the previous bin.
+// Its two running maxima live in the padding slot of the lane's T1 / E columns (index SMAX), the argmax travels
+// in the return value (back | i1 << 8), so the hot path carries no extra registers for it.
+template <int SMAX>
+__device__ __noinline__ int decode_step_general(double* colT, double* colE, int S, double init, double tr_self,
+                                                double tr_off, int i1_in, int first)
+{
+    SgbSeqState<SMAX> st;
+    double e[SMAX];
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) { e[i] = colE[i]; st.T1[i] = colT[i]; }
+    st.m1 = colT[SMAX]; st.m2 = colE[SMAX]; st.i1 = i1_in;
+    int back = 0;
+    if (first) sgb_seq_init<SMAX>(st, e, S, init);
+    else back = sgb_seq_step_general<SMAX>(st, e, S, tr_self, tr_off);
+#pragma unroll
+    for (int i = 0; i < SMAX; i++) colT[i] = st.T1[i];
+    colT[SMAX] = st.m1; colE[SMAX] = st.m2;
+    return back | (st.i1 << 8);
+}
+
 // Fused emission + forward recursion + decode.  One lane per (cell, chromosome) sequence, 32 sequences
 // of similar length per warp, warps fetch groups from a global counter (longest first).
 // The kernel is bound by shared-memory bandwidth and FP64 issue, so per bin step a warp
@@ -412,8 +434,9 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                                                          LIKBB ? gLGK + (long)t1 * 2 * SGB_LGK : sLT, sp, sLT, sET, r0, r1);
                     } else {
                         const int bi0 = bI[ol0], bi1 = bI[ol1];
-                        r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
-                        r1 = v1 ? sgb_emit_item<MODEL, LIKBB>(bi1 & 0xffff, bi1 >> 16, d1.x, d1.y, lx1, ly1, gs1, mm1, TB, sp) : 0.0;
+                        // rare: keep the hot loop small -- the out-of-line general path handles lean items too (same bits)
+                        r0 = sgb_emit_item_slow<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
+                        r1 = v1 ? sgb_emit_item_slow<MODEL, LIKBB>(bi1 & 0xffff, bi1 >> 16, d1.x, d1.y, lx1, ly1, gs1, mm1, TB, sp) : 0.0;
                     }
                     myE[ol0 * P + m0] = r0;
                     if (v1) myE[ol1 * P + mm1] = r1;
@@ -439,7 +462,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                                                              LIKBB ? gLGK + (long)t0 * 2 * SGB_LGK : sLT, sp, sLT, sET);
                     } else {
                         const int bi0 = bI[ol0];
-                        r0 = sgb_emit_item<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
+                        r0 = sgb_emit_item_slow<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
                     }
                     if (v0) myE[ol0 * P + m0] = r0;
                     base += 32;
@@ -459,8 +482,18 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                         A.state_out[ostart + t - 1] = (uint8_t)back;
                         if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
                     }
+                } else if (CHAINED == 0) {
+                    // general transition (selftransitionprob < 1/S)
+                    const int bi = decode_step_general<SMAX>(colT, colE, S, sp.init, sp.tr_self, sp.tr_off, i1, t == 0);
+                    back = bi & 0xff; i1 = bi >> 8;
+                    if (t == 0) {
+                        if (len == 1) A.state_out[ostart] = 0;
+                    } else {
+                        A.state_out[ostart + t - 1] = (uint8_t)back;
+                        if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
+                    }
                 } else {
-                    // general transition (selftransitionprob < 1/S) or chained decode: register-resident step
+                    // chained decode: register-resident step, backpointers of every state to global scratch
                     SgbSeqState<SMAX> st;
                     double e[SMAX];
 #pragma unroll
@@ -468,11 +501,6 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     st.m1 = m1; st.m2 = m2; st.i1 = i1;
                     if (t == 0) {
                         sgb_seq_init<SMAX>(st, e, S, sp.init);
-                        if (CHAINED == 0 && len == 1) A.state_out[ostart] = 0;
-                    } else if (CHAINED == 0) {
-                        back = sgb_seq_step<SMAX>(st, e, colE, 1, S, sp.tr_self, sp.tr_off, 0);
-                        A.state_out[ostart + t - 1] = (uint8_t)back;
-                        if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
                     } else {
                         unsigned char bpv[SMAX];
                         sgb_seq_step_chained<SMAX>(st, e, S, sp.tr_self, sp.tr_off, bpv);
