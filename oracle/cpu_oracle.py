@@ -10,7 +10,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "liboracle.so")
 
-MATH_LIBM, MATH_DET = 0, 1
+MATH_LIBM, MATH_DET, MATH_RMATH = 0, 1, 2
 MODEL_HSCN, MODEL_ASCN = 0, 1
 LIK_BINOMIAL, LIK_BETABINOMIAL = 0, 1
 DECODE_REFERENCE, DECODE_CHAINED = 0, 1

@@ -29,6 +29,10 @@
  *   ORC_MATH_DET  (1): the deterministic functions of signals_b200/csrc/sgb_math.h
  *                      (header-only, shared with the device) so that emissions and
  *                      therefore state paths are bit-identical to the CUDA kernels.
+ *   ORC_MATH_RMATH (2): like LIBM, but the binomial log-density is computed the way base R does
+ *                      (nmath/dbinom.c dbinom_raw with bd0 and stirlerr, C. Loader 2000), restated from the
+ *                      published algorithm -- used to show that the lgamma form stays within the 1e-9
+ *                      tolerance of what stats::dbinom itself returns.
  * The emission logic itself (probabilities, masks, special cases, recursion,
  * decode rule) is written here independently of the CUDA code.
  */
@@ -42,6 +46,7 @@
 
 #define ORC_MATH_LIBM 0
 #define ORC_MATH_DET 1
+#define ORC_MATH_RMATH 2   /* binomial density by R's own algorithm (Loader's saddle-point dbinom_raw); rest as LIBM */
 #define ORC_MODEL_HSCN 0
 #define ORC_MODEL_ASCN 1
 #define ORC_LIK_BINOMIAL 0
@@ -114,6 +119,68 @@ int orc_selftest(void)
     return (unfused == 0.0 && fused != 0.0) ? 0 : 1;
 }
 
+/* ------------------------------------------------------------------ R's dbinom_raw (restated) */
+/* stirlerr(n) = log(n!) - log( sqrt(2 pi n) (n/e)^n ); exact table for n = 0, 0.5, ..., 15 (generated with
+ * 60-digit mpmath), Stirling series above (nmath/stirlerr.c). */
+static const double ORC_SFERR_HALVES[31] = {
+    0x0.0p+0, 0x1.3a37a020b8c22p-3, 0x1.4c071bcda0a5bp-4, 0x1.c1098b28dcf33p-5, 0x1.52a9b923ea649p-5,
+    0x1.0fab9626b44ffp-5, 0x1.c579a268d80b3p-6, 0x1.850ea113caf0ep-6, 0x1.54a2662fd78a9p-6, 0x1.2eea2e990f134p-6,
+    0x1.10b4e513fcbedp-6, 0x1.eff15b81c9cc5p-7, 0x1.c6b167bebdf36p-7, 0x1.a3c5f8a1e7d1dp-7, 0x1.85d4d612e4a86p-7,
+    0x1.6bdfcc7fbdb0ap-7, 0x1.552805e7b3076p-7, 0x1.411b75e41049cp-7, 0x1.2f4871b12ab64p-7, 0x1.1f553026fbce1p-7,
+    0x1.10f9d4c0743a7p-7, 0x1.03fc2d49c8fb9p-7, 0x1.f0593088014f8p-8, 0x1.dac773cc5b3cdp-8, 0x1.c7018733aa9c6p-8,
+    0x1.b4d04a067629fp-8, 0x1.a40514700f36cp-8, 0x1.947826547fe6cp-8, 0x1.86076c002d4a7p-8, 0x1.789583ffc5e8cp-8,
+    0x1.6c08f6f194a10p-8};
+
+static double orc_stirlerr(double n)
+{
+    const double S0 = 1.0 / 12.0, S1 = 1.0 / 360.0, S2 = 1.0 / 1260.0, S3 = 1.0 / 1680.0, S4 = 1.0 / 1188.0;
+    if (n <= 15.0) {
+        double nn = n + n;
+        if (nn == (double)(int)nn) return ORC_SFERR_HALVES[(int)nn];
+        return lgamma(n + 1.0) - (n + 0.5) * log(n) + n - 0.918938533204672741780329736406; /* log(sqrt(2 pi)) */
+    }
+    double nn = n * n;
+    if (n > 500) return (S0 - S1 / nn) / n;
+    if (n > 80) return (S0 - (S1 - S2 / nn) / nn) / n;
+    if (n > 35) return (S0 - (S1 - (S2 - S3 / nn) / nn) / nn) / n;
+    return (S0 - (S1 - (S2 - (S3 - S4 / nn) / nn) / nn) / nn) / n;
+}
+
+/* bd0(x, np) = x log(x/np) + np - x, evaluated without cancellation when x ~ np (nmath/bd0.c) */
+static double orc_bd0(double x, double np)
+{
+    if (fabs(x - np) < 0.1 * (x + np)) {
+        double v = (x - np) / (x + np);
+        double s = (x - np) * v;
+        if (fabs(s) < 2.2250738585072014e-308) return s;
+        double ej = 2 * x * v;
+        v = v * v;
+        for (int j = 1; j < 1000; j++) {
+            ej *= v;
+            double s1 = s + ej / ((j << 1) + 1);
+            if (s1 == s) return s1;
+            s = s1;
+        }
+    }
+    return x * log(x / np) + np - x;
+}
+
+/* dbinom_raw(x, n, p, q, give_log = TRUE) (nmath/dbinom.c) */
+static double orc_dbinom_raw_log(double x, double n, double p, double q)
+{
+    if (p == 0) return x == 0 ? 0.0 : -INFINITY;
+    if (q == 0) return x == n ? 0.0 : -INFINITY;
+    if (x == 0) {
+        if (n == 0) return 0.0;
+        return (p < 0.1) ? -orc_bd0(n, n * q) - n * p : n * log(q);
+    }
+    if (x == n) return (q < 0.1) ? -orc_bd0(n, n * p) - n * q : n * log(p);
+    if (x < 0 || x > n) return -INFINITY;
+    double lc = orc_stirlerr(n) - orc_stirlerr(x) - orc_stirlerr(n - x) - orc_bd0(x, n * p) - orc_bd0(n - x, n * q);
+    double lf = 1.837877066409345483560659472811 /* log(2 pi) */ + log(x) + log1p(-x / n);
+    return lc - 0.5 * lf;
+}
+
 /* ------------------------------------------------------------------ emission densities */
 /* stats::dbinom(k, n, p, log=TRUE) restated: argument checks in R's order
  * (p outside [0,1] or NaN -> NaN; k outside 0..n -> -Inf; p==0 / p==1 limits). */
@@ -123,6 +190,7 @@ static double orc_dbinom_log(int64_t k, int64_t n, double p, int math)
     if (k < 0 || k > n) return -INFINITY;
     if (p == 0.0) return k == 0 ? 0.0 : -INFINITY;
     if (p == 1.0) return k == n ? 0.0 : -INFINITY;
+    if (math == ORC_MATH_RMATH) return orc_dbinom_raw_log((double)k, (double)n, p, 1.0 - p);
     double lc = (m_logfact(n, math) - m_logfact(k, math)) - m_logfact(n - k, math);
     return m_combine(lc, (double)k, m_log(p, math), (double)(n - k), m_log1p(-p, math), math);
 }

@@ -146,6 +146,38 @@ def test_densities_vs_mpmath(oracle):
     assert worst[1] < 5e-12      # keep an eye on the deterministic flavour's real accuracy
 
 
+def test_lgamma_form_matches_r_style_saddle_point_dbinom(oracle):
+    """stats::dbinom is Loader's saddle-point algorithm (bd0 / stirlerr), not an lgamma formula: the oracle's
+    restatement of it (flavour RMATH) and the lgamma forms used everywhere else agree far inside 1e-9"""
+    rng = np.random.default_rng(44)
+    P = oracle.params(S=12, eps=0.0, loherror=0.02)
+    worst_rel = 0.0
+    for _ in range(400):
+        c = int(rng.integers(1, 12))
+        n = int(max(1, round(c * rng.gamma(1.76, 1 / 0.09))))
+        x = int(rng.binomial(n, rng.uniform(0.02, 0.98)))
+        lr = oracle.emission([n], [x], [c], P, oracle.MATH_RMATH)[0]
+        for m in (oracle.MATH_LIBM, oracle.MATH_DET):
+            l = oracle.emission([n], [x], [c], P, m)[0]
+            fin = np.isfinite(lr)
+            assert np.array_equal(np.isfinite(l), fin)
+            worst_rel = max(worst_rel, float(np.max(np.abs(l[fin] - lr[fin]) / np.maximum(np.abs(lr[fin]), 1e-3))))
+        # and the saddle-point restatement itself against 50-digit arithmetic
+        for s in range(min(c, 11) + 1):
+            p = s / c + (0.02 if 2 * s < c else -0.02 if 2 * s > c else 0.0)
+            t = float(onp.dbinom_log_mp(x, n, p))
+            assert abs(lr[s] - t) <= 4e-14 * max(1.0, abs(t)), (n, x, c, s)
+    assert worst_rel < 1e-11
+    # paths decoded from the R-style densities differ from the lgamma ones only at structural ties (CN 0)
+    d = cases.small_cohort("binomial", n_cells=20, seed=6)
+    cn = d["cn"].astype(np.int32)
+    Pd = oracle.params(S=12, selftransitionprob=0.95)
+    a = oracle.decode_batch(d["n"], d["x"], cn, d["seg_off"], Pd, oracle.MATH_RMATH, nthreads=4)
+    b = oracle.decode_batch(d["n"], d["x"], cn, d["seg_off"], Pd, oracle.MATH_DET, nthreads=4)
+    diff = np.nonzero(a != b)[0]
+    assert diff.size < 1e-3 * a.size and (cn[diff] == 0).all()
+
+
 def test_libm_and_det_flavours_agree_except_structural_ties(oracle):
     d = cases.small_cohort("binomial", n_cells=30, seed=5)
     P = oracle.params(S=12, selftransitionprob=0.95)
