@@ -180,12 +180,12 @@ __device__ __forceinline__ void sgb_mbar_wait(unsigned long long* bar, unsigned 
 //   T1 [32][P]  forward column of every lane's sequence
 //   bD/bL/bG    per-lane bin fields for the item queue ({x, n-x}, log-choose terms, lgamma(s+n))
 //   bI [32]     cprime | in_support << 16
-//   q           work queue, SMAX*32 uint16 entries
+//   q           work queue, SMAX*32 uint32 entries (pre-scaled offsets, see below)
 //   stage       2 x SGB_CH x 32 records + 2 mbarriers (TMA staging only)
 static inline size_t decode_warp_doubles(int SMAX, int model, int lik_bb, int stage)
 {
     const size_t P = (size_t)SMAX + 1;
-    size_t d = 2 * 32 * P + 16 + (size_t)SMAX * 8;
+    size_t d = 2 * 32 * P + 16 + (size_t)SMAX * 16;
     d += 64 + (model == SGB_MODEL_ASCN ? 64 : 32) + (lik_bb ? 32 : 0);
     if (stage == SGB_STAGE_TMA) d += 2 * 32 * SGB_CH + 2;
     return (d + 1) & ~(size_t)1;
@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     const int CTS = SGB_CN_TABLE * S;
     constexpr int P = SMAX + 1;
     constexpr int NL = (MODEL == SGB_MODEL_ASCN) ? 64 : 32;
-    constexpr int WD0 = 2 * 32 * P + 16 + SMAX * 8 + 64 + NL + (LIKBB ? 32 : 0) +
+    constexpr int WD0 = 2 * 32 * P + 16 + SMAX * 16 + 64 + NL + (LIKBB ? 32 : 0) +
                         (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_CH + 2 : 0);
     constexpr int WARP_DOUBLES = (WD0 + 1) & ~1;
     double* sLT = smem;
@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     double* bL = (double*)(bD + 32);                          // HSCN lcx[32]; ASCN {lcx, lcy}[32]
     double* bG = bL + NL;                                     // beta-binomial: lgamma(s+n)[32]
     int* bI = (int*)(bG + (LIKBB ? 32 : 0));                  // cprime | in_support << 16
-    unsigned short* q = (unsigned short*)(bI + 32);
+    unsigned int* q = (unsigned int*)(bI + 32);
     unsigned long long* stg = (unsigned long long*)(q + SMAX * 32);     // [2][SGB_CH][32] records
     unsigned long long* bar = stg + 2 * 32 * SGB_CH;                    // [2] mbarriers
     if (STAGE == SGB_STAGE_TMA && lane == 0) {
@@ -380,7 +380,9 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 Lprev = L;
             }
             const int Lw = __reduce_max_sync(SGB_FULL, L);
-            // ---- (2) queue of live (lane, state) pairs: lane | lean << 5 | state << 6 | cprime << 11
+            // ---- (2) queue of live (lane, state) pairs.  Entry (32 bit): E-tile index lane*P + state (bits 0-11) |
+            //      table row cprime*S + state (bits 12-21) | lane (bits 22-26) | lean-path flag (bit 27): every
+            //      address an item needs is one shift/mask away, and consecutive states differ by a constant.
             unsigned need = 0;          // bit m: state m of this lane's bin is queued
             if (act) {
                 bD[lane] = make_double2(kd, nkd);
@@ -399,12 +401,13 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
             }
             const int tot = __shfl_sync(SGB_FULL, incl, 31);
             {
-                int qpos = incl - cnt;
-                const int allfast = ((fastmask & need) == need) ? 32 : 0;
-                const int ebase = lane | allfast | (((cprime < SGB_CN_TABLE) ? cprime : 0) << 11);
+                const int qpos = incl - cnt;
+                const unsigned allfast = ((fastmask & need) == need) ? (1u << 27) : 0u;
+                const unsigned trow = (cprime < SGB_CN_TABLE) ? (unsigned)(cprime * S) : 0u;
+                const unsigned ebase = (unsigned)(lane * P) | (trow << 12) | ((unsigned)lane << 22) | allfast;
 #pragma unroll
                 for (int m = 0; m < SMAX; m++)
-                    if (m < L) q[qpos + m] = (unsigned short)(ebase + (m << 6));
+                    if (m < L) q[qpos + m] = ebase + (unsigned)m * 0x1001u;
             }
             __syncwarp();
             // ---- (3) the queue: two entries per lane per round while more than 32 remain, else one
@@ -413,9 +416,10 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 if (remaining > 32) {
                     const int j0 = base + lane, j1 = j0 + 32;
                     const bool v1 = j1 < tot;
-                    const int en0 = q[j0], en1 = q[v1 ? j1 : j0];
-                    const int ol0 = en0 & 31, m0 = (en0 >> 6) & 31, ol1 = en1 & 31, mm1 = (en1 >> 6) & 31;
-                    const int t0 = (en0 >> 11) * S + m0, t1 = (en1 >> 11) * S + mm1;
+                    const unsigned en0 = q[j0], en1 = q[v1 ? j1 : j0];
+                    const int ol0 = (en0 >> 22) & 31, ol1 = (en1 >> 22) & 31;
+                    const int e0 = en0 & 0xfff, e1 = en1 & 0xfff;               // E-tile indices
+                    const int t0 = (en0 >> 12) & 0x3ff, t1 = (en1 >> 12) & 0x3ff;     // table rows
                     const double2 d0 = bD[ol0], d1 = bD[ol1];
                     double lx0, ly0 = 0.0, lx1, ly1 = 0.0;
                     if (MODEL == SGB_MODEL_ASCN) {
@@ -426,7 +430,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     }
                     const double gs0 = LIKBB ? bG[ol0] : 0.0, gs1 = LIKBB ? bG[ol1] : 0.0;
                     double r0, r1;
-                    if (en0 & en1 & 32) {
+                    if (en0 & en1 & (1u << 27)) {
                         sgb_emission_fast2<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
                                                          LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, d1.x, d1.y, lx1, ly1, gs1,
                                                          sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0, LIKBB ? sB[t1] : 0.0,
@@ -435,17 +439,16 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     } else {
                         const int bi0 = bI[ol0], bi1 = bI[ol1];
                         // rare: keep the hot loop small -- the out-of-line general path handles lean items too (same bits)
-                        r0 = sgb_emit_item_slow<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
-                        r1 = v1 ? sgb_emit_item_slow<MODEL, LIKBB>(bi1 & 0xffff, bi1 >> 16, d1.x, d1.y, lx1, ly1, gs1, mm1, TB, sp) : 0.0;
+                        r0 = sgb_emit_item_slow<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, e0 - ol0 * P, TB, sp);
+                        r1 = v1 ? sgb_emit_item_slow<MODEL, LIKBB>(bi1 & 0xffff, bi1 >> 16, d1.x, d1.y, lx1, ly1, gs1, e1 - ol1 * P, TB, sp) : 0.0;
                     }
-                    myE[ol0 * P + m0] = r0;
-                    if (v1) myE[ol1 * P + mm1] = r1;
+                    myE[e0] = r0;
+                    if (v1) myE[e1] = r1;
                     base += 64;
                 } else {
                     const bool v0 = lane < remaining;
-                    const int en0 = q[v0 ? base + lane : base];
-                    const int ol0 = en0 & 31, m0 = (en0 >> 6) & 31;
-                    const int t0 = (en0 >> 11) * S + m0;
+                    const unsigned en0 = q[v0 ? base + lane : base];
+                    const int ol0 = (en0 >> 22) & 31, e0 = en0 & 0xfff, t0 = (en0 >> 12) & 0x3ff;
                     const double2 d0 = bD[ol0];
                     double lx0, ly0 = 0.0;
                     if (MODEL == SGB_MODEL_ASCN) {
@@ -456,15 +459,15 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     }
                     const double gs0 = LIKBB ? bG[ol0] : 0.0;
                     double r0;
-                    if (en0 & 32) {
+                    if (en0 & (1u << 27)) {
                         r0 = sgb_emission_fast<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
                                                              LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0,
                                                              LIKBB ? gLGK + (long)t0 * 2 * SGB_LGK : sLT, sp, sLT, sET);
                     } else {
                         const int bi0 = bI[ol0];
-                        r0 = sgb_emit_item_slow<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, m0, TB, sp);
+                        r0 = sgb_emit_item_slow<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, e0 - ol0 * P, TB, sp);
                     }
-                    if (v0) myE[ol0 * P + m0] = r0;
+                    if (v0) myE[e0] = r0;
                     base += 32;
                 }
             }
