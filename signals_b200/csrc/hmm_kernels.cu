@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
         if (STAGE == SGB_STAGE_TMA) {
             if (Tmax > 0) issue_chunk(0);
         } else {
-            rec_next = (Tmax > 0) ? __ldg(gtile + lane) : 0ull;
+            rec_next = (Tmax > 0) ? __ldcs(gtile + lane) : 0ull;
         }
         int back = 0;
         int Lprev = SMAX;          // states >= L hold -Inf in this lane's E column; refreshed when L shrinks
@@ -354,7 +354,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 rec = stg[((ci & 1) * SGB_CH + w) * 32 + lane];
             } else {
                 rec = rec_next;
-                if (t + 1 < Tmax) rec_next = __ldg(gtile + (long long)(t + 1) * 32 + lane);
+                if (t + 1 < Tmax) rec_next = __ldcs(gtile + (long long)(t + 1) * 32 + lane);
             }
             // ---- (1) per-bin quantities of this lane's sequence
             int L = 0, cprime = 0, ins = 0, fastmask = 0;
