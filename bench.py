@@ -4,7 +4,7 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload target|cfg2|cfg3] [--impl reference]
 
 A "step" is one pass of the hot path over one batch of synthetic DLP-shaped cell-bins.
-  value     cell-bins/s with inputs already resident in HBM (k_setup + k_pack + k_decode [+ NCCL gather of
+  value     cell-bins/s with inputs already resident in HBM (k_setup + k_pack + k_decode [+ all-gather of
             the uint8 state paths when N > 1]); CUDA events on the launch stream, max over ranks
   e2e       the same metric through the host-buffer C-ABI call sgb_hmm_decode: pinned host inputs are
             copied to the device, decoded, and the state paths copied back, every step
@@ -191,17 +191,25 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
 
         def step():
             plan.decode(P, tn, tx, tc, out, stream=stream)
+
+        def drain():
+            pass
     else:
         # Cells are independent: each rank decodes its own shard; the only exchange is the gather of the uint8
         # paths.  Preferred: every rank PUSHES its slice into all peers' gather buffers with copy-engine (DMA)
-        # copies over NVLink (symmetric memory, no SMs involved) and one barrier closes the step.  (Splitting the
-        # shard in halves to overlap the first half's transfer with the second half's decode was measured and
-        # lost more to the second kernel tail than it hid.)  Fallback: NCCL all-gather.
+        # copies over NVLink (symmetric memory, no SMs involved) and one barrier closes the exchange.  The push of
+        # step k runs on a side stream into the gather buffer of parity k&1, so it overlaps the decode of step
+        # k+1 (which writes the other buffer); the timed region ends only after the last push and its barrier.
+        # (Splitting ONE step's shard in halves to overlap inside a step was measured and lost more to the second
+        # kernel tail than it hid.)  BENCH_GATHER=p2p_serial keeps push and decode back to back on one stream;
+        # BENCH_GATHER=nccl, or symmetric memory being unavailable, uses NCCL all-gather.
         plan = hmm.DevicePlan(N, so, n_states=PARAMS["n_states"])
         plan.enable_timing(True)
         plans = [plan]
         hdl = None
-        if os.environ.get("BENCH_GATHER", "p2p") == "p2p":
+        want = os.environ.get("BENCH_GATHER", "p2p")
+        nbuf = 1 if want == "p2p_serial" else 2
+        if want in ("p2p", "p2p_serial"):
             try:
                 import torch.distributed._symmetric_memory as symm_mem
                 if hasattr(symm_mem, "enable_symm_mem_for_group"):
@@ -209,30 +217,59 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                         symm_mem.enable_symm_mem_for_group(dist.group.WORLD.group_name)
                     except Exception:
                         pass
-                gathered = symm_mem.empty(N * world, dtype=torch.uint8, device=dev)
-                hdl = symm_mem.rendezvous(gathered, dist.group.WORLD)
-                peers = [hdl.get_buffer(r, (N * world,), torch.uint8) for r in range(world)]
-                gather_mode = "p2p_dma_push"
+                gathered_all = symm_mem.empty(nbuf * N * world, dtype=torch.uint8, device=dev)
+                hdl = symm_mem.rendezvous(gathered_all, dist.group.WORLD)
+                peers = [hdl.get_buffer(r, (nbuf * N * world,), torch.uint8) for r in range(world)]
+                gather_mode = "p2p_dma_push" if nbuf == 1 else "p2p_dma_push_pipelined"
             except Exception as ex:          # symmetric memory unavailable: NCCL path below
                 hdl = None
                 sys.stderr.write("symmetric memory unavailable (%s); using NCCL all_gather\n" % ex)
         if hdl is None:
-            gathered = torch.empty(N * world, dtype=torch.uint8, device=dev)
+            nbuf = 1
+            gathered_all = torch.empty(N * world, dtype=torch.uint8, device=dev)
             gather_mode = "nccl_all_gather"
-        out = gathered[rank * N: (rank + 1) * N] if hdl is not None else torch.zeros(N, dtype=torch.uint8, device=dev)
+        W = N * world
+        outs = [gathered_all[b * W + rank * N: b * W + (rank + 1) * N] for b in range(nbuf)] if hdl is not None \
+            else [torch.zeros(N, dtype=torch.uint8, device=dev)]
+        side = torch.cuda.Stream(device=dev) if nbuf == 2 else None
+        ev_dec = [torch.cuda.Event() for _ in range(nbuf)]
+        ev_push = [None] * nbuf
+        step_no = [0]
+
+        def push(b):
+            for k in range(1, world):
+                r = (rank + k) % world
+                peers[r][b * W + rank * N: b * W + (rank + 1) * N].copy_(outs[b], non_blocking=True)
+            hdl.barrier()
 
         def step():
-            plan.decode(P, tn, tx, tc, out, stream=stream)
-            if hdl is not None:
-                for k in range(1, world):
-                    r = (rank + k) % world
-                    peers[r][rank * N: (rank + 1) * N].copy_(out, non_blocking=True)
-                hdl.barrier()
+            b = step_no[0] % nbuf
+            step_no[0] += 1
+            if hdl is None:
+                plan.decode(P, tn, tx, tc, outs[0], stream=stream)
+                dist.all_gather_into_tensor(gathered_all, outs[0])
+            elif side is None:
+                plan.decode(P, tn, tx, tc, outs[0], stream=stream)
+                push(0)
             else:
-                dist.all_gather_into_tensor(gathered, out)
+                if ev_push[b] is not None:
+                    torch.cuda.current_stream().wait_event(ev_push[b])      # the push that last read outs[b] is done
+                plan.decode(P, tn, tx, tc, outs[b], stream=stream)
+                ev_dec[b].record()
+                with torch.cuda.stream(side):
+                    side.wait_event(ev_dec[b])
+                    push(b)
+                    ev_push[b] = torch.cuda.Event()
+                    ev_push[b].record()
+
+        def drain():
+            # joins the side stream: every gather issued so far has landed on every rank
+            if side is not None:
+                torch.cuda.current_stream().wait_stream(side)
 
     for _ in range(max(warmup, 3)):
         step()
+    drain()
     for pl in plans:
         pl.check(stream)
     torch.cuda.synchronize()
@@ -247,6 +284,7 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         e0.record()
         for _ in range(steps):
             step()
+        drain()
         e1.record()
         torch.cuda.synchronize()
         elapsed = e0.elapsed_time(e1)
@@ -256,7 +294,7 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         for _ in range(steps):
             flush.fill_(1)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(); step(); e1.record()
+            e0.record(); step(); drain(); e1.record()
             torch.cuda.synchronize()
             elapsed += e0.elapsed_time(e1)
         del flush
@@ -269,6 +307,10 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
     total_ms = float(ms.item())
     for pl in plans:
         pl.check(stream)
+    if world > 1:
+        last = (step_no[0] - 1) % nbuf          # the buffer the last step decoded into and gathered
+        out = outs[last]
+        gathered = gathered_all[last * W: (last + 1) * W]
     pack_ms = sum(float(pl.read_timing(64)[0].mean()) for pl in plans)
     decode_ms = sum(float(pl.read_timing(64)[1].mean()) for pl in plans)      # one launch per plan per step
     res = dict(ms_per_step=total_ms / steps, value=N * world * steps / (total_ms * 1e-3),
@@ -363,9 +405,21 @@ def main():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dist = None
+    numa_bound = False
     if world > 1:
+        # several ranks stream pinned host buffers at once: keep this rank's threads (and so its first-touch
+        # pinned pages) on the CPUs NVML reports as local to its GPU.  Best effort; N=1 keeps every core.
+        if os.environ.get("BENCH_NUMA", "1") == "1":
+            try:
+                import pynvml
+                pynvml.nvmlInit()
+                pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
+                numa_bound = True
+            except Exception as ex:
+                sys.stderr.write("rank %d: no NUMA binding (%s)\n" % (rank, ex))
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    config["host_numa_binding"] = numa_bound
     from signals_b200 import _lib, hmm
     lib = _lib.load()
     hmm.check(lib.sgb_init(local_rank))
