@@ -341,6 +341,8 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
         int back = 0;
         int Lprev = SMAX;          // states >= L hold -Inf in this lane's E column; refreshed when L shrinks
         int Lw_prev = SMAX;        // warp-wide maximum live-state count of the previous bin
+        int Lw = 0, tot = 0;       // ... of the current bin, and the length of the item queue (both kept while it is reused)
+        int prev_key = -1;         // (copy number, validity, active) the queue entries of this lane were built from
         for (int t = 0; t < Tmax; t++) {
             const bool act = t < len;
             unsigned long long rec;
@@ -357,7 +359,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 if (t + 1 < Tmax) rec_next = __ldcs(gtile + (long long)(t + 1) * 32 + lane);
             }
             // ---- (1) per-bin quantities of this lane's sequence
-            int L = 0, cprime = 0, ins = 0, fastmask = 0;
+            int L = 0, cprime = 0, ins = 0;
             double kd = 0.0, nkd = 0.0, lcx = 0.0, lcy = 0.0, lgs = 0.0;
             if (act) {
                 const int n = (int)(rec & SGB_COUNT_MASK), x = (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK);
@@ -374,33 +376,41 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     if (LIKBB) lgs = sgb_lgamma_pos(sgb_add(sp.bb_s, (double)n), sLT);
                 }
                 kd = (double)x; nkd = (double)(n - x);
-                const bool tab = cprime < SGB_CN_TABLE;
-                fastmask = (tab && ins && sp.fast_ok) ? sKM[cprime] : 0;
                 for (int i = L; i < Lprev; i++) colE[i] = NEG_INF;      // rare: only when L shrinks
                 Lprev = L;
             }
-            const int Lw = __reduce_max_sync(SGB_FULL, L);
             // ---- (2) queue of live (lane, state) pairs.  Entry (32 bit): E-tile index lane*P + state (bits 0-11) |
             //      table row cprime*S + state (bits 12-21) | lane (bits 22-26) | lean-path flag (bit 27): every
             //      address an item needs is one shift/mask away, and consecutive states differ by a constant.
-            unsigned need = 0;          // bit m: state m of this lane's bin is queued
+            //      A queue entry depends on (lane, copy number, count validity) only, and copy number is piecewise
+            //      constant along a chromosome: the queue of the previous bin is reused verbatim unless some lane's
+            //      key changed (warp-uniform vote), which skips the scan and the entry stores on most bins.
             if (act) {
                 bD[lane] = make_double2(kd, nkd);
                 if (MODEL == SGB_MODEL_ASCN) ((double2*)bL)[lane] = make_double2(lcx, lcy);
                 else bL[lane] = lcx;
                 if (LIKBB) bG[lane] = lgs;
-                bI[lane] = cprime | (ins << 16);
-                need = (1u << L) - 1u;
             }
-            int cnt = __popc(need);
-            int incl = cnt;
+            const int key = act ? (cprime | (ins << 16) | (1 << 17)) : 0;
+            const bool rebuild = __any_sync(SGB_FULL, key != prev_key);
+            prev_key = key;
+            if (rebuild) {
+                Lw = __reduce_max_sync(SGB_FULL, L);
+                unsigned need = 0;          // bit m: state m of this lane's bin is queued
+                int fastmask = 0;
+                if (act) {
+                    fastmask = (cprime < SGB_CN_TABLE && ins && sp.fast_ok) ? sKM[cprime] : 0;
+                    bI[lane] = cprime | (ins << 16);
+                    need = (1u << L) - 1u;
+                }
+                const int cnt = __popc(need);
+                int incl = cnt;
 #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                int v = __shfl_up_sync(SGB_FULL, incl, d);
-                if (lane >= d) incl += v;
-            }
-            const int tot = __shfl_sync(SGB_FULL, incl, 31);
-            {
+                for (int d = 1; d < 32; d <<= 1) {
+                    int v = __shfl_up_sync(SGB_FULL, incl, d);
+                    if (lane >= d) incl += v;
+                }
+                tot = __shfl_sync(SGB_FULL, incl, 31);
                 const int qpos = incl - cnt;
                 const unsigned allfast = ((fastmask & need) == need) ? (1u << 27) : 0u;
                 const unsigned trow = (cprime < SGB_CN_TABLE) ? (unsigned)(cprime * S) : 0u;
