@@ -314,7 +314,9 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
     pack_ms = sum(float(pl.read_timing(64)[0].mean()) for pl in plans)
     decode_ms = sum(float(pl.read_timing(64)[1].mean()) for pl in plans)      # one launch per plan per step
     res = dict(ms_per_step=total_ms / steps, value=N * world * steps / (total_ms * 1e-3),
-               decode_ms=decode_ms, pack_ms=pack_ms, N=N, gather=gather_mode, launches_per_step=3 * len(plans),
+               decode_ms=decode_ms, pack_ms=pack_ms, N=N, gather=gather_mode,
+               staging=[pl.last_staging() for pl in plans],
+               launches_per_step=sum(2 if pl.last_staging() == 2 else 3 for pl in plans),
                scratch_bytes=sum(pl.scratch_bytes() for pl in plans), checksum=int(out.to(torch.int64).sum().item()))
     if world > 1:
         # every rank must hold every rank's paths: compare checksums of the gathered slices with their owners'
@@ -458,7 +460,8 @@ def main():
             "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": main_res["ms_per_step"], "higher_is_better": True,
             "scaling": "strong" if a.workload in BIG else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": config, "clocks": clocks, "e2e": main_res.get("e2e"), "gpu_launches": main_res["launches_per_step"] * a.steps, "gather": main_res["gather"],
-            "gpu_kernels_per_step": ["k_setup", "k_pack", "k_decode"], "roofline": roofline,
+            "gpu_kernels_per_step": (["k_setup", "k_decode"] if main_res["staging"] == [2] else ["k_setup", "k_pack", "k_decode"]),
+            "staging": ("in_place" if main_res["staging"] == [2] else "packed_records"), "roofline": roofline,
             "scratch_bytes": main_res["scratch_bytes"], "torch_peak_device_bytes": int(torch.cuda.max_memory_allocated())}
 
     if rank == 0 and world == 1 and not a.no_extras:

@@ -104,8 +104,14 @@ SGB_API int sgb_plan_check(sgb_plan* plan, void* stream);
 SGB_API int sgb_plan_enable_timing(sgb_plan* plan, int32_t on);
 SGB_API int sgb_plan_read_timing(sgb_plan* plan, int32_t max_records, float* pack_ms, float* decode_ms,
                                  int32_t* n_out);
-/* bytes of device scratch the plan holds (packed records + optional backpointers) */
+/* bytes of device scratch the plan holds (plan arrays, optional backpointers, and -- only once a call has
+ * needed them -- the packed records of the k_pack path) */
 SGB_API int64_t sgb_plan_scratch_bytes(const sgb_plan* plan);
+/* How the plan's most recent sgb_hmm_decode_device call fed k_decode (no reference counterpart; diagnostic):
+ * 2 = the caller's columns were read in place (binomial models, uint8 cn, n/x 16-byte and cn 4-byte aligned:
+ * 2 kernels per call, k_setup + k_decode), 1 / 0 = through k_pack's packed records (TMA / plain loads: 3
+ * kernels per call), -1 = no call yet. */
+SGB_API int sgb_plan_last_staging(const sgb_plan* plan);
 
 /* ---- the two Rcpp exports ---------------------------------------------------------------- */
 /* viterbi(emission, transition, observations)  src/code.cpp:11-45, R/RcppExports.R:8-10.

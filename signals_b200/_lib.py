@@ -41,6 +41,7 @@ SIGNATURES = {
     "sgb_hmm_decode_device": (ctypes.c_int, [_PP, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "sgb_plan_check": (ctypes.c_int, [_vp, _vp]),
     "sgb_plan_scratch_bytes": (_i64, [_vp]),
+    "sgb_plan_last_staging": (ctypes.c_int, [_vp]),
     "sgb_plan_enable_timing": (ctypes.c_int, [_vp, _i32]),
     "sgb_plan_read_timing": (ctypes.c_int, [_vp, _i32, _vp, _vp, ctypes.POINTER(_i32)]),
     "sgb_viterbi": (ctypes.c_int, [_vp, _i64, _vp, _vp, _i64, _i32, _i32, _i32, _vp]),

@@ -174,7 +174,8 @@ struct Ctx {
     int device = -1;
     int sm_count = 148;
     int group_hint = 0;         // SGB_GROUP=32|16|8 forces the sequences-per-warp choice (0 = automatic)
-    int stage = 1;              // record staging of k_decode: 1 = TMA bulk copies (default), 0 = plain LDG (SGB_STAGE=ldg)
+    int stage = 2;              // input staging of k_decode: 2 = RAW (default: caller's columns read in place, no k_pack),
+                                // 1 = packed records by TMA bulk copies (SGB_STAGE=tma), 0 = packed records by LDG (SGB_STAGE=ldg)
     Slot slot[2];
     cudaStream_t main = nullptr;
     cudaEvent_t ev_setup = nullptr;
@@ -206,7 +207,7 @@ int get_ctx(Ctx** out)
         c->sm_count = prop.multiProcessorCount;
         {
             const char* e = getenv("SGB_STAGE");
-            c->stage = (e && (!strcmp(e, "ldg") || !strcmp(e, "0"))) ? 0 : 1;
+            c->stage = !e ? 2 : (!strcmp(e, "ldg") || !strcmp(e, "0")) ? 0 : (!strcmp(e, "tma") || !strcmp(e, "1")) ? 1 : 2;
             const char* gsz = getenv("SGB_GROUP");
             if (gsz) { int v = atoi(gsz); if (v == 32 || v == 16 || v == 8) c->group_hint = v; }
         }
@@ -325,8 +326,7 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
         if (build_host_plan(seg_off, s0, s1, r0, SL.hp, (long long)C->sm_count * 16, C->group_hint)) return 1;
         if (rows > 0) {
             if (SL.n.reserve((size_t)rows * 4) || SL.x.reserve((size_t)rows * 4) ||
-                SL.cn.reserve((size_t)rows * cn_itemsize) || SL.out.reserve((size_t)rows) ||
-                SL.packed.reserve((size_t)SL.hp.packed_len * 8 + 16))
+                SL.cn.reserve((size_t)rows * cn_itemsize) || SL.out.reserve((size_t)rows))
                 return 1;
             if (m.decode == SGB_DECODE_CHAINED &&
                 (SL.bp.reserve((size_t)rows * S) || SL.last_state.reserve((size_t)SL.hp.nseq * 4 + 16)))
@@ -339,10 +339,14 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
             SGB_CUDA(cudaMemcpyAsync(SL.cn.p, (const char*)cn + (size_t)r0 * cn_itemsize, (size_t)rows * cn_itemsize,
                                      cudaMemcpyHostToDevice, st));
             SGB_CUDA(cudaStreamWaitEvent(st, C->ev_setup, 0));
-            SGB_CUDA(sgbk_pack((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, pd,
-                               (unsigned long long*)SL.packed.p, C->d_err, st));
-            SGB_CUDA(sgbk_decode(pd, (const unsigned long long*)SL.packed.p, C->d_tabs, m, (uint8_t*)SL.out.p,
-                                 (uint8_t*)SL.bp.p, (int*)SL.last_state.p, SL.counter, C->sm_count, C->stage, st));
+            const SgbRawIn raw = {(const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, rows, C->d_err};
+            const int stage = sgbk_resolve_stage(m, C->stage, raw);
+            if (stage != 2 && SL.packed.reserve((size_t)SL.hp.packed_len * 8 + 16)) return 1;    // packed records: only off the RAW path
+            if (stage != 2)
+                SGB_CUDA(sgbk_pack((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, pd,
+                                   (unsigned long long*)SL.packed.p, C->d_err, st));
+            SGB_CUDA(sgbk_decode(pd, (const unsigned long long*)SL.packed.p, raw, C->d_tabs, m, (uint8_t*)SL.out.p,
+                                 (uint8_t*)SL.bp.p, (int*)SL.last_state.p, SL.counter, C->sm_count, stage, st));
             if (m.decode == SGB_DECODE_CHAINED)
                 SGB_CUDA(sgbk_backtrace(pd, (const uint8_t*)SL.bp.p, (const int*)SL.last_state.p, S, (uint8_t*)SL.out.p, st));
             SGB_CUDA(cudaMemcpyAsync(state_out + r0, SL.out.p, (size_t)rows, cudaMemcpyDeviceToHost, st));
@@ -505,6 +509,7 @@ struct sgb_plan {
     cudaEvent_t ev[kRing][3];
     bool ev_ready = false;
     long long calls = 0;
+    int last_stage = -1;
 };
 
 int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_states, int32_t decode,
@@ -522,8 +527,10 @@ int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_s
     if (build_host_plan(seg_off, 0, nseg, 0, pl->hp, (long long)C->sm_count * 16, C->group_hint)) { delete pl; return 1; }
     size_t ns = (size_t)pl->hp.nseq;
     size_t ng = pl->hp.goff.size();
+    // the packed-record buffer is only needed off the RAW staging path: reserved now when that is already certain,
+    // else on the first decode call that turns out to need it
     int bad = pl->goff.reserve(ng * 8 + 16) || pl->ostart.reserve(ns * 8 + 16) || pl->len.reserve(ns * 4 + 16) ||
-              pl->packed.reserve((size_t)pl->hp.packed_len * 8 + 16);
+              ((C->stage != 2 || decode == SGB_DECODE_CHAINED) && pl->packed.reserve((size_t)pl->hp.packed_len * 8 + 16));
     if (!bad && decode == SGB_DECODE_CHAINED)
         bad = pl->bp.reserve((size_t)N * n_states + 16) || pl->last_state.reserve(ns * 4 + 16);
     if (bad) { sgb_plan_destroy(pl); return 1; }
@@ -591,10 +598,15 @@ int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t*
     SGB_CUDA(sgbk_setup(pl->d_tabs, m, params->eps, params->Abias, params->selftransitionprob, st));
     const int slot = (int)(pl->calls % sgb_plan::kRing);
     if (pl->timing) SGB_CUDA(cudaEventRecord(pl->ev[slot][0], st));
-    SGB_CUDA(sgbk_pack(d_n, d_x, d_cn, cn_itemsize, pl->pd, (unsigned long long*)pl->packed.p, pl->d_err, st));
+    const SgbRawIn raw = {d_n, d_x, d_cn, cn_itemsize, (long long)pl->N, pl->d_err};
+    const int stage = sgbk_resolve_stage(m, C->stage, raw);
+    if (stage != 2 && pl->packed.reserve((size_t)pl->hp.packed_len * 8 + 16)) return 1;
+    pl->last_stage = stage;
+    if (stage != 2)
+        SGB_CUDA(sgbk_pack(d_n, d_x, d_cn, cn_itemsize, pl->pd, (unsigned long long*)pl->packed.p, pl->d_err, st));
     if (pl->timing) SGB_CUDA(cudaEventRecord(pl->ev[slot][1], st));
-    SGB_CUDA(sgbk_decode(pl->pd, (const unsigned long long*)pl->packed.p, pl->d_tabs, m, d_state_out,
-                         (uint8_t*)pl->bp.p, (int*)pl->last_state.p, pl->counter, C->sm_count, C->stage, st));
+    SGB_CUDA(sgbk_decode(pl->pd, (const unsigned long long*)pl->packed.p, raw, pl->d_tabs, m, d_state_out,
+                         (uint8_t*)pl->bp.p, (int*)pl->last_state.p, pl->counter, C->sm_count, stage, st));
     if (pl->timing) { SGB_CUDA(cudaEventRecord(pl->ev[slot][2], st)); pl->calls++; }
     if (m.decode == SGB_DECODE_CHAINED)
         SGB_CUDA(sgbk_backtrace(pl->pd, (const uint8_t*)pl->bp.p, (const int*)pl->last_state.p, m.S, d_state_out, st));
@@ -602,6 +614,8 @@ int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t*
         SGB_CUDA(sgbk_loglik(d_n, d_x, d_cn, cn_itemsize, pl->pd, pl->d_tabs, m, d_loglik_out, st));
     return 0;
 }
+
+int sgb_plan_last_staging(const sgb_plan* pl) { return pl ? pl->last_stage : -1; }
 
 int sgb_plan_enable_timing(sgb_plan* pl, int32_t on)
 {

@@ -134,6 +134,12 @@ struct SgbDecodeArgs {
     unsigned int* counter;  // dynamic group scheduler
     int S, lik;
     double loherror, rho;
+    // SGB_STAGE_RAW only: the caller's columns, read in place (no k_pack pass)
+    const int32_t* n;
+    const int32_t* x;
+    const void* cn;
+    long long rows;                     // length of the columns: copies are clamped to it
+    int* err;
 };
 
 #ifndef SGB_DECODE_THREADS
@@ -148,6 +154,27 @@ struct SgbDecodeArgs {
 #endif
 #define SGB_STAGE_LDG 0        // records read straight from global memory (one LDG.64 per lane per bin)
 #define SGB_STAGE_TMA 1        // records staged through shared memory by 1-D bulk copies (cp.async.bulk + mbarrier)
+#define SGB_STAGE_RAW 2        // no packed records at all: every lane streams its own sequence out of the caller's n / x /
+                               // cn columns in aligned 4-bin blocks (16-byte cp.async copies) through a 3-block ring in
+                               // shared memory (binomial models, uint8 cn, 16-byte aligned columns)
+#define SGB_RAW_WORDS (3 * 32 * 9)      // ring: 3 blocks x 32 lanes x (4 words n + 4 words x + 1 word cn)
+
+// src_bytes < 16 zero-fills the rest of the destination (used at the end of the caller's columns)
+__device__ __forceinline__ void sgb_cp_async16(void* dst, const void* src, unsigned src_bytes)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void sgb_cp_async4(void* dst, const void* src, unsigned src_bytes)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void sgb_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void sgb_cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+// log-factorial entries cached in shared memory: the raw ring needs the room, larger counts read the L1/L2 copy
+__host__ __device__ constexpr int sgb_lf_smem(int model, int stage)
+{
+    return stage == SGB_STAGE_RAW ? (model == SGB_MODEL_ASCN ? 256 : 512) : SGB_LF_SMEM;
+}
 
 // ---- TMA (bulk asynchronous copy) / mbarrier wrappers --------------------------------------
 __device__ __forceinline__ unsigned sgb_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -188,11 +215,12 @@ static inline size_t decode_warp_doubles(int SMAX, int model, int lik_bb, int st
     size_t d = 2 * 32 * P + 16 + (size_t)SMAX * 16;
     d += 64 + (model == SGB_MODEL_ASCN ? 64 : 32) + (lik_bb ? 32 : 0);
     if (stage == SGB_STAGE_TMA) d += 2 * 32 * SGB_CH + 2;
+    if (stage == SGB_STAGE_RAW) d += SGB_RAW_WORDS / 2;
     return (d + 1) & ~(size_t)1;
 }
 static inline size_t decode_smem_bytes(int SMAX, int S, int model, int lik_bb, int stage)
 {
-    size_t d = SGB_LOGTAB_LEN + SGB_EXPTAB_LEN + SGB_LF_SMEM;
+    size_t d = SGB_LOGTAB_LEN + SGB_EXPTAB_LEN + sgb_lf_smem(model, stage);
     d += (size_t)SGB_CN_TABLE * S * (lik_bb ? 5 : 2);
     d += (size_t)SGB_DECODE_WARPS * decode_warp_doubles(SMAX, model, lik_bb, stage);
     return d * sizeof(double) + ((size_t)SGB_CN_TABLE * S + SGB_CN_TABLE) * sizeof(int);
@@ -242,12 +270,13 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     constexpr int P = SMAX + 1;
     constexpr int NL = (MODEL == SGB_MODEL_ASCN) ? 64 : 32;
     constexpr int WD0 = 2 * 32 * P + 16 + SMAX * 16 + 64 + NL + (LIKBB ? 32 : 0) +
-                        (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_CH + 2 : 0);
+                        (STAGE == SGB_STAGE_TMA ? 2 * 32 * SGB_CH + 2 : 0) + (STAGE == SGB_STAGE_RAW ? SGB_RAW_WORDS / 2 : 0);
     constexpr int WARP_DOUBLES = (WD0 + 1) & ~1;
+    constexpr int LFN = sgb_lf_smem(MODEL, STAGE);
     double* sLT = smem;
     double* sET = sLT + SGB_LOGTAB_LEN;
     double* sLF = sET + SGB_EXPTAB_LEN;
-    double* sLP = sLF + SGB_LF_SMEM;
+    double* sLP = sLF + LFN;
     double* sLQ = sLP + CTS;
     double* sA = sLQ + CTS;
     double* sB = sA + (LIKBB ? CTS : 0);
@@ -258,7 +287,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
 
     for (int i = threadIdx.x; i < SGB_LOGTAB_LEN; i += blockDim.x) sLT[i] = g_logtab[i];
     for (int i = threadIdx.x; i < SGB_EXPTAB_LEN; i += blockDim.x) sET[i] = g_exptab[i];
-    for (int i = threadIdx.x; i < SGB_LF_SMEM; i += blockDim.x) sLF[i] = g_lftab[i];
+    for (int i = threadIdx.x; i < LFN; i += blockDim.x) sLF[i] = g_lftab[i];
     for (int i = threadIdx.x; i < CTS; i += blockDim.x) {
         int c = i / S, s = i - c * S, src = c * SGB_MAX_STATES + s;
         sLP[i] = A.tabs->lp[src];
@@ -293,6 +322,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     unsigned int* q = (unsigned int*)(bI + 32);
     unsigned long long* stg = (unsigned long long*)(q + SMAX * 32);     // [2][SGB_CH][32] records
     unsigned long long* bar = stg + 2 * 32 * SGB_CH;                    // [2] mbarriers
+    unsigned int* sraw = (unsigned int*)stg;                            // RAW ring: n [3][32][4], x [3][32][4], cn words [3][32]
     if (STAGE == SGB_STAGE_TMA && lane == 0) {
         sgb_mbar_init(&bar[0], 1);
         sgb_mbar_init(&bar[1], 1);
@@ -319,7 +349,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
             len = A.plan.len[r];
             ostart = A.plan.ostart[r];
         }
-        const unsigned long long* gtile = A.packed + A.plan.goff[g];      // [bin][lane] records of this group
+        const unsigned long long* gtile = (STAGE == SGB_STAGE_RAW) ? nullptr : A.packed + A.plan.goff[g];   // [bin][lane] records
         const int Tmax = __shfl_sync(SGB_FULL, len, 0);                   // lane 0 holds the group's longest sequence
         double m1 = NEG_INF;            // running column maximum of this lane's sequence
         double m2 = NEG_INF;            // second maximum / argmax: only the general and chained variants use them
@@ -333,8 +363,32 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 sgb_tma_load_1d(stg + (c & 1) * 32 * SGB_CH, gtile + (long long)c * SGB_CH * 32, SGB_CH * 32 * 8, b);
             }
         };
+        // RAW: block B of a lane = rows [a0 + 4B, a0 + 4B + 4) of the caller's columns, a0 = ostart rounded down to a
+        // multiple of 4, so every copy is 16-byte aligned whatever the sequence's first row is (the rows before ostart
+        // belong to the previous sequence and are ignored).  Ring slot B % 3; the bin a lane reads at step t sits in block
+        // (sh + t) >> 2, sh = ostart & 3, i.e. block t/4 or t/4 + 1: two blocks resident, a third in flight.  Every lane
+        // commits exactly one cp.async group per block, empty or not.
+        const int sh = (int)(ostart & 3);
+        const long long a0 = ostart - sh;
+        const int span = sh + len;                                   // rows of this lane's sequence, counted from a0
+        const long long tail = A.rows - a0;                          // rows of the columns, counted from a0
+        const int avail = tail > 0x7fffffffll ? 0x7fffffff : (int)tail;
+        auto issue_raw = [&](int B, int slot) {
+            if (4 * B < span) {
+                const int left = avail - 4 * B;                      // > 0: the sequence lies inside the columns
+                const long long row = a0 + 4ll * B;
+                unsigned int* d = sraw + (slot * 32 + lane) * 4;
+                sgb_cp_async16(d, A.n + row, left >= 4 ? 16u : (unsigned)left * 4u);
+                sgb_cp_async16(d + 3 * 32 * 4, A.x + row, left >= 4 ? 16u : (unsigned)left * 4u);
+                sgb_cp_async4(sraw + 2 * 3 * 32 * 4 + slot * 32 + lane, (const uint8_t*)A.cn + row, left >= 4 ? 4u : (unsigned)left);
+            }
+            sgb_cp_async_commit();
+        };
+        int slot_m = 0;            // ring slot of block t/4
         if (STAGE == SGB_STAGE_TMA) {
             if (Tmax > 0) issue_chunk(0);
+        } else if (STAGE == SGB_STAGE_RAW) {
+            if (Tmax > 0) { issue_raw(0, 0); issue_raw(1, 1); }
         } else {
             rec_next = (Tmax > 0) ? __ldcs(gtile + lane) : 0ull;
         }
@@ -345,30 +399,54 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
         int prev_key = -1;         // (copy number, validity, active) the queue entries of this lane were built from
         for (int t = 0; t < Tmax; t++) {
             const bool act = t < len;
-            unsigned long long rec;
-            if (STAGE == SGB_STAGE_TMA) {
-                const int ci = t / SGB_CH, w = t % SGB_CH;
-                if (w == 0) {
-                    if (ci & 1) { sgb_mbar_wait(&bar[1], use1 & 1); use1++; }
-                    else { sgb_mbar_wait(&bar[0], use0 & 1); use0++; }
-                    if ((ci + 1) * SGB_CH < Tmax) issue_chunk(ci + 1);
+            int n = 0, x = 0, cnv = 0;         // this lane's bin: total count, B-allele count, total copy number
+            if (STAGE == SGB_STAGE_RAW) {
+                if ((t & 3) == 0) {
+                    if (t) slot_m = slot_m == 2 ? 0 : slot_m + 1;
+                    issue_raw((t >> 2) + 2, slot_m == 0 ? 2 : slot_m - 1);      // into the slot block t/4 - 1 has left
+                    sgb_cp_async_wait1();       // all but the group just committed have landed: blocks t/4 and t/4 + 1
+                    __syncwarp();
                 }
-                rec = stg[((ci & 1) * SGB_CH + w) * 32 + lane];
+                if (act) {
+                    const int u = sh + (t & 3);
+                    int slot = slot_m + (u >> 2);
+                    slot = slot >= 3 ? slot - 3 : slot;
+                    const unsigned int* rN = sraw + (slot * 32 + lane) * 4 + (u & 3);
+                    n = (int)rN[0]; x = (int)rN[3 * 32 * 4];
+                    cnv = (int)((sraw[2 * 3 * 32 * 4 + slot * 32 + lane] >> (8 * (u & 3))) & 255u);
+                    // the checks k_pack makes on the packed path; a bad bin is neutralised, the call fails afterwards
+                    if ((unsigned)(n | x) >> SGB_COUNT_BITS) {
+                        atomicOr(A.err, (n | x) < 0 ? SGB_ERR_NEGATIVE_COUNT : SGB_ERR_COUNT_TOO_LARGE);
+                        n = 0; x = 0; cnv = 0;
+                    }
+                }
             } else {
-                rec = rec_next;
-                if (t + 1 < Tmax) rec_next = __ldcs(gtile + (long long)(t + 1) * 32 + lane);
+                unsigned long long rec;
+                if (STAGE == SGB_STAGE_TMA) {
+                    const int ci = t / SGB_CH, w = t % SGB_CH;
+                    if (w == 0) {
+                        if (ci & 1) { sgb_mbar_wait(&bar[1], use1 & 1); use1++; }
+                        else { sgb_mbar_wait(&bar[0], use0 & 1); use0++; }
+                        if ((ci + 1) * SGB_CH < Tmax) issue_chunk(ci + 1);
+                    }
+                    rec = stg[((ci & 1) * SGB_CH + w) * 32 + lane];
+                } else {
+                    rec = rec_next;
+                    if (t + 1 < Tmax) rec_next = __ldcs(gtile + (long long)(t + 1) * 32 + lane);
+                }
+                n = (int)(rec & SGB_COUNT_MASK); x = (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK);
+                cnv = (int)(rec >> 56);
             }
             // ---- (1) per-bin quantities of this lane's sequence
             int L = 0, cprime = 0, ins = 0;
             double kd = 0.0, nkd = 0.0, lcx = 0.0, lcy = 0.0, lgs = 0.0;
             if (act) {
-                const int n = (int)(rec & SGB_COUNT_MASK), x = (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK);
-                cprime = sgb_cprime(MODEL, (int)(rec >> 56));
+                cprime = sgb_cprime(MODEL, cnv);
                 ins = x <= n;
                 L = sgb_live_states(MODEL, cprime, S);
                 if (ins) {
                     double fn, fx, fy;
-                    if (n < SGB_LF_SMEM) { fn = sLF[n]; fx = sLF[x]; fy = sLF[n - x]; }
+                    if (n < LFN) { fn = sLF[n]; fx = sLF[x]; fy = sLF[n - x]; }
                     else if (n < SGB_NLF) { fn = g_lftab[n]; fx = g_lftab[x]; fy = g_lftab[n - x]; }
                     else { fn = sgb_logfact(n, g_lftab, sLT); fx = sgb_logfact(x, g_lftab, sLT); fy = sgb_logfact(n - x, g_lftab, sLT); }
                     lcx = sgb_sub(sgb_sub(fn, fx), fy);
@@ -588,6 +666,7 @@ static cudaError_t dispatch_decode(const SgbDecodeArgs& A, const SgbModelArgs& m
     if (m.lik_bb) stage = SGB_STAGE_LDG;
 #define SGB_CASE(MD, LK, CH, SG) \
     if (m.model == MD && m.lik_bb == LK && ch == CH && stage == SG) return launch_decode<SMAX, MD, LK, CH, SG>(A, sm_count, st);
+    SGB_CASE(0, 0, 0, 2) SGB_CASE(1, 0, 0, 2)
     SGB_CASE(0, 0, 0, 1) SGB_CASE(0, 1, 0, 1) SGB_CASE(1, 0, 0, 1) SGB_CASE(1, 1, 0, 1)
     SGB_CASE(0, 0, 0, 0) SGB_CASE(0, 1, 0, 0) SGB_CASE(1, 0, 0, 0) SGB_CASE(1, 1, 0, 0)
     SGB_CASE(0, 0, 1, 0) SGB_CASE(0, 1, 1, 0) SGB_CASE(1, 0, 1, 0) SGB_CASE(1, 1, 1, 0)
@@ -595,9 +674,34 @@ static cudaError_t dispatch_decode(const SgbDecodeArgs& A, const SgbModelArgs& m
     return cudaErrorInvalidValue;
 }
 
-cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_packed, const SgbDevTables* d_tabs,
-                        const SgbModelArgs& m, uint8_t* d_state_out, uint8_t* d_bp, int* d_last_state,
-                        unsigned int* d_counter, int sm_count, int stage, cudaStream_t st)
+// RAW staging exists for the binomial, reference-decode kernels and must not cost a resident CTA
+template <int SMAX>
+static int resolve_stage_t(const SgbModelArgs& m, int stage)
+{
+    if (m.decode == SGB_DECODE_CHAINED || m.lik_bb) return SGB_STAGE_LDG;
+    if (stage != SGB_STAGE_RAW) return stage;
+    const int occ_raw = m.model == SGB_MODEL_ASCN ? decode_occupancy<SMAX, 1, 0, 0, SGB_STAGE_RAW>(m.S)
+                                                  : decode_occupancy<SMAX, 0, 0, 0, SGB_STAGE_RAW>(m.S);
+    const int occ_ldg = m.model == SGB_MODEL_ASCN ? decode_occupancy<SMAX, 1, 0, 0, SGB_STAGE_LDG>(m.S)
+                                                  : decode_occupancy<SMAX, 0, 0, 0, SGB_STAGE_LDG>(m.S);
+    return (occ_raw >= 1 && occ_raw >= occ_ldg) ? SGB_STAGE_RAW : SGB_STAGE_TMA;
+}
+
+int sgbk_resolve_stage(const SgbModelArgs& m, int stage, const SgbRawIn& raw)
+{
+    if (stage == SGB_STAGE_RAW) {
+        // 16-byte cp.async copies of 4-bin blocks: count columns 16-byte aligned, a uint8 cn column word-aligned
+        const unsigned long long al = (unsigned long long)raw.n | (unsigned long long)raw.x;
+        if ((al & 15ull) || ((unsigned long long)raw.cn & 3ull) || raw.cn_itemsize != 1) stage = SGB_STAGE_TMA;
+    }
+    if (m.S <= 12) return resolve_stage_t<12>(m, stage);
+    if (m.S <= 16) return resolve_stage_t<16>(m, stage);
+    return resolve_stage_t<SGB_MAX_STATES>(m, stage);
+}
+
+cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_packed, const SgbRawIn& raw,
+                        const SgbDevTables* d_tabs, const SgbModelArgs& m, uint8_t* d_state_out, uint8_t* d_bp,
+                        int* d_last_state, unsigned int* d_counter, int sm_count, int stage, cudaStream_t st)
 {
     if (plan.nseq == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(d_counter, 0, sizeof(unsigned int), st);
@@ -607,6 +711,7 @@ cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_pack
     A.last_state = d_last_state; A.counter = d_counter; A.S = m.S;
     A.lik = m.lik_bb ? SGB_LIK_BETABINOMIAL : SGB_LIK_BINOMIAL;
     A.loherror = m.loherror; A.rho = m.rho;
+    A.n = raw.n; A.x = raw.x; A.cn = raw.cn; A.rows = raw.rows; A.err = raw.err;
     if (m.S <= 12) return dispatch_decode<12>(A, m, stage, sm_count, st);
     if (m.S <= 16) return dispatch_decode<16>(A, m, stage, sm_count, st);
     if (m.S <= SGB_MAX_STATES) return dispatch_decode<SGB_MAX_STATES>(A, m, stage, sm_count, st);

@@ -49,9 +49,20 @@ cudaError_t sgbk_setup(SgbDevTables* d_tabs, const SgbModelArgs& m, double eps, 
                        cudaStream_t st);
 cudaError_t sgbk_pack(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,
                       const SgbPlanDev& plan, unsigned long long* d_packed, int* d_err, cudaStream_t st);
-cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_packed, const SgbDevTables* d_tabs,
-                        const SgbModelArgs& m, uint8_t* d_state_out, uint8_t* d_bp, int* d_last_state,
-                        unsigned int* d_counter, int sm_count, int stage, cudaStream_t st);
+// the caller's columns as k_decode's RAW staging reads them (rows = length of the columns, err = device error word)
+struct SgbRawIn {
+    const int32_t* n;
+    const int32_t* x;
+    const void* cn;
+    int cn_itemsize;
+    long long rows;
+    int* err;
+};
+// stage the decode will really use for this model / these columns: 2 = RAW (no k_pack needed), 1 = TMA, 0 = LDG
+int sgbk_resolve_stage(const SgbModelArgs& m, int stage, const SgbRawIn& raw);
+cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_packed, const SgbRawIn& raw,
+                        const SgbDevTables* d_tabs, const SgbModelArgs& m, uint8_t* d_state_out, uint8_t* d_bp,
+                        int* d_last_state, unsigned int* d_counter, int sm_count, int stage, cudaStream_t st);
 cudaError_t sgbk_backtrace(const SgbPlanDev& plan, const uint8_t* d_bp, const int* d_last_state, int S,
                            uint8_t* d_state_out, cudaStream_t st);
 cudaError_t sgbk_loglik(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,

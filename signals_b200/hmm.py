@@ -198,6 +198,10 @@ class DevicePlan:
     def scratch_bytes(self):
         return int(self._lib.sgb_plan_scratch_bytes(self._h))
 
+    def last_staging(self):
+        """2 = the last decode read the caller's columns in place, 1 / 0 = via k_pack's records, -1 = no call yet"""
+        return int(self._lib.sgb_plan_last_staging(self._h))
+
     def close(self):
         if self._h:
             self._lib.sgb_plan_destroy(self._h)

@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 : > gpurun_out/variants.txt
 for lib in signals_b200/libsignals_b200*.so; do
-  for stg in tma ldg; do
+  for stg in ${STAGES:-raw tma ldg}; do
     out=$(SGB_LIB=$PWD/$lib SGB_STAGE=$stg timeout 300 python bench.py --steps ${STEPS:-10} --no-extras --workload ${WL:-target} 2>&1 | tail -1)
     echo "$lib $stg $(echo "$out" | python -c "import json,sys
 try:
