@@ -136,7 +136,8 @@ int build_host_plan(const int64_t* seg_off, int64_t s0, int64_t s1, int64_t row_
     int G = 32;
     if (group_hint > 0) G = group_hint;
     else if (warp_slots > 0) {
-        if ((nreal + 31) / 32 < warp_slots) G = 16;       // measured: 16 helps small batches ~12 %, 8 does not
+        if ((nreal + 31) / 32 < warp_slots) G = 16;       // measured on 1,000 cells x 5,700 bins: 16 helps ~12 %,
+        if ((nreal + 31) / 32 < warp_slots / 2) G = 8;    // 8 another ~5 %, 4 loses
     }
     const long long ngroups = (nreal + G - 1) / G;
     hp.nseq = ngroups * 32;                       // padded: kernels index sequence r = group * 32 + lane
@@ -209,7 +210,7 @@ int get_ctx(Ctx** out)
             const char* e = getenv("SGB_STAGE");
             c->stage = !e ? 2 : (!strcmp(e, "ldg") || !strcmp(e, "0")) ? 0 : (!strcmp(e, "tma") || !strcmp(e, "1")) ? 1 : 2;
             const char* gsz = getenv("SGB_GROUP");
-            if (gsz) { int v = atoi(gsz); if (v == 32 || v == 16 || v == 8) c->group_hint = v; }
+            if (gsz) { int v = atoi(gsz); if (v == 32 || v == 16 || v == 8 || v == 4) c->group_hint = v; }
         }
         SGB_CUDA(cudaStreamCreate(&c->main));
         SGB_CUDA(cudaEventCreateWithFlags(&c->ev_setup, cudaEventDisableTiming));

@@ -1,6 +1,7 @@
 #!/bin/bash
-for wl in cfg2 target; do
-for g in 32 16 8 0; do
+# sequences-per-warp sweep (SGB_GROUP) on small and large batches
+for wl in ${WLS:-cfg2 target}; do
+for g in ${GROUPS_:-32 16 8 4}; do
   out=$(SGB_GROUP=$g timeout 300 python bench.py --steps 10 --no-extras --workload $wl 2>&1 | tail -1)
   echo "$wl group=$g $(echo "$out" | python -c "import json,sys
 try:
