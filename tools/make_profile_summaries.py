@@ -10,8 +10,8 @@ keep = ['gpu__time_duration.sum', 'launch__registers_per_thread', 'launch__grid_
         'l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed', 'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum',
         'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum', 'smsp__average_warps_issue_stalled', 'sass__inst_executed_local',
         'smsp__sass_thread_inst_executed_op_dfma_pred_on.sum', 'smsp__sass_thread_inst_executed_op_dadd_pred_on.sum',
-        'smsp__sass_thread_inst_executed_op_dmul_pred_on.sum', 'smsp__inst_executed_op_tma_ld.sum', 'sm__throughput.avg.pct']
-desc = {'target': 'k_decode<12,HSCN,binomial,reference,TMA> on 10,000 cells x 5,700 bins (57 M cell-bins)',
+        'smsp__sass_thread_inst_executed_op_dmul_pred_on.sum', 'smsp__inst_executed_op_tma_ld.sum', 'sm__throughput.avg.pct', 'sm__icc_request_hit_rate.pct']
+desc = {'target': 'k_decode<12,HSCN,binomial,reference,RAW (columns read in place)> on 10,000 cells x 5,700 bins (57 M cell-bins)',
         'cfg3': 'k_decode<12,ASCN,beta-binomial,reference,LDG> on 10,000 cells x 5,700 bins (57 M cell-bins)'}
 traffic = {}
 for wl in ('target', 'cfg3'):
