@@ -266,6 +266,7 @@ SGB_HD void sgb_emission_fast2(double kd0, double nk0, double lx0, double ly0, d
 // untabulated path needs to recompute an entry on the fly.
 struct SgbTables {
     const double *LT, *ET, *LP, *LQ, *A, *B, *L0;
+    int pstride;          // element stride of LP / LQ: 1 = two plain arrays, 2 = interleaved {lp, lq} pairs (LQ = LP + 1)
     const double* LGK;    // [entry][2][SGB_LGK]: lgamma(a + k), lgamma(b + k) for k < SGB_LGK (beta-binomial; same bits as sgb_lgamma_pos)
     const int* KIND;
     int S, lik;
@@ -280,7 +281,7 @@ SGB_NOINLINE double sgb_emit_item_slow(int cprime, int in_support, double kd, do
     SgbStateConst sc;
     if (cprime < SGB_CN_TABLE) {
         const int ti = cprime * T.S + m;
-        sc.lp = T.LP[ti]; sc.lq = T.LQ[ti]; sc.kind = T.KIND[ti];
+        sc.lp = T.LP[ti * T.pstride]; sc.lq = T.LQ[ti * T.pstride]; sc.kind = T.KIND[ti];
         sc.a = LIKBB ? T.A[ti] : 0.0; sc.b = LIKBB ? T.B[ti] : 0.0; sc.l0 = LIKBB ? T.L0[ti] : 0.0;
     } else {
         sc = sgb_state_const(cprime, m, T.loherror, T.lik, T.rho, sp.bb_s, T.LT);
@@ -299,7 +300,7 @@ SGB_HD double sgb_emit_item(int cprime, int in_support, double kd, double nkd, d
     const int ti = (cprime < SGB_CN_TABLE) ? cprime * T.S + m : 0;
     const bool fast = (cprime < SGB_CN_TABLE) && in_support && sp.fast_ok && (T.KIND[ti] == SGB_KIND_NORMAL);
     if (fast)
-        return sgb_emission_fast<MODEL, LIKBB>(kd, nkd, lc_x, lc_y, lg_sn, T.LP[ti], T.LQ[ti], LIKBB ? T.A[ti] : 0.0,
+        return sgb_emission_fast<MODEL, LIKBB>(kd, nkd, lc_x, lc_y, lg_sn, T.LP[ti * T.pstride], T.LQ[ti * T.pstride], LIKBB ? T.A[ti] : 0.0,
                                                LIKBB ? T.B[ti] : 0.0, LIKBB ? T.L0[ti] : 0.0,
                                                LIKBB ? T.LGK + (long)ti * 2 * SGB_LGK : T.LT, sp, T.LT, T.ET);
     return sgb_emit_item_slow<MODEL, LIKBB>(cprime, in_support, kd, nkd, lc_x, lc_y, lg_sn, m, T, sp);
@@ -485,10 +486,10 @@ SGB_HD int sgb_seq_step_mem_nl(double* T1, int ts, const double* E, int es, doub
     const double u1 = sgb_add(m1io, tr_off);
 #pragma unroll
     for (int i = 0; i < NL; i++) {
-        const double e = E[i * es];
-        const double voff = sgb_add(u1, e);
-        const double vdia = sgb_add(sgb_add(T1[i * ts], tr_self), e);
-        Tn[i] = (vdia > voff) ? vdia : voff;
+        // max(fl(u1 + e), fl(fl(T1[i] + tr_self) + e)) == fl(max(u1, fl(T1[i] + tr_self)) + e): rounding is monotone,
+        // so taking the maximum before the common addend gives the same bits with one addition less
+        const double td = sgb_add(T1[i * ts], tr_self);
+        Tn[i] = sgb_add((td > u1) ? td : u1, E[i * es]);
     }
     // first maximum by a tournament: the left operand always holds the lower indices, so a strict '>' keeps
     // the lowest index on ties (what which_max does)

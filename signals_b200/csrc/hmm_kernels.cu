@@ -295,8 +295,8 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     for (int i = threadIdx.x; i < LFN; i += blockDim.x) sLF[i] = g_lftab[i];
     for (int i = threadIdx.x; i < CTS; i += blockDim.x) {
         int c = i / S, s = i - c * S, src = c * SGB_MAX_STATES + s;
-        sLP[i] = A.tabs->lp[src];
-        sLQ[i] = A.tabs->lq[src];
+        sLP[2 * i] = A.tabs->lp[src];           // {log p, log(1-p)} pairs: one 16-byte load per item
+        sLP[2 * i + 1] = A.tabs->lq[src];
         sKind[i] = A.tabs->kind[src];
         if (LIKBB) { sA[i] = A.tabs->a[src]; sB[i] = A.tabs->b[src]; sL0[i] = A.tabs->l0[src]; }
     }
@@ -310,7 +310,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     __shared__ SgbTables s_TB;
     if (threadIdx.x == 0) {
         s_sp = A.tabs->sp;
-        s_TB.LT = sLT; s_TB.ET = sET; s_TB.LP = sLP; s_TB.LQ = sLQ; s_TB.A = sA; s_TB.B = sB; s_TB.L0 = sL0;
+        s_TB.LT = sLT; s_TB.ET = sET; s_TB.LP = sLP; s_TB.LQ = sLP + 1; s_TB.pstride = 2; s_TB.A = sA; s_TB.B = sB; s_TB.L0 = sL0;
         s_TB.LGK = A.tabs->lgk; s_TB.KIND = sKind; s_TB.S = S; s_TB.lik = A.lik; s_TB.loherror = A.loherror; s_TB.rho = A.rho;
     }
     const SgbScalars& sp = s_sp;
@@ -524,9 +524,10 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     const double gs0 = LIKBB ? bG[ol0] : 0.0, gs1 = LIKBB ? bG[ol1] : 0.0;
                     double r0, r1;
                     if (en0 & en1 & (1u << 27)) {
-                        sgb_emission_fast2<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
+                        const double2 pq0 = ((const double2*)sLP)[t0], pq1 = ((const double2*)sLP)[t1];
+                        sgb_emission_fast2<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, pq0.x, pq0.y, LIKBB ? sA[t0] : 0.0,
                                                          LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0, d1.x, d1.y, lx1, ly1, gs1,
-                                                         sLP[t1], sLQ[t1], LIKBB ? sA[t1] : 0.0, LIKBB ? sB[t1] : 0.0,
+                                                         pq1.x, pq1.y, LIKBB ? sA[t1] : 0.0, LIKBB ? sB[t1] : 0.0,
                                                          LIKBB ? sL0[t1] : 0.0, LIKBB ? gLGK + (long)t0 * 2 * SGB_LGK : sLT,
                                                          LIKBB ? gLGK + (long)t1 * 2 * SGB_LGK : sLT, sp, sLT, sET, r0, r1);
                     } else {
@@ -553,7 +554,8 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     const double gs0 = LIKBB ? bG[ol0] : 0.0;
                     double r0;
                     if (en0 & (1u << 27)) {
-                        r0 = sgb_emission_fast<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, sLP[t0], sLQ[t0], LIKBB ? sA[t0] : 0.0,
+                        const double2 pq0 = ((const double2*)sLP)[t0];
+                        r0 = sgb_emission_fast<MODEL, LIKBB>(d0.x, d0.y, lx0, ly0, gs0, pq0.x, pq0.y, LIKBB ? sA[t0] : 0.0,
                                                              LIKBB ? sB[t0] : 0.0, LIKBB ? sL0[t0] : 0.0,
                                                              LIKBB ? gLGK + (long)t0 * 2 * SGB_LGK : sLT, sp, sLT, sET);
                     } else {

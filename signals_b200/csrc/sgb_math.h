@@ -271,8 +271,14 @@ SGB_HD double sgb_max(double a, double b)            // operands are never NaN h
 SGB_HD double sgb_logspace_add_lean(double a, double b, const double* __restrict__ LT, const double* __restrict__ ET)
 {
     double mx = sgb_max(a, b);
-    double d = sgb_u2d(sgb_d2u(sgb_sub(a, b)) | 0x8000000000000000ULL);      // -fabs(a-b)
-    double u = sgb_exp_core(sgb_max(d, -708.0), ET);
+    // -fabs(a-b) with its magnitude clamped near 708, both on the high word only (sign bit set, unsigned minimum
+    // with the high word of -708.0): one integer min instead of an FP64 compare-and-select.  A clamped value
+    // lands in (-708.0005, -708], where exp is ~3e-308 and vanishes against max(a,b) just as exp(-708) does.
+    uint64_t db = sgb_d2u(sgb_sub(a, b));
+    uint32_t hi = (uint32_t)(db >> 32) | 0x80000000u;
+    hi = hi < 0xC0862000u ? hi : 0xC0862000u;
+    double d = sgb_u2d(((uint64_t)hi << 32) | (uint64_t)(uint32_t)db);
+    double u = sgb_exp_core(d, ET);
     return sgb_add(mx, sgb_log1p01_core(u, sgb_add(1.0, u), LT));
 }
 

@@ -32,7 +32,7 @@ static void run(int S, int decode, double loherror, double eps, double rho, doub
                 }
         }
     SgbTables TB;
-    TB.LT = LT; TB.ET = ET; TB.LP = tLP.data(); TB.LQ = tLQ.data(); TB.A = tA.data(); TB.B = tB.data();
+    TB.LT = LT; TB.ET = ET; TB.LP = tLP.data(); TB.LQ = tLQ.data(); TB.pstride = 1; TB.A = tA.data(); TB.B = tB.data();
     TB.L0 = tL0.data(); TB.LGK = tG.data(); TB.KIND = tK.data(); TB.S = S; TB.lik = lik; TB.loherror = loherror; TB.rho = rho;
     SgbSeqState<SMAX> st;
     double T1m[SMAX], m1m = 0.0;
