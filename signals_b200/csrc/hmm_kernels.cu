@@ -501,15 +501,18 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
 #pragma unroll
                 for (int m = 0; m < SMAX; m++)
                     if (m < L) q[qpos + m] = ebase + (unsigned)m * 0x1001u;
+                // pad the queue to a multiple of 32 with copies of its first entry (re-evaluating an item and storing
+                // the same value twice is harmless), so the rounds below need no per-lane validity predicates
+                __syncwarp();
+                if (tot > 0 && tot + lane < ((tot + 31) & ~31)) q[tot + lane] = q[0];
+                tot = (tot + 31) & ~31;
             }
             __syncwarp();
-            // ---- (3) the queue: two entries per lane per round while more than 32 remain, else one
+            // ---- (3) the queue: two entries per lane per round while at least 64 remain, else one
             for (int base = 0; base < tot;) {
-                const int remaining = tot - base;
-                if (SGB_PAIR_OK(LIKBB) && remaining > 32) {
+                if (SGB_PAIR_OK(LIKBB) && tot - base >= 64) {
                     const int j0 = base + lane, j1 = j0 + 32;
-                    const bool v1 = j1 < tot;
-                    const unsigned en0 = q[j0], en1 = q[v1 ? j1 : j0];
+                    const unsigned en0 = q[j0], en1 = q[j1];
                     const int ol0 = (en0 >> 22) & 31, ol1 = (en1 >> 22) & 31;
                     const int e0 = en0 & 0xfff, e1 = en1 & 0xfff;               // E-tile indices
                     const int t0 = (en0 >> 12) & 0x3ff, t1 = (en1 >> 12) & 0x3ff;     // table rows
@@ -534,14 +537,13 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                         const int bi0 = bI[ol0], bi1 = bI[ol1];
                         // rare: keep the hot loop small -- the out-of-line general path handles lean items too (same bits)
                         r0 = sgb_emit_item_slow<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, e0 - ol0 * P, TB, sp);
-                        r1 = v1 ? sgb_emit_item_slow<MODEL, LIKBB>(bi1 & 0xffff, bi1 >> 16, d1.x, d1.y, lx1, ly1, gs1, e1 - ol1 * P, TB, sp) : 0.0;
+                        r1 = sgb_emit_item_slow<MODEL, LIKBB>(bi1 & 0xffff, bi1 >> 16, d1.x, d1.y, lx1, ly1, gs1, e1 - ol1 * P, TB, sp);
                     }
                     myE[e0] = r0;
-                    if (v1) myE[e1] = r1;
+                    myE[e1] = r1;
                     base += 64;
                 } else {
-                    const bool v0 = lane < remaining;
-                    const unsigned en0 = q[v0 ? base + lane : base];
+                    const unsigned en0 = q[base + lane];
                     const int ol0 = (en0 >> 22) & 31, e0 = en0 & 0xfff, t0 = (en0 >> 12) & 0x3ff;
                     const double2 d0 = bD[ol0];
                     double lx0, ly0 = 0.0;
@@ -562,7 +564,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                         const int bi0 = bI[ol0];
                         r0 = sgb_emit_item_slow<MODEL, LIKBB>(bi0 & 0xffff, bi0 >> 16, d0.x, d0.y, lx0, ly0, gs0, e0 - ol0 * P, TB, sp);
                     }
-                    if (v0) myE[e0] = r0;
+                    myE[e0] = r0;
                     base += 32;
                 }
             }
