@@ -177,7 +177,8 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
     N = d["n"].size
     # pinned host buffers (e2e inputs / outputs) and resident device copies (value)
     hn = torch.from_numpy(d["n"]).pin_memory(); hx = torch.from_numpy(d["x"]).pin_memory()
-    hc = torch.from_numpy(d["cn"]).pin_memory()
+    cn_host = d["cn"].astype(np.int32) if os.environ.get("BENCH_CN32") == "1" else d["cn"]   # R hands int32 states over
+    hc = torch.from_numpy(cn_host).pin_memory()
     hout = torch.zeros(N, dtype=torch.uint8).pin_memory()
     tn, tx, tc = hn.to(dev), hx.to(dev), hc.to(dev)
     stream = torch.cuda.current_stream().cuda_stream
@@ -328,7 +329,7 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
 
     if want_e2e:
         lib = _lib.load()
-        args = (ctypes.byref(P), N, hn.data_ptr(), hx.data_ptr(), hc.data_ptr(), 1, d["seg_off"].size - 1,
+        args = (ctypes.byref(P), N, hn.data_ptr(), hx.data_ptr(), hc.data_ptr(), cn_host.dtype.itemsize, d["seg_off"].size - 1,
                 d["seg_off"].ctypes.data, hout.data_ptr(), None)
         for _ in range(max(2, min(warmup, 3))):
             hmm.check(lib.sgb_hmm_decode(*args))
@@ -352,7 +353,7 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         e2e_ms = float(ems.item()) / e2e_steps
         nseq = d["seg_off"].size - 1
         res["e2e"] = dict(value=N * world / (e2e_ms * 1e-3), unit="cell-bins/s", ms_per_step=e2e_ms,
-                          h2d_bytes_per_step=int(N * 9 + nseq * 20), d2h_bytes_per_step=int(N), steps=e2e_steps,
+                          h2d_bytes_per_step=int(N * (8 + cn_host.dtype.itemsize) + nseq * 20), d2h_bytes_per_step=int(N), steps=e2e_steps,
                           api="sgb_hmm_decode (host buffers, pinned, chunked copy/compute overlap)")
         assert int(hout.to(torch.int64).sum().item()) == res["checksum"], "host-API and device-API results differ"
     for pl in plans:

@@ -109,8 +109,9 @@ SGB_API int sgb_plan_read_timing(sgb_plan* plan, int32_t max_records, float* pac
 SGB_API int64_t sgb_plan_scratch_bytes(const sgb_plan* plan);
 /* How the plan's most recent sgb_hmm_decode_device call fed k_decode (no reference counterpart; diagnostic):
  * 2 = the caller's columns were read in place (binomial models, uint8 cn, n/x 16-byte and cn 4-byte aligned:
- * 2 kernels per call, k_setup + k_decode), 1 / 0 = through k_pack's packed records (TMA / plain loads: 3
- * kernels per call), -1 = no call yet. */
+ * 2 kernels per call, k_setup + k_decode), 3 = in place after narrowing an int32 cn column to uint8 (k_setup +
+ * k_narrow_cn + k_decode), 1 / 0 = through k_pack's packed records (TMA / plain loads: 3 kernels per call),
+ * -1 = no call yet. */
 SGB_API int sgb_plan_last_staging(const sgb_plan* plan);
 
 /* ---- the two Rcpp exports ---------------------------------------------------------------- */

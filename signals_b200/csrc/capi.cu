@@ -340,7 +340,17 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
             SGB_CUDA(cudaMemcpyAsync(SL.cn.p, (const char*)cn + (size_t)r0 * cn_itemsize, (size_t)rows * cn_itemsize,
                                      cudaMemcpyHostToDevice, st));
             SGB_CUDA(cudaStreamWaitEvent(st, C->ev_setup, 0));
-            const SgbRawIn raw = {(const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, rows, C->d_err};
+            SgbRawIn raw = {(const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, rows, C->d_err};
+            if (cn_itemsize == 4) {
+                // an int32 cn column (R integers) is narrowed to uint8 on the device when that lets k_decode read in place
+                SgbRawIn probe = raw;
+                probe.cn = nullptr; probe.cn_itemsize = 1;
+                if (sgbk_resolve_stage(m, C->stage, probe) == 2) {
+                    if (SL.packed.reserve((size_t)rows + 16)) return 1;
+                    SGB_CUDA(sgbk_narrow_cn((const int32_t*)SL.cn.p, rows, (uint8_t*)SL.packed.p, C->d_err, st));
+                    raw.cn = SL.packed.p; raw.cn_itemsize = 1;
+                }
+            }
             const int stage = sgbk_resolve_stage(m, C->stage, raw);
             if (stage != 2 && SL.packed.reserve((size_t)SL.hp.packed_len * 8 + 16)) return 1;    // packed records: only off the RAW path
             if (stage != 2)
@@ -599,10 +609,21 @@ int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t*
     SGB_CUDA(sgbk_setup(pl->d_tabs, m, params->eps, params->Abias, params->selftransitionprob, st));
     const int slot = (int)(pl->calls % sgb_plan::kRing);
     if (pl->timing) SGB_CUDA(cudaEventRecord(pl->ev[slot][0], st));
-    const SgbRawIn raw = {d_n, d_x, d_cn, cn_itemsize, (long long)pl->N, pl->d_err};
+    SgbRawIn raw = {d_n, d_x, d_cn, cn_itemsize, (long long)pl->N, pl->d_err};
+    bool narrowed = false;
+    if (cn_itemsize == 4 && ((unsigned long long)d_cn & 15ull) == 0) {
+        SgbRawIn probe = raw;
+        probe.cn = nullptr; probe.cn_itemsize = 1;
+        if (sgbk_resolve_stage(m, C->stage, probe) == 2) {
+            if (pl->packed.reserve((size_t)pl->N + 16)) return 1;
+            SGB_CUDA(sgbk_narrow_cn((const int32_t*)d_cn, (long long)pl->N, (uint8_t*)pl->packed.p, pl->d_err, st));
+            raw.cn = pl->packed.p; raw.cn_itemsize = 1;
+            narrowed = true;
+        }
+    }
     const int stage = sgbk_resolve_stage(m, C->stage, raw);
     if (stage != 2 && pl->packed.reserve((size_t)pl->hp.packed_len * 8 + 16)) return 1;
-    pl->last_stage = stage;
+    pl->last_stage = (stage == 2 && narrowed) ? 3 : stage;
     if (stage != 2)
         SGB_CUDA(sgbk_pack(d_n, d_x, d_cn, cn_itemsize, pl->pd, (unsigned long long*)pl->packed.p, pl->d_err, st));
     if (pl->timing) SGB_CUDA(cudaEventRecord(pl->ev[slot][1], st));

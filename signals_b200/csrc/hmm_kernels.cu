@@ -123,6 +123,38 @@ cudaError_t sgbk_pack(const int32_t* d_n, const int32_t* d_x, const void* d_cn, 
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------ k_narrow_cn
+// int32 copy-number column (what R hands over) -> uint8, validated, so that k_decode can read the columns in
+// place: 5 B per cell-bin of traffic instead of k_pack's 17.
+__global__ void __launch_bounds__(256) k_narrow_cn(const int32_t* __restrict__ cn, long long rows,
+                                                   uint8_t* __restrict__ out, int* err)
+{
+    const long long nvec = rows >> 2;
+    int bad = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+        const int4 v = __ldcs((const int4*)cn + i);
+        bad |= (v.x | v.y | v.z | v.w) & ~255;
+        ((uint32_t*)out)[i] = (uint32_t)(v.x & 255) | ((uint32_t)(v.y & 255) << 8) | ((uint32_t)(v.z & 255) << 16) |
+                              ((uint32_t)(v.w & 255) << 24);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (rows & 3)) {
+        const int v = cn[(nvec << 2) + threadIdx.x];
+        bad |= v & ~255;
+        out[(nvec << 2) + threadIdx.x] = (uint8_t)v;
+    }
+    if (bad) atomicOr(err, SGB_ERR_BAD_CN);
+}
+
+cudaError_t sgbk_narrow_cn(const int32_t* d_cn, long long rows, uint8_t* d_out, int* d_err, cudaStream_t st)
+{
+    if (rows <= 0) return cudaSuccess;
+    long long blocks = ((rows >> 2) + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks < 1) blocks = 1;
+    k_narrow_cn<<<(unsigned)blocks, 256, 0, st>>>(d_cn, rows, d_out, d_err);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------ k_decode
 struct SgbDecodeArgs {
     SgbPlanDev plan;

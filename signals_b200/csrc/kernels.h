@@ -58,6 +58,8 @@ struct SgbRawIn {
     long long rows;
     int* err;
 };
+// int32 cn column -> validated uint8 copy (d_cn 16-byte aligned, d_out 4-byte aligned)
+cudaError_t sgbk_narrow_cn(const int32_t* d_cn, long long rows, uint8_t* d_out, int* d_err, cudaStream_t st);
 // stage the decode will really use for this model / these columns: 2 = RAW (no k_pack needed), 1 = TMA, 0 = LDG
 int sgbk_resolve_stage(const SgbModelArgs& m, int stage, const SgbRawIn& raw);
 cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_packed, const SgbRawIn& raw,

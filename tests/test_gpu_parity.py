@@ -316,6 +316,17 @@ def test_in_place_and_packed_staging_agree(oracle):
             plan.decode(P, tn, tx, tc, out, stream=stream)
             plan.check(stream)
             assert np.array_equal(out.cpu().numpy(), ref), (ps[0], off)
+            assert plan.last_staging() == (1 if off == 1 else 2), (off, plan.last_staging())
+        # an int32 copy-number column (what R passes) is narrowed on the device and then read in place
+        out.zero_()
+        plan.decode(P, torch.from_numpy(n).to(dev), torch.from_numpy(x).to(dev), torch.from_numpy(cn.astype(np.int32)).to(dev),
+                    out, stream=stream)
+        plan.check(stream)
+        assert np.array_equal(out.cpu().numpy(), ref) and plan.last_staging() == 3
+        badc = torch.from_numpy(cn.astype(np.int32)).to(dev); badc[keep - 1] = 300
+        plan.decode(P, torch.from_numpy(n).to(dev), torch.from_numpy(x).to(dev), badc, out, stream=stream)
+        with pytest.raises(hmm.SignalsB200Error, match="copy-number"):
+            plan.check(stream)
         # validation on the in-place path
         bad = torch.from_numpy(n).to(dev); bad[5] = 1 << 28
         plan.decode(P, bad, torch.from_numpy(x).to(dev), torch.from_numpy(cn).to(dev), out, stream=stream)
