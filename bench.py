@@ -237,10 +237,24 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         ev_push = [None] * nbuf
         step_no = [0]
 
+        # the copies to the peers are spread over a few streams so that several copy engines run at once
+        n_cp = max(1, min(int(os.environ.get("BENCH_PUSH_STREAMS", "3")), world - 1))
+        cp_streams = [torch.cuda.Stream(device=dev) for _ in range(n_cp - 1)]
+
         def push(b):
+            here = torch.cuda.current_stream()
+            if cp_streams:
+                start = torch.cuda.Event()
+                start.record(here)
             for k in range(1, world):
                 r = (rank + k) % world
-                peers[r][b * W + rank * N: b * W + (rank + 1) * N].copy_(outs[b], non_blocking=True)
+                st = ([here] + cp_streams)[(k - 1) % n_cp]
+                if st is not here:
+                    st.wait_event(start)
+                with torch.cuda.stream(st):
+                    peers[r][b * W + rank * N: b * W + (rank + 1) * N].copy_(outs[b], non_blocking=True)
+            for st in cp_streams:
+                here.wait_stream(st)
             hdl.barrier()
 
         def step():
