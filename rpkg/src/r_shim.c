@@ -1,9 +1,9 @@
 /* r_shim.c -- .Call glue between the signals R package and libsignals_b200.so.
  *
- * SOURCE ONLY: neither R nor its headers exist where this repository is built and tested, so this file
- * has never been compiled; it is written against R's C API only (no Rcpp) and kept thin enough to be
- * checked by reading.  Every numeric path it reaches is exercised through the same C ABI by the Python
- * test-suite (tests/test_gpu_parity.py).
+ * Neither R nor its headers exist where this repository is built and tested, so this file has never been
+ * built inside R.  It is written against R's C API only (no Rcpp); tests/test_r_shim_mock.py compiles it
+ * unmodified against a mock of that API (tests/r_mock/) and drives the three entry points -- registration,
+ * coercion, error unwinding, and on a GPU box the results -- so what remains unverified is R itself.
  *
  * It keeps the two routines the reference registers (src/RcppExports.cpp:39-48) under their original
  * names so R/RcppExports.R works unchanged, and adds the batched entry points the modified R functions in

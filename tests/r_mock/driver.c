@@ -1,0 +1,95 @@
+/* driver.c -- calls the .Call entry points of rpkg/src/r_shim.c the way R would, on mock SEXPs, and hands the
+ * results back through plain C arrays (loaded with ctypes by tests/test_r_shim_mock.py).  Test infrastructure. */
+#include <R.h>
+#include <Rinternals.h>
+#include <R_ext/Rdynload.h>
+#include <setjmp.h>
+#include <string.h>
+
+extern jmp_buf mock_error_jmp;
+extern int mock_error_armed;
+extern char mock_error_msg[1024];
+extern const R_CallMethodDef* mock_registered_calls;
+extern int mock_dynamic_symbols;
+
+void R_init_signals(DllInfo* dll);
+SEXP _signals_logspace_addcpp(SEXP, SEXP);
+SEXP _signals_viterbi(SEXP, SEXP, SEXP);
+SEXP _signals_hmm_decode_batch(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
+
+static int fail(char* err)
+{
+    if (err) { strncpy(err, mock_error_msg, 1023); err[1023] = 0; }
+    mock_error_armed = 0;
+    mock_reset();
+    return 1;
+}
+#define GUARDED(err) mock_error_armed = 1; if (setjmp(mock_error_jmp)) return fail(err)
+#define DONE() mock_error_armed = 0; mock_reset(); return 0
+
+/* names (';'-separated) and arities of what R_init_signals registers; returns the number of routines */
+int drv_registered(char* names, int names_cap, int* nargs, int nargs_cap, int* dynamic)
+{
+    DllInfo info = {NULL, -1};
+    R_init_signals(&info);
+    int k = 0;
+    names[0] = 0;
+    for (const R_CallMethodDef* d = mock_registered_calls; d && d->name; d++, k++) {
+        if ((int)(strlen(names) + strlen(d->name) + 2) < names_cap) { strcat(names, d->name); strcat(names, ";"); }
+        if (k < nargs_cap) nargs[k] = d->numArgs;
+    }
+    *dynamic = mock_dynamic_symbols;
+    return k;
+}
+
+int drv_logspace_add(double a, double b, double* out, char* err)
+{
+    GUARDED(err);
+    SEXP r = _signals_logspace_addcpp(Rf_ScalarReal(a), Rf_ScalarReal(b));
+    *out = REAL(r)[0];
+    DONE();
+}
+
+int drv_viterbi(const double* emission, int nrow, int S, const double* transition, const double* observations, int T,
+                double* path_out, char* err)
+{
+    GUARDED(err);
+    /* R passes `observations` as a numeric (double) vector: 1:nrow */
+    SEXP r = _signals_viterbi(mock_real_matrix(emission, nrow, S), mock_real_matrix(transition, S, S),
+                              mock_real_vector(observations, T));
+    if (XLENGTH(r) != T) Rf_error("driver: viterbi returned %ld values for T = %d", (long)XLENGTH(r), T);
+    memcpy(path_out, REAL(r), (size_t)T * sizeof(double));
+    DONE();
+}
+
+/* counts_as_double: hand totalcounts / alleleB / state over as double vectors (as data.table columns often are) */
+int drv_decode_batch(int model, const int* n, const int* x, const int* state, long N, const double* seg_off, long nseg,
+                     const char* likelihood, int maxCN, double loherror, double eps, double rho, double Abias, double stp,
+                     int want_l, int counts_as_double, double* path_out, double* l_out, char* err)
+{
+    GUARDED(err);
+    SEXP sn, sx, sc;
+    if (counts_as_double) {
+        sn = Rf_coerceVector(mock_int_vector(n, N), REALSXP);
+        sx = Rf_coerceVector(mock_int_vector(x, N), REALSXP);
+        sc = Rf_coerceVector(mock_int_vector(state, N), REALSXP);
+    } else {
+        sn = mock_int_vector(n, N); sx = mock_int_vector(x, N); sc = mock_int_vector(state, N);
+    }
+    int mdl = model, mcn = maxCN;
+    SEXP r = _signals_hmm_decode_batch(mock_int_vector(&mdl, 1), sn, sx, sc, mock_real_vector(seg_off, nseg + 1),
+                                       mock_string(likelihood), mock_int_vector(&mcn, 1), Rf_ScalarReal(loherror),
+                                       Rf_ScalarReal(eps), Rf_ScalarReal(rho), Rf_ScalarReal(Abias), Rf_ScalarReal(stp),
+                                       mock_logical(want_l));
+    if (TYPEOF(r) != VECSXP || XLENGTH(r) != 2) Rf_error("driver: decode_batch must return a list of 2");
+    SEXP p = VECTOR_ELT(r, 0), l = VECTOR_ELT(r, 1);
+    if (XLENGTH(p) != N) Rf_error("driver: path length %ld != N", (long)XLENGTH(p));
+    memcpy(path_out, REAL(p), (size_t)N * sizeof(double));
+    if (want_l) {
+        if (l == R_NilValue || XLENGTH(l) != N * (maxCN + 1)) Rf_error("driver: l has the wrong length");
+        memcpy(l_out, REAL(l), (size_t)XLENGTH(l) * sizeof(double));
+    } else if (l != R_NilValue) {
+        Rf_error("driver: l should be NULL when not requested");
+    }
+    DONE();
+}
