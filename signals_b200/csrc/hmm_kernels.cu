@@ -1,9 +1,12 @@
 // hmm_kernels.cu -- sm_100a kernels for the signals HSCN/ASCN HMM hot path.
 //
 //   k_setup        per-call constants (log p, log1p(-p), beta-binomial shapes, transitions) on the device
-//   k_pack         caller's flat int32/uint8 columns -> 8-byte records, sequences sorted by length
 //   k_decode       fused emission + max-plus forward recursion + the reference's decode rule
-//                  (one lane per (cell, chromosome) sequence, 32 sequences per warp)
+//                  (one lane per (cell, chromosome) sequence, 32 sequences per warp); reads the caller's
+//                  columns in place (binomial models) or k_pack's records
+//   k_narrow_cn    int32 copy-number column -> validated uint8 copy (so R-style input can be read in place)
+//   k_pack         caller's flat int32/uint8 columns -> 8-byte records, sequences sorted by length
+//                  (beta-binomial, chained decode, unaligned columns)
 //   k_backtrace    opt-in textbook backtrace over uint8 backpointers (decode = chained)
 //   k_loglik       bins x states log-likelihood matrix `l` (HaplotypeHMM()$l, alleleHMM()$l)
 //   k_viterbi      stand-alone viterbi(emission, transition, observations), dense S x S transition
@@ -287,15 +290,16 @@ __device__ __noinline__ int decode_step_general(double* colT, double* colE, int 
 
 // Fused emission + forward recursion + decode.  One lane per (cell, chromosome) sequence, 32 sequences
 // of similar length per warp, warps fetch groups from a global counter (longest first).
-// The kernel is bound by shared-memory bandwidth and FP64 issue, so per bin step a warp
-//  (0) takes its 32 packed records from a shared-memory stage that a 1-D TMA bulk copy filled one chunk
-//      (SGB_CH bins x 32 sequences, 2 KB contiguous) ahead, completion tracked by an mbarrier per stage;
-//  (1) unpacks them, looks the log-factorials up;
-//  (2) binomial: every lane evaluates the (2-fma) log densities of its own live states; states whose density
-//      is provably floored by eps get log(eps) without any transcendental (sp.lsa_skip, exact), the others
-//      are queued.  beta-binomial: all live (lane, state) pairs are queued;
-//  (3) the queue -- compacted across the 32 lanes by a prefix sum, so a lane with copy number 2 does not
-//      idle while a lane with copy number 9 works -- is evaluated two entries per lane per round;
+// The kernel is bound by instruction issue and shared-memory bandwidth, so per bin step a warp
+//  (0) takes each lane's n / x / cn from shared memory -- STAGE RAW: a 3-block ring that every lane fills from
+//      its own rows of the caller's columns with aligned 16-byte cp.async copies; STAGE TMA: packed records
+//      moved by 1-D bulk copies one chunk (SGB_CH bins x 32 sequences, 2 KB) ahead, an mbarrier per stage;
+//      STAGE LDG: packed records by plain coalesced loads;
+//  (1) looks the log-factorials up and publishes the lane's per-bin terms ({x, n-x}, log-choose, lgamma(s+n));
+//  (2) keeps a queue of all live (lane, state) pairs, compacted across the 32 lanes by a prefix sum -- a lane
+//      with copy number 2 does not idle while a lane with copy number 9 works -- and rebuilt only on bins
+//      where some lane's copy number changed;
+//  (3) evaluates the queue, two entries per lane per round (one for beta-binomial), into E[lane][state];
 //  (4) each lane runs the O(S) max-plus step of its sequence over the live states only and stores the
 //      decoded state of the previous bin.
 template <int SMAX, int MODEL, int LIKBB, int CHAINED, int STAGE>
