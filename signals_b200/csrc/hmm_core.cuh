@@ -52,7 +52,7 @@ struct SgbScalars {
     double bb_s;        // (1-rho)/rho
     int use_eps;
     int use_abias;
-    int fast_ok;        // the lean emission path is valid (no Abias, log(eps) finite)
+    int fast_ok;        // the lean emission path is valid (no Abias, eps > 0 with log(eps) finite: the default set-up)
     int diag_dominant;  // tr_self >= tr_off: the O(S) recursion needs only the column maximum
 };
 
@@ -109,7 +109,7 @@ SGB_HD SgbScalars sgb_scalars(int S, double eps, double Abias, double stp, doubl
     if (S == 1) s.tr_off = -sgb_inf();                       // a 1 x 1 transition matrix has no off-diagonal entry
     s.init = -sgb_log((double)S, LT);
     s.bb_s = (rho > 0.0) ? sgb_div(sgb_sub(1.0, rho), rho) : 0.0;
-    s.fast_ok = !s.use_abias && (!s.use_eps || (s.log_eps == s.log_eps && sgb_fabs(s.log_eps) != sgb_inf()));
+    s.fast_ok = !s.use_abias && s.use_eps && s.log_eps == s.log_eps && sgb_fabs(s.log_eps) != sgb_inf();
     s.diag_dominant = (s.tr_self >= s.tr_off) ? 1 : 0;
     return s;
 }
@@ -210,8 +210,7 @@ SGB_HD double sgb_emission_fast(double kd, double nkd, double lc_x, double lc_y,
         }
         l = sgb_logspace_add_lean(l, l2, LT, ET);
     }
-    if (sp.use_eps) l = sgb_logspace_add_lean(l, sp.log_eps, LT, ET);
-    return l;
+    return sgb_logspace_add_lean(l, sp.log_eps, LT, ET);        // sp.fast_ok implies sp.use_eps
 }
 
 // Two lean emissions at once: identical arithmetic per item (so identical bits), but written so that both
@@ -247,12 +246,9 @@ SGB_HD void sgb_emission_fast2(double kd0, double nk0, double lx0, double ly0, d
         l0 = sgb_logspace_add_lean(l0, m0, LT, ET);
         l1 = sgb_logspace_add_lean(l1, m1, LT, ET);
     }
-    if (sp.use_eps) {
-        const double le = sp.log_eps;
-        l0 = sgb_logspace_add_lean(l0, le, LT, ET);
-        l1 = sgb_logspace_add_lean(l1, le, LT, ET);
-    }
-    r0 = l0; r1 = l1;
+    const double le = sp.log_eps;                              // sp.fast_ok implies sp.use_eps
+    r0 = sgb_logspace_add_lean(l0, le, LT, ET);
+    r1 = sgb_logspace_add_lean(l1, le, LT, ET);
 }
 
 #if defined(__CUDA_ARCH__)

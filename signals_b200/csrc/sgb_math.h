@@ -223,7 +223,7 @@ SGB_HD double sgb_log(double x, const double* __restrict__ LT)
 SGB_HD double sgb_log1p01_core(double u, double w, const double* __restrict__ LT)
 {
     double c = sgb_sub(u, sgb_sub(w, 1.0));          // exact rounding residual of 1+u
-    int32_t i = (int32_t)((sgb_d2u(w) - 0x3ff0000000000000ULL) >> 45);
+    int32_t i = (int32_t)(((uint32_t)(sgb_d2u(w) >> 32) - 0x3ff00000u) >> 13);     // top 7 mantissa bits (w == 2 -> 128)
     double invc = LT[2 * i], logc = LT[2 * i + 1];
     double r = sgb_fma(w, invc, -1.0);
     // Estrin evaluation of C2 + C3 r + ... + C9 r^7 (3 dependent levels instead of 7)
