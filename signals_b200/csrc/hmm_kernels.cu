@@ -440,15 +440,30 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
         int prev_key = -1;         // (copy number, validity, active) the queue entries of this lane were built from
         for (int t = 0; t < Tmax; t++) {
             const bool act = t < len;
-            int n = 0, x = 0, cnv = 0;         // this lane's bin: total count, B-allele count, total copy number
-            if (STAGE == SGB_STAGE_RAW) {
-                if ((t & 3) == 0) {
-                    if (t) slot_m = slot_m == 2 ? 0 : slot_m + 1;
-                    issue_raw((t >> 2) + 2, slot_m == 0 ? 2 : slot_m - 1);      // into the slot block t/4 - 1 has left
-                    sgb_cp_async_wait1();       // all but the group just committed have landed: blocks t/4 and t/4 + 1
-                    __syncwarp();
+            if (STAGE == SGB_STAGE_RAW && (t & 3) == 0) {
+                if (t) slot_m = slot_m == 2 ? 0 : slot_m + 1;
+                issue_raw((t >> 2) + 2, slot_m == 0 ? 2 : slot_m - 1);      // into the slot block t/4 - 1 has left
+                sgb_cp_async_wait1();       // all but the group just committed have landed: blocks t/4 and t/4 + 1
+                __syncwarp();
+            }
+            unsigned long long rec = 0ull;      // packed-record stages only
+            if (STAGE == SGB_STAGE_TMA) {
+                const int ci = t / SGB_CH, w = t % SGB_CH;
+                if (w == 0) {
+                    if (ci & 1) { sgb_mbar_wait(&bar[1], use1 & 1); use1++; }
+                    else { sgb_mbar_wait(&bar[0], use0 & 1); use0++; }
+                    if ((ci + 1) * SGB_CH < Tmax) issue_chunk(ci + 1);
                 }
-                if (act) {
+                rec = stg[((ci & 1) * SGB_CH + w) * 32 + lane];
+            } else if (STAGE == SGB_STAGE_LDG) {
+                rec = rec_next;
+                if (t + 1 < Tmax) rec_next = __ldcs(gtile + (long long)(t + 1) * 32 + lane);
+            }
+            // ---- (1) per-bin quantities of this lane's sequence, published for the item queue: ONE divergent region
+            int L = 0, cprime = 0, ins = 0;
+            if (act) {
+                int n, x, cnv;                  // this lane's bin: total count, B-allele count, total copy number
+                if (STAGE == SGB_STAGE_RAW) {
                     const int u = sh + (t & 3);
                     int slot = slot_m + (u >> 2);
                     slot = slot >= 3 ? slot - 3 : slot;
@@ -460,28 +475,11 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                         atomicOr(A.err, (n | x) < 0 ? SGB_ERR_NEGATIVE_COUNT : SGB_ERR_COUNT_TOO_LARGE);
                         n = 0; x = 0; cnv = 0;
                     }
-                }
-            } else {
-                unsigned long long rec;
-                if (STAGE == SGB_STAGE_TMA) {
-                    const int ci = t / SGB_CH, w = t % SGB_CH;
-                    if (w == 0) {
-                        if (ci & 1) { sgb_mbar_wait(&bar[1], use1 & 1); use1++; }
-                        else { sgb_mbar_wait(&bar[0], use0 & 1); use0++; }
-                        if ((ci + 1) * SGB_CH < Tmax) issue_chunk(ci + 1);
-                    }
-                    rec = stg[((ci & 1) * SGB_CH + w) * 32 + lane];
                 } else {
-                    rec = rec_next;
-                    if (t + 1 < Tmax) rec_next = __ldcs(gtile + (long long)(t + 1) * 32 + lane);
+                    n = (int)(rec & SGB_COUNT_MASK); x = (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK);
+                    cnv = (int)(rec >> 56);
                 }
-                n = (int)(rec & SGB_COUNT_MASK); x = (int)((rec >> SGB_COUNT_BITS) & SGB_COUNT_MASK);
-                cnv = (int)(rec >> 56);
-            }
-            // ---- (1) per-bin quantities of this lane's sequence
-            int L = 0, cprime = 0, ins = 0;
-            double kd = 0.0, nkd = 0.0, lcx = 0.0, lcy = 0.0, lgs = 0.0;
-            if (act) {
+                double lcx = 0.0, lcy = 0.0, lgs = 0.0;
                 cprime = sgb_cprime(MODEL, cnv);
                 ins = x <= n;
                 L = sgb_live_states(MODEL, cprime, S);
@@ -494,9 +492,12 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     if (MODEL == SGB_MODEL_ASCN) lcy = sgb_sub(sgb_sub(fn, fy), fx);
                     if (LIKBB) lgs = sgb_lgamma_pos(sgb_add(sp.bb_s, (double)n), sLT);
                 }
-                kd = (double)x; nkd = (double)(n - x);
                 for (int i = L; i < Lprev; i++) colE[i] = NEG_INF;      // rare: only when L shrinks
                 Lprev = L;
+                bD[lane] = make_double2((double)x, (double)(n - x));
+                if (MODEL == SGB_MODEL_ASCN) ((double2*)bL)[lane] = make_double2(lcx, lcy);
+                else bL[lane] = lcx;
+                if (LIKBB) bG[lane] = lgs;
             }
             // ---- (2) queue of live (lane, state) pairs.  Entry (32 bit): E-tile index lane*P + state (bits 0-11) |
             //      table row cprime*S + state (bits 12-21) | lane (bits 22-26) | lean-path flag (bit 27): every
@@ -504,12 +505,6 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
             //      A queue entry depends on (lane, copy number, count validity) only, and copy number is piecewise
             //      constant along a chromosome: the queue of the previous bin is reused verbatim unless some lane's
             //      key changed (warp-uniform vote), which skips the scan and the entry stores on most bins.
-            if (act) {
-                bD[lane] = make_double2(kd, nkd);
-                if (MODEL == SGB_MODEL_ASCN) ((double2*)bL)[lane] = make_double2(lcx, lcy);
-                else bL[lane] = lcx;
-                if (LIKBB) bG[lane] = lgs;
-            }
             const int key = act ? (cprime | (ins << 16) | (1 << 17)) : 0;
             const bool rebuild = __any_sync(SGB_FULL, key != prev_key);
             prev_key = key;
@@ -659,11 +654,15 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
 template <int SMAX, int MODEL, int LIKBB, int CHAINED, int STAGE>
 static int decode_occupancy(int S)
 {
-    static int cached_S[2] = {-1, -1}, cached_occ[2] = {0, 0};      // per instantiation; the answer depends on S only
+    // per instantiation and per device (the shared-memory attribute below is a per-device setting); the answer
+    // depends on S only.  Host threads of different devices touch different entries; two threads of the same
+    // device would store the same values.
+    constexpr int MAXDEV = 64;
+    static int cached_S[MAXDEV], cached_occ[MAXDEV];                // zero-initialised: key 0 = not computed yet
     int dev = 0;
     cudaGetDevice(&dev);
-    const int slot = dev & 1;
-    if (cached_S[slot] == S + 1000 * dev) return cached_occ[slot];
+    const int slot = dev & (MAXDEV - 1);
+    if (cached_S[slot] == S + 1) return cached_occ[slot];
     size_t smem = decode_smem_bytes(SMAX, S, MODEL, LIKBB, STAGE);
     auto kern = k_decode<SMAX, MODEL, LIKBB, CHAINED, STAGE>;
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
@@ -676,7 +675,7 @@ static int decode_occupancy(int S)
         return 0;
     }
     cached_occ[slot] = occ;
-    cached_S[slot] = S + 1000 * dev;
+    cached_S[slot] = S + 1;
     return occ;
 }
 

@@ -335,6 +335,18 @@ def test_in_place_and_packed_staging_agree(oracle):
         plan.close()
 
 
+def test_shutdown_and_reinitialise():
+    """sgb_shutdown releases every per-device resource; the next call rebuilds the context (sgb_init is optional)"""
+    lib = _lib.load()
+    d = cases.small_cohort("binomial", n_cells=6, seed=3)
+    ps = cases.PARAM_SETS[0]
+    ref = hmm.decode_arrays(d["n"], d["x"], d["cn"], d["seg_off"], **_kw(ps))
+    for _ in range(2):
+        assert lib.sgb_shutdown() == 0
+        assert np.array_equal(hmm.decode_arrays(d["n"], d["x"], d["cn"], d["seg_off"], **_kw(ps)), ref)
+    assert lib.sgb_shutdown() == 0 and lib.sgb_init(0) == 0
+
+
 def test_multi_device_sharding_matches_single_device():
     lib = _lib.load()
     if lib.sgb_device_count() < 2:
