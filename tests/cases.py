@@ -66,3 +66,38 @@ def concat_sequences(seqs):
 
 def small_cohort(likelihood="binomial", n_cells=40, seed=11, ragged=0.05):
     return synth.make_cohort(n_cells, lens=synth.LENS_DLPBINS, seed=seed, likelihood=likelihood, ragged_drop=ragged)
+
+
+def random_case(seed):
+    """(n, x, cn, seg_off, kwargs of hmm.decode_arrays) of one randomised model + input; see the tests using it"""
+    rng = np.random.default_rng(1000 + seed)
+    S = int(rng.choice([2, 3, 7, 12, 12, 12, 13, 16, 20, 32]))
+    nseq = int(rng.integers(20, 90))
+    lens = np.where(rng.random(nseq) < 0.2, rng.integers(1, 5, nseq), rng.integers(5, 160, nseq))
+    n_l, x_l, c_l = [], [], []
+    for T in lens:
+        pieces = 1 + rng.poisson(1.0)
+        cuts = np.sort(rng.integers(0, T + 1, pieces - 1))
+        bounds = np.concatenate(([0], cuts, [T]))
+        cn = np.zeros(T, np.int64)
+        for a, b in zip(bounds[:-1], bounds[1:]):
+            cn[a:b] = rng.choice([0, 1, 2, 2, 3, 4, 6, 9, 11, 15, 16, 19, 25]) if rng.random() < 0.8 else rng.integers(0, 30)
+        depth = rng.choice([3.0, 20.0, 200.0, 900.0])
+        n = rng.poisson(depth * np.maximum(cn, 1) * rng.gamma(2.0, 0.5, T))
+        n[rng.random(T) < 0.03] = 0
+        b = (rng.random(T) * (cn + 1)).astype(np.int64)
+        pb = np.where(cn > 0, b / np.maximum(cn, 1), 0.5)
+        x = rng.binomial(n, np.clip(pb, 0.01, 0.99))
+        bad = rng.random(T) < 0.01
+        x[bad] = n[bad] + rng.integers(1, 4, int(bad.sum()))          # outside the support
+        n_l.append(n); x_l.append(x); c_l.append(cn)
+    n = np.concatenate(n_l).astype(np.int32); x = np.concatenate(x_l).astype(np.int32); cn = np.concatenate(c_l)
+    seg = np.concatenate(([0], np.cumsum(lens))).astype(np.int64)
+    model = str(rng.choice(["hscn", "ascn"]))
+    lik = str(rng.choice(["binomial", "binomial", "betabinomial"]))
+    kw = dict(model=model, likelihood=lik, n_states=S, loherror=float(rng.choice([0.0, 0.01, 0.02, 0.3])),
+              eps=float(rng.choice([0.0, 1e-12, 1e-12, 1e-6])), rho=float(rng.choice([0.0, 0.005, 0.02, 0.1])) if lik == "betabinomial" else 0.0,
+              Abias=float(rng.choice([0.0, 0.0, 0.0, 0.05])),
+              selftransitionprob=float(rng.choice([0.0, 0.5 / S, 0.5, 0.95, 0.95, 0.9999, 1.0])))
+    cn = cn.astype(np.uint8) if rng.random() < 0.5 else cn.astype(np.int32)
+    return n, x, cn, seg, kw

@@ -335,6 +335,25 @@ def test_in_place_and_packed_staging_agree(oracle):
         plan.close()
 
 
+@pytest.mark.parametrize("seed", range(24))
+def test_randomised_models_and_inputs_bit_exact(oracle, seed):
+    """random state counts (all three kernel buckets), transition regimes, eps / Abias / loherror settings, total copy
+    numbers beyond the tables and the state space, counts on both sides of every log-factorial branch, counts
+    outside the support, 1-bin sequences; uint8 (in place) and int32 (narrowed) copy-number columns"""
+    n, x, cn, seg, kw = cases.random_case(seed)
+    P = oracle.params(model=kw["model"], likelihood=kw["likelihood"], S=kw["n_states"], loherror=kw["loherror"], eps=kw["eps"],
+                      rho=kw["rho"], Abias=kw["Abias"], selftransitionprob=kw["selftransitionprob"])
+    ref = oracle.decode_batch(n, x, cn.astype(np.int32), seg, P, oracle.MATH_DET)
+    got = hmm.decode_arrays(n, x, cn, seg, **kw)
+    assert np.array_equal(got, ref), (kw, np.nonzero(got != ref)[0][:8])
+    if seed % 3 == 0:
+        Pc = oracle.params(model=kw["model"], likelihood=kw["likelihood"], S=kw["n_states"], loherror=kw["loherror"],
+                           eps=kw["eps"], rho=kw["rho"], Abias=kw["Abias"], selftransitionprob=kw["selftransitionprob"],
+                           decode="chained")
+        refc = oracle.decode_batch(n, x, cn.astype(np.int32), seg, Pc, oracle.MATH_DET)
+        assert np.array_equal(hmm.decode_arrays(n, x, cn, seg, decode="chained", **kw), refc)
+
+
 def test_shutdown_and_reinitialise():
     """sgb_shutdown releases every per-device resource; the next call rebuilds the context (sgb_init is optional)"""
     lib = _lib.load()

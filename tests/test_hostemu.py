@@ -56,3 +56,15 @@ def test_core_bit_exact_vs_oracle(oracle, emu, ps):
         got = _emu_decode(emu, (n, x, cn, seg), kw, decode)
         assert np.array_equal(ref, got), (ps[0], dname, int((ref != got).sum()))
 
+
+@pytest.mark.parametrize("seed", range(24))
+def test_core_bit_exact_on_randomised_cases(oracle, emu, seed):
+    """the same randomised models / inputs the GPU parity test uses (tests/cases.py::random_case), on the CPU"""
+    n, x, cn, seg, g = cases.random_case(seed)
+    kw = dict(model=g["model"], likelihood=g["likelihood"], S=g["n_states"], loherror=g["loherror"], eps=g["eps"],
+              rho=g["rho"], Abias=g["Abias"], selftransitionprob=g["selftransitionprob"])
+    cn = cn.astype(np.int32)
+    for decode, dname in ((0, "reference"), (1, "chained")):
+        ref = oracle.decode_batch(n, x, cn, seg, oracle.params(**kw, decode=dname), oracle.MATH_DET)
+        got = _emu_decode(emu, (n, x, cn, seg), kw, decode)
+        assert np.array_equal(ref, got), (kw, dname, np.nonzero(ref != got)[0][:8])
