@@ -34,6 +34,46 @@ def build(force=False):
     return _SO
 
 
+# ---- oracle/_ref: the reference's own src/code.cpp compiled verbatim against oracle/rcpp_mock (see oracle/Makefile)
+_REF_SO = os.path.join(_HERE, "_ref", "libref_code.so")
+_REF_SRC = "/root/reference/src/code.cpp"
+_ref = None
+
+
+def build_ref(force=False):
+    """compile oracle/_ref/libref_code.so when the reference tree is present (it is not on the GPU box, where the
+    prebuilt file travels with the repository snapshot); returns the path or None"""
+    if os.path.exists(_REF_SRC):
+        deps = [_REF_SRC, os.path.join(_HERE, "ref_driver.cpp"), os.path.join(_HERE, "rcpp_mock", "Rcpp.h")]
+        if force or not os.path.exists(_REF_SO) or any(os.path.getmtime(d) > os.path.getmtime(_REF_SO) for d in deps):
+            subprocess.check_call(["make", "-C", _HERE, "-B", "_ref"], stdout=subprocess.DEVNULL)
+    return _REF_SO if os.path.exists(_REF_SO) else None
+
+
+def ref_lib():
+    """the compiled reference routines, or None when neither the prebuilt file nor the reference tree exists"""
+    global _ref
+    if _ref is None and build_ref():
+        L = ctypes.CDLL(_REF_SO)
+        L.ref_logspace_addcpp.restype = ctypes.c_double
+        L.ref_logspace_addcpp.argtypes = [ctypes.c_double, ctypes.c_double]
+        L.ref_viterbi.restype = ctypes.c_int
+        _ref = L
+    return _ref
+
+
+def ref_viterbi(emission_mat, transition_mat, observations):
+    """the reference's viterbi (src/code.cpp:11-45) itself: R-style (bins x states) emission, 1-based observations"""
+    e = np.asfortranarray(emission_mat, dtype=np.float64)
+    tr = np.asfortranarray(transition_mat, dtype=np.float64)
+    obs = np.ascontiguousarray(observations, dtype=np.float64)
+    out = np.empty(obs.size, dtype=np.float64)
+    rc = ref_lib().ref_viterbi(_p(e), int(e.shape[0]), int(tr.shape[0]), _p(tr), _p(obs), int(obs.size), _p(out))
+    if rc:
+        raise ValueError("ref_viterbi rc=%d" % rc)
+    return out
+
+
 _lib = None
 
 

@@ -6,12 +6,15 @@
  * the timed CPU baseline.  The product (signals_b200/) never links, imports
  * or calls it and has no CPU fallback.
  *
- * PARITY UNPINNED: the reference ships no golden vectors / known-answer tests
- * for viterbi, logspace_addcpp, HaplotypeHMM or alleleHMM and
- * neither R, Rcpp nor VGAM exist in this image, so the reference itself cannot
- * be run to produce any.  The restatement below follows the reference sources
- * line by line (citations on every function) and its emission densities are
- * pinned against 50-digit mpmath instead (tests/test_oracle.py).
+ * PARITY: the reference ships no golden vectors / known-answer tests for
+ * viterbi, logspace_addcpp, HaplotypeHMM or alleleHMM and neither
+ * R, Rcpp nor VGAM exist in this image, so the reference as a whole cannot be run.
+ *   - decode side (orc_viterbi, orc_logspace_add): PINNED against oracle/_ref, the
+ *     reference's own src/code.cpp compiled verbatim against a mock of the few Rcpp
+ *     classes it uses (oracle/rcpp_mock/Rcpp.h); tests/test_oracle.py::test_ref_*.
+ *   - emission side (HaplotypeHMM / alleleHMM are R code over stats::dbinom and
+ *     VGAM::dbetabinom): PARITY UNPINNED -- restated line by line below (citations on
+ *     every function) and pinned against 50-digit mpmath densities instead.
  *
  * Third-party arithmetic that is NOT under /root/reference (restated from the
  * published algorithms; versions unpinned by the reference's DESCRIPTION):

@@ -185,6 +185,29 @@ def test_standalone_viterbi(oracle):
         hmm.viterbi(e, tr, [1, 2, 9])
 
 
+def test_standalone_viterbi_against_compiled_reference(oracle):
+    """sgb_viterbi vs oracle/_ref (the reference's src/code.cpp compiled verbatim against oracle/rcpp_mock): the
+    routine is additions and comparisons only, so the paths must agree exactly wherever the device's log(S) for the
+    initial column has the same bits as libm's"""
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref is not built")
+    rng = np.random.default_rng(12)
+    checked = 0
+    for S in (2, 3, 4, 7, 8, 12, 16, 25):
+        if float(oracle.math_eval(1, np.array([float(S)]), math=oracle.MATH_DET)[0]) != math.log(S):
+            continue
+        for T in (1, 2, 50, 400):
+            em = np.round(np.log(rng.random((T + 2, S))), int(rng.choice([1, 2, 15])))
+            em[rng.random(em.shape) < 0.1] = -np.inf
+            stp = 0.95
+            tp = np.full((S, S), (1 - stp) / (S - 1)); np.fill_diagonal(tp, stp)
+            for tr in (np.log(tp), np.log(rng.dirichlet(np.ones(S), size=S))):
+                obs = np.arange(1, T + 1)
+                assert np.array_equal(hmm.viterbi(em, tr, obs), oracle.ref_viterbi(em, tr, obs)), (S, T)
+                checked += 1
+    assert checked >= 16
+
+
 def test_postprocess_codes(oracle):
     rng = np.random.default_rng(9)
     cn = rng.integers(0, 12, 5000).astype(np.int32)

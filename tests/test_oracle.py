@@ -242,3 +242,56 @@ def test_postprocess_matches_r_semantics(oracle):
     assert r["phase"].tolist() == [0, 1, 2, 0, 2, 1, 0, 1]
     assert r["state_phase"].tolist() == [0, 3, 4, 0, 4, 1, 0, 3]
     assert np.allclose(r["state_BAF"], [0.5, 0.0, 1.0, 0.5, 1.0, 0.4, 0.5, 0.0])
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# oracle/_ref: the reference's own src/code.cpp compiled verbatim (against oracle/rcpp_mock).  These tests pin the
+# restated viterbi / logspace_add of oracle.c -- and through it every GPU parity test -- to the reference's text.
+@pytest.fixture(scope="module")
+def ref(oracle):
+    if oracle.ref_lib() is None:
+        pytest.skip("oracle/_ref is not built and /root/reference is absent")
+    return oracle
+
+
+def test_ref_logspace_addcpp_equals_oracle_bit_for_bit(ref):
+    rng = np.random.default_rng(3)
+    a = np.concatenate((rng.uniform(-800, 5, 4000), [-np.inf, 0.0, -27.631021115928547, -745.2, -1e-300]))
+    b = np.concatenate((rng.uniform(-800, 5, 4000), [-3.0, 0.0, -27.631021115928547, -np.inf, -1e-300]))
+    L = ref.ref_lib()
+    for u, v in zip(a, b):
+        r, o = L.ref_logspace_addcpp(float(u), float(v)), ref.logspace_add(float(u), float(v), ref.MATH_LIBM)
+        assert (math.isnan(r) and math.isnan(o)) or r == o, (u, v, r, o)
+    assert math.isnan(L.ref_logspace_addcpp(-math.inf, -math.inf))          # the Inf - Inf case of src/code.cpp:7
+
+
+@pytest.mark.parametrize("S,T", [(2, 1), (3, 2), (12, 5), (12, 300), (7, 64), (32, 40)])
+def test_ref_viterbi_equals_oracle(ref, S, T):
+    """random emissions with -Inf entries and planted exact ties, structured and dense transitions, shuffled
+    observation indices: the compiled reference routine and oracle.c's restatement return the same path"""
+    rng = np.random.default_rng(100 * S + T)
+    for trial in range(6):
+        nrow = T + int(rng.integers(0, 4))
+        em = np.round(np.log(rng.random((nrow, S))), int(rng.choice([1, 3, 15])))     # coarse rounding plants ties
+        em[rng.random((nrow, S)) < 0.15] = -np.inf
+        if trial % 2 == 0:
+            stp = float(rng.choice([0.5, 0.95, 0.999]))
+            tp = np.full((S, S), (1 - stp) / max(S - 1, 1)); np.fill_diagonal(tp, stp)
+        else:
+            tp = rng.dirichlet(np.ones(S), size=S)
+        tr = np.log(tp) if S > 1 else np.zeros((1, 1))
+        obs = rng.permutation(nrow)[:T] + 1 if trial == 5 else np.arange(1, T + 1)
+        want = ref.ref_viterbi(em, tr, obs)
+        got = ref.viterbi(em, tr, obs, init_mode=0, decode=ref.DECODE_REFERENCE, math=ref.MATH_LIBM)
+        assert np.array_equal(want, got), (S, T, trial, np.nonzero(want != got)[0][:5])
+
+
+def test_ref_viterbi_decode_rule_is_not_a_backtrace(ref):
+    """the quirk DESIGN.md section 2 describes, shown on the reference's own code: path[t] is read from the column
+    winner of t+1 (no chaining), the last entry repeats, and one observation yields state 0"""
+    em = np.log(np.array([[0.9, 0.1], [0.1, 0.9], [0.9, 0.1], [0.1, 0.9]]))
+    tr = np.log(np.array([[0.5, 0.5], [0.5, 0.5]]))
+    p = ref.ref_viterbi(em, tr, [1, 2, 3, 4])
+    assert p[-1] == p[-2]
+    assert ref.ref_viterbi(em[:1], tr, [1]).tolist() == [0.0]
+    assert np.array_equal(p, ref.viterbi(em, tr, [1, 2, 3, 4]))
