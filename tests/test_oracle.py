@@ -295,3 +295,16 @@ def test_ref_viterbi_decode_rule_is_not_a_backtrace(ref):
     assert p[-1] == p[-2]
     assert ref.ref_viterbi(em[:1], tr, [1]).tolist() == [0.0]
     assert np.array_equal(p, ref.viterbi(em, tr, [1, 2, 3, 4]))
+
+
+@pytest.mark.parametrize("ps", cases.PARAM_SETS[:8], ids=[p[0] for p in cases.PARAM_SETS[:8]])
+def test_ref_viterbi_on_restated_emissions_reproduces_the_sequence_decode(ref, ps):
+    """HaplotypeHMM / alleleHMM end in `viterbi(l, log(tProbs), seq_len(T))` (R/callHSCN.R:99-104, R/callASCN.R:98-101):
+    feeding the compiled reference routine the restated emission and transition matrices gives the oracle's paths"""
+    P = ref.params(**cases.param_dict(ps))
+    tr = ref.transition(P, ref.MATH_LIBM)
+    for name, n, x, cn in cases.edge_sequences():
+        l = ref.emission(n, x, cn, P, ref.MATH_LIBM)                    # bins x states, as R holds it
+        want = ref.ref_viterbi(l, tr, np.arange(1, n.size + 1))
+        got = ref.hmm_sequence(n, x, cn, P, ref.MATH_LIBM)
+        assert np.array_equal(want, got), (ps[0], name)
