@@ -53,12 +53,14 @@ def make_data(name, rank=0):
     n_cells, lens, model, lik, rho, seed, desc = WORKLOADS[name]
     lens = synth.LENS_5700 if lens == "5700" else synth.LENS_30000
     if name not in BIG:
-        return synth.make_cohort(n_cells, lens=lens, seed=seed + 1000 * rank, likelihood=lik)
+        # weak scaling = one cohort (one set of clones) whose cells are spread over the ranks: rank 0 holds exactly
+        # the 1-GPU data, the other ranks further cells of the same clones
+        return synth.make_cohort(n_cells, lens=lens, seed=seed, likelihood=lik, shard=rank if rank else None)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     mine = n_cells // world                       # these two configs fix the TOTAL number of cells
     base = min(2000, mine)
     reps = max(1, mine // base)
-    b = synth.make_cohort(base, lens=lens, seed=seed + 1000 * rank, likelihood=lik)
+    b = synth.make_cohort(base, lens=lens, seed=seed, likelihood=lik, shard=rank if rank else None)
     d = dict(b)
     for k in ("n", "x", "cn", "truth_b"):
         d[k] = np.tile(b[k], reps)
@@ -233,6 +235,7 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         outs = [gathered_all[b * W + rank * N: b * W + (rank + 1) * N] for b in range(nbuf)] if hdl is not None \
             else [torch.zeros(N, dtype=torch.uint8, device=dev)]
         side = torch.cuda.Stream(device=dev) if nbuf == 2 else None
+        trace = [] if os.environ.get("BENCH_TRACE") == "1" else None       # per-step (decode start, decode end, push end) events
         ev_dec = [torch.cuda.Event() for _ in range(nbuf)]
         ev_push = [None] * nbuf
         step_no = [0]
@@ -269,13 +272,18 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
             else:
                 if ev_push[b] is not None:
                     torch.cuda.current_stream().wait_event(ev_push[b])      # the push that last read outs[b] is done
+                if trace is not None:
+                    t0 = torch.cuda.Event(enable_timing=True); t0.record()
                 plan.decode(P, tn, tx, tc, outs[b], stream=stream)
+                ev_dec[b] = torch.cuda.Event(enable_timing=trace is not None)
                 ev_dec[b].record()
                 with torch.cuda.stream(side):
                     side.wait_event(ev_dec[b])
                     push(b)
-                    ev_push[b] = torch.cuda.Event()
+                    ev_push[b] = torch.cuda.Event(enable_timing=trace is not None)
                     ev_push[b].record()
+                if trace is not None:
+                    trace.append((t0, ev_dec[b], ev_push[b]))
 
         def drain():
             # joins the side stream: every gather issued so far has landed on every rank
@@ -314,6 +322,13 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
             elapsed += e0.elapsed_time(e1)
         del flush
     sampler.active = False
+    if world > 1 and trace:
+        # diagnostic only: where a step's time goes on this rank (ms relative to the first traced decode start)
+        tr_ = trace[-steps:]
+        base = tr_[0][0]
+        rows = ["%2d start %.3f dec_end %.3f push_end %.3f" % (i, base.elapsed_time(a_), base.elapsed_time(b_), base.elapsed_time(c_))
+                for i, (a_, b_, c_) in enumerate(tr_)]
+        sys.stderr.write("rank %d trace\n  " % rank + "\n  ".join(rows) + "\n")
     if world > 1:
         dist.barrier()
     ms = torch.tensor([elapsed], dtype=torch.float64, device=dev)

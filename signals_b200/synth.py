@@ -33,13 +33,14 @@ CN_PROBS = CN_PROBS / CN_PROBS.sum()
 
 def make_cohort(n_cells: int, lens=LENS_5700, seed: int = 20260001, likelihood: str = "binomial",
                 rho: float = 0.02, loherror: float = 0.02, n_clones: int = 4, ragged_drop: float = 0.0,
-                extra_piece_rate: float = 0.3, max_cn: int = 11):
+                extra_piece_rate: float = 0.3, max_cn: int = 11, shard=None):
     """Returns a dict of flat arrays:
          n, x      int32 [N]   total / B-allele read counts per cell-bin  (totalcounts, alleleB)
          cn        uint8 [N]   total copy number state per cell-bin       (state)
          seg_off   int64 [n_cells*len(lens)+1]  sequence boundaries
          truth_b   uint8 [N]   simulated B-allele copy number
          cell, chrom  int32 [nseg]  cell index / chromosome index of every sequence
+       shard: None, or the index of a further shard of the same cohort (see below)
     """
     rng = np.random.Generator(np.random.PCG64(seed))
     lens = np.asarray(lens, dtype=np.int64)
@@ -49,6 +50,10 @@ def make_cohort(n_cells: int, lens=LENS_5700, seed: int = 20260001, likelihood: 
     # clone-level whole-chromosome states
     clone_c = rng.choice(len(probs), size=(n_clones, nchr), p=probs)
     clone_b = (rng.random((n_clones, nchr)) * (clone_c + 1)).astype(np.int64)
+    if shard is not None:
+        # another shard of the SAME cohort (same clones, other cells): the clone-level draws above come from
+        # `seed`, everything per cell from a stream of its own -- what sharding one tumour's cells over ranks gives
+        rng = np.random.Generator(np.random.PCG64([seed, int(shard)]))
     clone_of_cell = rng.integers(0, n_clones, size=n_cells)
 
     nseg = n_cells * nchr
