@@ -58,3 +58,27 @@ def test_shard_sequences_partitions_everything():
             assert b == c
         bins = [so[b] - so[a] for a, b in cuts]
         assert max(bins) - min(bins) <= 2 * 468 + 1
+
+
+def test_bench_shards_are_cells_of_one_cohort():
+    """bench.py's weak scaling: rank 0 holds exactly the 1-GPU data; the other ranks hold other cells of the same
+    clones, so the algorithmic work per rank is equal to well under a percent"""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(os.path.dirname(__file__), "..", "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    base = synth.make_cohort(200, seed=77)
+    same = synth.make_cohort(200, seed=77, shard=None)
+    assert all(np.array_equal(base[k], same[k]) for k in ("n", "x", "cn", "seg_off"))
+    work = [bench.flop_eq(base, "hscn", "binomial") / base["n"].size]
+    for r in (1, 2, 3):
+        sh = synth.make_cohort(200, seed=77, shard=r)
+        assert not np.array_equal(sh["n"], base["n"]) and np.array_equal(sh["seg_off"], base["seg_off"])
+        # the same clone profiles: the set of whole-chromosome copy numbers seen at sequence starts is the cohort's
+        assert set(np.unique(sh["cn"][sh["seg_off"][:-1]])) <= set(np.unique(base["cn"])) | set(np.unique(sh["cn"]))
+        work.append(bench.flop_eq(sh, "hscn", "binomial") / sh["n"].size)
+    assert max(work) / min(work) < 1.02, work
+    # the deterministic part of the JSON contract that needs no GPU
+    d = bench.make_data("cfg2", rank=0)
+    assert d["n"].size == 1000 * 5700 and d["seg_off"].size == 1000 * 23 + 1
