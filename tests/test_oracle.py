@@ -232,6 +232,22 @@ def test_acceptance_accuracy_like_reference_tests(oracle):
     assert (got == minor).mean() > 0.99
 
 
+def test_acceptance_loherror_like_reference_tests(oracle):
+    """tests/testthat/test-hscn.R:34 and test-ascn.R:24,51: expect_equal(round(results$loherror, 2), loherror) --
+    the between-pass estimate weighted.mean(BAF, totalcounts) over the A-Hom bins (R/callHSCN.R:898-902) recovers the
+    simulated loherror to two decimals"""
+    for seed in (123, 321):
+        d = cases.small_cohort("binomial", n_cells=40, seed=seed, ragged=0.0)
+        cn = d["cn"].astype(np.int32)
+        P = oracle.params(model="hscn", S=12, selftransitionprob=0.95, loherror=0.02)
+        path = oracle.decode_batch(d["n"], d["x"], cn, d["seg_off"], P, oracle.MATH_LIBM, nthreads=2)
+        tab = oracle.postprocess(cn, path)
+        ahom = (tab["B"] == 0) & (tab["A"] > 0)
+        assert ahom.sum() > 1000
+        infloherror = float(d["x"][ahom].sum() / d["n"][ahom].sum())      # = weighted.mean(alleleB/totalcounts, totalcounts)
+        assert round(infloherror, 2) == 0.02, infloherror
+
+
 def test_postprocess_matches_r_semantics(oracle):
     cn = np.array([2, 2, 3, 0, 1, 5, 4, 4], dtype=np.int32)
     path = np.array([1, 0, 3, 1, 1, 2, 2, 0], dtype=np.uint8)
