@@ -4,15 +4,17 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload target|cfg2|cfg3] [--impl reference]
 
 A "step" is one pass of the hot path over one batch of synthetic DLP-shaped cell-bins.
-  value     cell-bins/s with inputs already resident in HBM (k_setup + k_pack + k_decode [+ all-gather of
-            the uint8 state paths when N > 1]); CUDA events on the launch stream, max over ranks
+  value     cell-bins/s with inputs already resident in HBM (k_setup + k_decode, which reads the caller's columns
+            in place; k_pack only on the packed-record path [+ all-gather of the uint8 state paths when N > 1,
+            pipelined with the next step's decode]); CUDA events on the launch stream, max over ranks
   e2e       the same metric through the host-buffer C-ABI call sgb_hmm_decode: pinned host inputs are
             copied to the device, decoded, and the state paths copied back, every step
   roofline  k_decode against the FP64 pipe (the path is FP64-bound, not HBM- or tensor-bound):
             algorithmic flop-eq per launch / mean k_decode duration (CUDA events over the timed region) vs a
             DFMA peak measured in this process; the HBM view (10 B per cell-bin) is reported beside it
   cpu_baseline  the oracle's libm flavour (CPU restatement of the reference) on this box's host cores
-Under torchrun (N > 1) every rank owns one GPU and an independent shard of cells (weak scaling).
+Under torchrun (N > 1) every rank owns one GPU and its own shard of the cohort's cells (weak scaling: rank 0 holds
+exactly the 1-GPU data, the other ranks further cells of the same clones).
 """
 import argparse
 import ctypes
