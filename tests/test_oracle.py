@@ -324,3 +324,19 @@ def test_ref_viterbi_on_restated_emissions_reproduces_the_sequence_decode(ref, p
         want = ref.ref_viterbi(l, tr, np.arange(1, n.size + 1))
         got = ref.hmm_sequence(n, x, cn, P, ref.MATH_LIBM)
         assert np.array_equal(want, got), (ps[0], name)
+
+
+def test_thin_decision_margins_occur_only_at_cn0_bins(oracle):
+    """bins decoded on a margin below 1e-9 are where a different but equally accurate dbinom could flip
+    the call.  tools/margin_report.py counts them; on the synthetic cohort they are rare and all sit at
+    homozygous-deletion (CN 0) bins, whose two live states have mirror-image likelihoods."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("margin_report", os.path.join(os.path.dirname(__file__), "..", "tools", "margin_report.py"))
+    mr = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mr)
+    r = mr.report(n_cells=12, model="hscn", likelihood="binomial", seed=11)
+    assert r["bins"] > 40000
+    assert r["lt_1e-9"] <= 1e-3 * r["bins"]
+    assert r["lt_1e-9"] == r["lt_1e-9_at_cn0"]
+    r2 = mr.report(n_cells=6, model="ascn", likelihood="betabinomial", seed=11)
+    assert r2["lt_1e-9"] == r2["lt_1e-9_at_cn0"] <= 1e-3 * r2["bins"]
