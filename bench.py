@@ -512,6 +512,24 @@ def main():
         line["other_workloads"] = others
         cb, _, _ = cpu_reference_run(d, model, lik, rho, 12.0, 1, 0)
         line["cpu_baseline"] = cb
+    if world > 1:
+        # the in-library multi-device entry point (one host thread per device inside ONE process, what the R drop-in
+        # uses) on the GPUs of this job: rank 0 decodes a small cohort with n_devices = world and with one device and
+        # the two results must be equal.  Outside the timed region; the other ranks wait at the barrier.
+        dist.barrier()
+        if rank == 0:
+            dd = make_data("cfg2")
+            kw = dict(model="hscn", likelihood="binomial", rho=0.0, **PARAMS)
+            nd = min(world, lib.sgb_device_count())
+            one = hmm.decode_arrays(dd["n"], dd["x"], dd["cn"], dd["seg_off"], **kw)
+            t0 = time.perf_counter()
+            many = hmm.decode_arrays(dd["n"], dd["x"], dd["cn"], dd["seg_off"], n_devices=nd, **kw)
+            dt = time.perf_counter() - t0
+            assert np.array_equal(one, many), "sgb_hmm_decode_multi differs from sgb_hmm_decode"
+            line["multi_device_check"] = {"api": "sgb_hmm_decode_multi", "n_devices": nd, "cell_bins": int(one.size),
+                                          "equal_to_single_device": True, "wall_ms_first_call": dt * 1e3}
+            torch.cuda.set_device(local_rank)
+        dist.barrier()
     sampler.stop_flag = True
     if rank == 0:
         print(json.dumps(line))

@@ -90,9 +90,14 @@ SGB_API int sgb_hmm_decode_multi(const sgb_params* params, int32_t n_devices, in
  * sgb_plan_create sorts the sequences by length on the host, uploads the index and reserves the
  * packed-record scratch; the plan can be reused for any inputs with the same seg_off.
  * sgb_hmm_decode_device only enqueues work on `stream` (a cudaStream_t, NULL = legacy default stream)
- * and returns; sgb_plan_check synchronises that stream and reports input-validation errors. */
+ * and returns; sgb_plan_check synchronises that stream and reports input-validation errors.
+ * One exception: the packed-record scratch (8 B per cell-bin, needed by the beta-binomial likelihood, by decode = chained and
+ * by columns that are not 16-byte aligned) is reserved by sgb_plan_create only when it is certain to be needed; otherwise the
+ * FIRST decode call that needs it allocates it (an implicit device-wide synchronisation, not allowed during
+ * stream capture).  Call sgb_plan_reserve_packed after sgb_plan_create to take that allocation up front. */
 SGB_API int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_states, int32_t decode,
                     sgb_plan** plan_out);
+SGB_API int sgb_plan_reserve_packed(sgb_plan* plan);
 SGB_API int sgb_plan_destroy(sgb_plan* plan);
 SGB_API int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* plan, const int32_t* d_n, const int32_t* d_x,
                           const void* d_cn, int32_t cn_itemsize, uint8_t* d_state_out, double* d_loglik_out,
@@ -123,12 +128,13 @@ SGB_API int sgb_plan_last_staging(const sgb_plan* plan);
 SGB_API int sgb_viterbi(const double* emission, int64_t nrow_e, const double* transition, const int32_t* observations,
                 int64_t T, int32_t S, int32_t init_mode, int32_t decode, int32_t* path_out);
 
-/* Chained-decode viterbi for callers that must not allocate device memory (host callbacks, fixed-arena
- * services, latency-critical loops -- see signals_b200/csrc/noalloc.cu).  This entry point has no counterpart
+/* Chained-decode viterbi for callers that must not allocate device memory (fixed-arena services,
+ * latency-critical loops that cannot take cudaMalloc's device-wide stall -- see signals_b200/csrc/noalloc.cu).  This entry point has no counterpart
  * in the reference.  Same arithmetic as sgb_viterbi(..., decode = SGB_DECODE_CHAINED) but every pointer is a
  * DEVICE pointer on the current device, the work is only enqueued on `stream`, and the uint8 backpointers live in
  * a 4 MiB array built into the library instead of a library-allocated buffer: T * S must not exceed 4,194,304
- * (larger problems return an error).  It calls no cudaMalloc / cudaFree.  The first call on a device resolves the
+ * (larger problems return an error).  It calls no cudaMalloc / cudaFree, but it does make ordinary non-allocating
+ * runtime calls and a kernel launch, so it may not run inside a cudaLaunchHostFunc callback.  The first call on a device resolves the
  * array's address: make it before any stream capture.  Calls that overlap on one GPU race on the shared array.
  * Observations must already be valid 1-based row indices (they cannot be checked on the host). */
 SGB_API int sgb_viterbi_chained_noalloc(const double* d_emission, int64_t nrow_e, const double* d_transition,

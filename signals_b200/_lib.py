@@ -38,6 +38,7 @@ SIGNATURES = {
     "sgb_hmm_decode_multi": (ctypes.c_int, [_PP, _i32, _i64, _vp, _vp, _vp, _i32, _i64, _vp, _vp]),
     "sgb_plan_create": (ctypes.c_int, [_i64, _i64, _vp, _i32, _i32, ctypes.POINTER(_vp)]),
     "sgb_plan_destroy": (ctypes.c_int, [_vp]),
+    "sgb_plan_reserve_packed": (ctypes.c_int, [_vp]),
     "sgb_hmm_decode_device": (ctypes.c_int, [_PP, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "sgb_plan_check": (ctypes.c_int, [_vp, _vp]),
     "sgb_plan_scratch_bytes": (_i64, [_vp]),

@@ -164,7 +164,7 @@ int build_host_plan(const int64_t* seg_off, int64_t s0, int64_t s1, int64_t row_
 
 struct Slot {
     cudaStream_t st = nullptr;
-    DevBuf n, x, cn, out, packed, bp, last_state, goff, ostart, len, loglik;
+    DevBuf n, x, cn, cn8, out, packed, bp, last_state, goff, ostart, len, loglik;
     unsigned int* counter = nullptr;
     HostPlan hp;
     PinBuf pin;                 // page-locked copy of hp's arrays for the upload
@@ -346,9 +346,9 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
                 SgbRawIn probe = raw;
                 probe.cn = nullptr; probe.cn_itemsize = 1;
                 if (sgbk_resolve_stage(m, C->stage, probe) == 2) {
-                    if (SL.packed.reserve((size_t)rows + 16)) return 1;
-                    SGB_CUDA(sgbk_narrow_cn((const int32_t*)SL.cn.p, rows, (uint8_t*)SL.packed.p, C->d_err, st));
-                    raw.cn = SL.packed.p; raw.cn_itemsize = 1;
+                    if (SL.cn8.reserve((size_t)rows + 16)) return 1;
+                    SGB_CUDA(sgbk_narrow_cn((const int32_t*)SL.cn.p, rows, (uint8_t*)SL.cn8.p, C->d_err, st));
+                    raw.cn = SL.cn8.p; raw.cn_itemsize = 1;
                 }
             }
             const int stage = sgbk_resolve_stage(m, C->stage, raw);
@@ -433,7 +433,7 @@ int sgb_shutdown(void)
         for (int i = 0; i < 2; i++) {
             Slot& s = c->slot[i];
             if (s.st) { cudaStreamSynchronize(s.st); cudaStreamDestroy(s.st); }
-            s.n.release(); s.x.release(); s.cn.release(); s.out.release(); s.packed.release(); s.bp.release();
+            s.n.release(); s.x.release(); s.cn.release(); s.cn8.release(); s.out.release(); s.packed.release(); s.bp.release();
             s.last_state.release(); s.pin.release(); s.goff.release(); s.ostart.release(); s.len.release(); s.loglik.release();
             if (s.counter) cudaFree(s.counter);
         }
@@ -509,7 +509,7 @@ struct sgb_plan {
     int64_t N = 0;
     int n_states = 0, decode = 0;
     HostPlan hp;
-    DevBuf goff, ostart, len, packed, bp, last_state;
+    DevBuf goff, ostart, len, packed, cn8, bp, last_state;
     unsigned int* counter = nullptr;
     int* d_err = nullptr;
     SgbDevTables* d_tabs = nullptr;
@@ -538,9 +538,11 @@ int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_s
     if (build_host_plan(seg_off, 0, nseg, 0, pl->hp, (long long)C->sm_count * 16, C->group_hint)) { delete pl; return 1; }
     size_t ns = (size_t)pl->hp.nseq;
     size_t ng = pl->hp.goff.size();
-    // the packed-record buffer is only needed off the RAW staging path: reserved now when that is already certain,
-    // else on the first decode call that turns out to need it
+    // the narrowed-cn buffer (1 B per cell-bin) is always reserved; the packed-record buffer (8 B per cell-bin) is only
+    // needed off the in-place path: reserved now when that is already certain, else by sgb_plan_reserve_packed or by the
+    // first decode call that turns out to need it
     int bad = pl->goff.reserve(ng * 8 + 16) || pl->ostart.reserve(ns * 8 + 16) || pl->len.reserve(ns * 4 + 16) ||
+              pl->cn8.reserve((size_t)N + 16) ||
               ((C->stage != 2 || decode == SGB_DECODE_CHAINED) && pl->packed.reserve((size_t)pl->hp.packed_len * 8 + 16));
     if (!bad && decode == SGB_DECODE_CHAINED)
         bad = pl->bp.reserve((size_t)N * n_states + 16) || pl->last_state.reserve(ns * 4 + 16);
@@ -574,7 +576,7 @@ int sgb_plan_destroy(sgb_plan* pl)
     if (pl->ev_ready)
         for (int i = 0; i < sgb_plan::kRing; i++)
             for (int j = 0; j < 3; j++) cudaEventDestroy(pl->ev[i][j]);
-    pl->goff.release(); pl->ostart.release(); pl->len.release(); pl->packed.release(); pl->bp.release();
+    pl->goff.release(); pl->ostart.release(); pl->len.release(); pl->packed.release(); pl->cn8.release(); pl->bp.release();
     pl->last_state.release();
     if (pl->counter) cudaFree(pl->counter);
     if (pl->d_err) cudaFree(pl->d_err);
@@ -583,10 +585,19 @@ int sgb_plan_destroy(sgb_plan* pl)
     return 0;
 }
 
+int sgb_plan_reserve_packed(sgb_plan* pl)
+{
+    if (!pl) return fail("plan is NULL");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    if (C->device != pl->device) return fail("plan belongs to another device");
+    return pl->packed.reserve((size_t)pl->hp.packed_len * 8 + 16);
+}
+
 int64_t sgb_plan_scratch_bytes(const sgb_plan* pl)
 {
     if (!pl) return 0;
-    return (int64_t)(pl->packed.cap + pl->bp.cap + pl->last_state.cap + pl->goff.cap + pl->ostart.cap + pl->len.cap);
+    return (int64_t)(pl->packed.cap + pl->cn8.cap + pl->bp.cap + pl->last_state.cap + pl->goff.cap + pl->ostart.cap + pl->len.cap);
 }
 
 int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t* d_n, const int32_t* d_x,
@@ -615,9 +626,8 @@ int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t*
         SgbRawIn probe = raw;
         probe.cn = nullptr; probe.cn_itemsize = 1;
         if (sgbk_resolve_stage(m, C->stage, probe) == 2) {
-            if (pl->packed.reserve((size_t)pl->N + 16)) return 1;
-            SGB_CUDA(sgbk_narrow_cn((const int32_t*)d_cn, (long long)pl->N, (uint8_t*)pl->packed.p, pl->d_err, st));
-            raw.cn = pl->packed.p; raw.cn_itemsize = 1;
+            SGB_CUDA(sgbk_narrow_cn((const int32_t*)d_cn, (long long)pl->N, (uint8_t*)pl->cn8.p, pl->d_err, st));
+            raw.cn = pl->cn8.p; raw.cn_itemsize = 1;
             narrowed = true;
         }
     }

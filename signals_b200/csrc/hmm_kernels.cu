@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
     if (threadIdx.x < SGB_CN_TABLE) {
         int mask = 0;
         for (int s = 0; s < S; s++)
-            if (A.tabs->kind[threadIdx.x * SGB_MAX_STATES + s] == SGB_KIND_NORMAL) mask |= 1 << s;
+            if (A.tabs->kind[threadIdx.x * SGB_MAX_STATES + s] == SGB_KIND_NORMAL) mask |= (int)(1u << s);
         sKM[threadIdx.x] = mask;
     }
     __shared__ SgbScalars s_sp;             // read-mostly scalars live in shared memory, not in registers
@@ -515,7 +515,7 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                 if (act) {
                     fastmask = (cprime < SGB_CN_TABLE && ins && sp.fast_ok) ? sKM[cprime] : 0;
                     bI[lane] = cprime | (ins << 16);
-                    need = (1u << L) - 1u;
+                    need = L >= 32 ? 0xffffffffu : (1u << L) - 1u;
                 }
                 const int cnt = __popc(need);
                 int incl = cnt;

@@ -1,13 +1,15 @@
 // noalloc.cu -- one entry point for callers that are not allowed to allocate device memory.
 //
-// Some users of this library cannot call cudaMalloc at the point where they need a decode: code that runs
-// inside a host callback enqueued with cudaLaunchHostFunc (CUDA API calls that allocate are forbidden there),
-// services that hand the whole device to a single arena at start-up and treat any later driver allocation as a
-// bug, and latency-critical loops that cannot afford the implicit device-wide synchronisation of
-// cudaMalloc / cudaFree.  Every other entry point of the library grows internal buffers on demand; this one
-// never does.  It is the chained (textbook-backtrace) variant of the stand-alone viterbi -- the one kernel
-// whose backpointer scratch is otherwise allocated by the library -- with that scratch held in a fixed array
-// that is part of the loaded module:
+// Some users of this library cannot call cudaMalloc at the point where they need a decode: services that hand
+// the whole device to a single arena at start-up and treat any later driver allocation as a bug, latency-critical
+// loops that cannot afford the implicit device-wide synchronisation of cudaMalloc / cudaFree, and code that has
+// made one warm-up call and from then on must stay free of allocations.  Every other entry point of the library
+// grows internal buffers on demand; this one never does.  It still makes ordinary, non-allocating CUDA runtime
+// calls (cudaGetDevice, cudaFuncSetAttribute, a kernel launch; cudaGetSymbolAddress on the first call), so it must
+// NOT be called from inside a cudaLaunchHostFunc callback, where every CUDA API call is forbidden.
+// It is the chained (textbook-backtrace) variant of the stand-alone viterbi -- the one kernel whose backpointer
+// scratch is otherwise allocated by the library -- with that scratch held in a fixed array that is part of the
+// loaded module:
 //
 //   * the array is SGB_NOALLOC_SCRATCH_BYTES (4 MiB) and every GPU that loads the library carries it until the
 //     process exits, whether or not this entry point is ever used;
@@ -50,10 +52,12 @@ extern "C" SGB_API int sgb_viterbi_chained_noalloc(const double* d_emission, int
     if (T < 0 || nrow_e < 0) return noalloc_fail("negative size");
     if (S < 1 || S > 128) return noalloc_fail("viterbi: number of states must be in 1..128");
     if (T == 0) return 0;
+    if (nrow_e < 1) return noalloc_fail("viterbi: the emission matrix has no rows, so no observation index can be valid");
     if (!d_emission || !d_transition || !d_observations || !d_path_out) return noalloc_fail("NULL device pointer");
-    const unsigned long long need = (unsigned long long)T * (unsigned long long)S;
-    if (need > SGB_NOALLOC_SCRATCH_BYTES)
-        return noalloc_fail("sgb_viterbi_chained_noalloc: T*S = " + std::to_string(need) +
+    // compared without forming T * S, which would wrap for absurd T and slip past the limit
+    if ((unsigned long long)T > SGB_NOALLOC_SCRATCH_BYTES / (unsigned)S)
+        return noalloc_fail("sgb_viterbi_chained_noalloc: T*S = " + std::to_string(T) + " x " + std::to_string(S) +
+                            (T <= (1ll << 40) ? " = " + std::to_string((unsigned long long)T * (unsigned)S) : std::string()) +
                             " bytes of backpointers exceed the fixed " + std::to_string(SGB_NOALLOC_SCRATCH_BYTES) +
                             "-byte scratch; use sgb_viterbi (which allocates) for a problem of this size");
     int dev = 0;

@@ -69,11 +69,21 @@ def small_cohort(likelihood="binomial", n_cells=40, seed=11, ragged=0.05):
 
 
 def random_case(seed):
-    """(n, x, cn, seg_off, kwargs of hmm.decode_arrays) of one randomised model + input; see the tests using it"""
+    """(n, x, cn, seg_off, kwargs of hmm.decode_arrays) of one randomised model + input; see the tests using it.
+    Seeds >= 24 are the long draws: a third of the sequences has 500..3,000 bins (the 100 kb grid of BASELINE
+    configs[4] reaches 2,463), and every fourth of them uses all 32 states with total copy numbers 31 / 40 / 255."""
     rng = np.random.default_rng(1000 + seed)
+    long_mode = seed >= 24
     S = int(rng.choice([2, 3, 7, 12, 12, 12, 13, 16, 20, 32]))
+    if long_mode and seed % 4 == 0:
+        S = 32
     nseq = int(rng.integers(20, 90))
     lens = np.where(rng.random(nseq) < 0.2, rng.integers(1, 5, nseq), rng.integers(5, 160, nseq))
+    if long_mode:
+        lens = np.where(rng.random(nseq) < 0.33, rng.integers(500, 3001, nseq), lens)
+    cn_menu = [0, 1, 2, 2, 3, 4, 6, 9, 11, 15, 16, 19, 25]
+    if S == 32:
+        cn_menu = cn_menu + [31, 31, 40, 255]
     n_l, x_l, c_l = [], [], []
     for T in lens:
         pieces = 1 + rng.poisson(1.0)
@@ -81,7 +91,7 @@ def random_case(seed):
         bounds = np.concatenate(([0], cuts, [T]))
         cn = np.zeros(T, np.int64)
         for a, b in zip(bounds[:-1], bounds[1:]):
-            cn[a:b] = rng.choice([0, 1, 2, 2, 3, 4, 6, 9, 11, 15, 16, 19, 25]) if rng.random() < 0.8 else rng.integers(0, 30)
+            cn[a:b] = rng.choice(cn_menu) if rng.random() < 0.8 else rng.integers(0, 30)
         depth = rng.choice([3.0, 20.0, 200.0, 900.0])
         n = rng.poisson(depth * np.maximum(cn, 1) * rng.gamma(2.0, 0.5, T))
         n[rng.random(T) < 0.03] = 0
@@ -101,3 +111,6 @@ def random_case(seed):
               selftransitionprob=float(rng.choice([0.0, 0.5 / S, 0.5, 0.95, 0.95, 0.9999, 1.0])))
     cn = cn.astype(np.uint8) if rng.random() < 0.5 else cn.astype(np.int32)
     return n, x, cn, seg, kw
+
+
+N_RANDOM_CASES = 40

@@ -57,7 +57,7 @@ def test_core_bit_exact_vs_oracle(oracle, emu, ps):
         assert np.array_equal(ref, got), (ps[0], dname, int((ref != got).sum()))
 
 
-@pytest.mark.parametrize("seed", range(24))
+@pytest.mark.parametrize("seed", range(cases.N_RANDOM_CASES))
 def test_core_bit_exact_on_randomised_cases(oracle, emu, seed):
     """the same randomised models / inputs the GPU parity test uses (tests/cases.py::random_case), on the CPU"""
     n, x, cn, seg, g = cases.random_case(seed)

@@ -340,3 +340,23 @@ def test_thin_decision_margins_occur_only_at_cn0_bins(oracle):
     assert r["lt_1e-9"] == r["lt_1e-9_at_cn0"]
     r2 = mr.report(n_cells=6, model="ascn", likelihood="betabinomial", seed=11)
     assert r2["lt_1e-9"] == r2["lt_1e-9_at_cn0"] <= 1e-3 * r2["bins"]
+
+
+@pytest.mark.parametrize("model,lik,rho", [("hscn", "binomial", 0.0), ("hscn", "betabinomial", 0.02),
+                                           ("ascn", "betabinomial", 0.02)])
+def test_tables_identical_across_math_flavours(oracle, model, lik, rho):
+    """CPU half of the table-identity argument (the GPU half is tests/test_gpu_parity.py): the libm, deterministic and
+    R-style (saddle-point dbinom) flavours may decode different raw paths at homozygous-deletion bins only, and the
+    clamp block R/callHSCN.R:282-290 removes exactly those differences -- every post-clamp column is identical."""
+    from signals_b200 import synth
+    d = synth.make_cohort(120, seed=77, likelihood=lik, ragged_drop=0.03)
+    n, x, cn, so = d["n"], d["x"], d["cn"].astype(np.int32), d["seg_off"]
+    P = oracle.params(model=model, likelihood=lik, S=12, rho=rho, selftransitionprob=0.95)
+    base_path = oracle.decode_batch(n, x, cn, so, P, oracle.MATH_DET, nthreads=4)
+    base = oracle.postprocess(cn, base_path)
+    for flavour in (oracle.MATH_LIBM, oracle.MATH_RMATH):
+        path = oracle.decode_batch(n, x, cn, so, P, flavour, nthreads=4)
+        assert (cn[path != base_path] == 0).all()
+        tab = oracle.postprocess(cn, path)
+        for k in tab:
+            assert np.array_equal(tab[k], base[k], equal_nan=True), (flavour, k)

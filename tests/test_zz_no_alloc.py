@@ -1,13 +1,14 @@
 """The allocation-free viterbi entry point, sgb_viterbi_chained_noalloc.
 
-Most of this library grows device buffers when it needs them.  A few callers cannot tolerate that -- code
-running in a CUDA host callback, services that gave the whole GPU to one arena, loops that cannot take the
-device-wide stall of cudaMalloc -- so one entry point keeps its scratch (the uint8 backpointers of the chained
-viterbi) in a fixed 4 MiB array inside the library and takes device pointers for everything else.
+Most of this library grows device buffers when it needs them.  A few callers cannot tolerate that -- services
+that gave the whole GPU to one arena, loops that cannot take the device-wide stall of cudaMalloc -- so one entry
+point keeps its scratch (the uint8 backpointers of the chained viterbi) in a fixed 4 MiB array inside the library
+and takes device pointers for everything else.  (It still makes non-allocating CUDA calls and launches a kernel,
+so it is not meant for cudaLaunchHostFunc callbacks.)
 
 The test drives it through the C ABI exactly like such a caller would (here torch owns the device buffers) and
-checks its paths against the ordinary, allocating entry point sgb_viterbi(decode = chained): both run the same
-kernel, so the integer paths must be identical.  It makes two calls in a row with different inputs, because
+checks its paths against the ordinary, allocating entry point sgb_viterbi(decode = chained) AND against the CPU
+oracle's chained viterbi: the integer paths must be identical to both.  It makes two calls in a row with different inputs, because
 every call reuses the same array and must not be disturbed by what the previous one left behind, and it checks
 that a problem larger than the fixed array is refused with a clear message.  The file name sorts last so a
 `pytest -x` run reaches it only after every other test; it also passes when run on its own in a fresh process.
@@ -18,6 +19,7 @@ import numpy as np
 import pytest
 
 from signals_b200 import _lib, hmm
+from oracle import cpu_oracle as oracle
 
 pytestmark = pytest.mark.gpu
 
@@ -56,6 +58,10 @@ def test_noalloc_viterbi_matches_allocating_entry_point_twice_in_a_row():
         got = _noalloc(lib, torch, e, tr, obs)
         ref = hmm.viterbi(e, tr, obs, decode="chained")          # existing entry point (allocates its scratch)
         assert np.array_equal(got.astype(np.float64), ref), (seed, int((got != ref).sum()))
+        # the independent comparand: the oracle's textbook backtrace (additions and comparisons only, so the
+        # deterministic flavour differs from libm only in the -log(S) of the first column)
+        orc = oracle.viterbi(e, tr, obs, decode=oracle.DECODE_CHAINED, math=oracle.MATH_DET)
+        assert np.array_equal(got.astype(np.float64), orc), (seed, int((got != orc).sum()))
     # and once more on the first problem: identical answer again
     e, tr, obs = _problem(101, 4000, 12)
     assert np.array_equal(_noalloc(lib, torch, e, tr, obs).astype(np.float64), hmm.viterbi(e, tr, obs, decode="chained"))
@@ -73,7 +79,14 @@ def test_noalloc_viterbi_refuses_problems_beyond_its_fixed_scratch():
     assert rc != 0
     msg = lib.sgb_last_error().decode()
     assert "4194304" in msg and "5120000" in msg
+    # a T so large that T * S wraps around 2^64 must be refused too, not slip under the limit
+    rc = lib.sgb_viterbi_chained_noalloc(d_e.data_ptr(), 1, d_e.data_ptr(), d_i.data_ptr(), 1 << 57, 128, 0, d_i.data_ptr(), None)
+    assert rc != 0 and "4194304" in lib.sgb_last_error().decode()
+    # an emission matrix without rows cannot hold any observation
+    rc = lib.sgb_viterbi_chained_noalloc(d_e.data_ptr(), 0, d_e.data_ptr(), d_i.data_ptr(), 4, 2, 0, d_i.data_ptr(), None)
+    assert rc != 0 and "no rows" in lib.sgb_last_error().decode()
     # exactly at the limit is accepted as a size (T * S == 4 MiB): build a real problem of that size
     e, tr, obs = _problem(7, 32768, 128)
     got = _noalloc(lib, torch, e, tr, obs)
     assert np.array_equal(got.astype(np.float64), hmm.viterbi(e, tr, obs, decode="chained"))
+    assert np.array_equal(got.astype(np.float64), oracle.viterbi(e, tr, obs, decode=oracle.DECODE_CHAINED, math=oracle.MATH_DET))
