@@ -98,6 +98,11 @@ SGB_API int sgb_hmm_decode_multi(const sgb_params* params, int32_t n_devices, in
 SGB_API int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_states, int32_t decode,
                     sgb_plan** plan_out);
 SGB_API int sgb_plan_reserve_packed(sgb_plan* plan);
+/* The default schedule of decode = reference calls (k_emit + k_recur) keeps the emission
+ * log-likelihoods of the live states in device scratch between its two kernels: at most 32 B per cell-bin and
+ * 4-state plane (96 B for maxCN = 11, usually ~41), capped at SGB_E_BUDGET_MB (default 8192) by decoding very large
+ * batches in slices.  It is allocated by the first decode call of a plan, or up front by sgb_plan_reserve_split. */
+SGB_API int sgb_plan_reserve_split(sgb_plan* plan);
 SGB_API int sgb_plan_destroy(sgb_plan* plan);
 SGB_API int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* plan, const int32_t* d_n, const int32_t* d_x,
                           const void* d_cn, int32_t cn_itemsize, uint8_t* d_state_out, double* d_loglik_out,
@@ -109,6 +114,10 @@ SGB_API int sgb_plan_check(sgb_plan* plan, void* stream);
 SGB_API int sgb_plan_enable_timing(sgb_plan* plan, int32_t on);
 SGB_API int sgb_plan_read_timing(sgb_plan* plan, int32_t max_records, float* pack_ms, float* decode_ms,
                                  int32_t* n_out);
+/* three-phase view of the same records: preparation (k_pack, or the split schedule's partition kernels), k_emit
+ * (0 on the fused schedule), and k_decode / k_recur */
+SGB_API int sgb_plan_read_timing3(sgb_plan* plan, int32_t max_records, float* prep_ms, float* emit_ms, float* decode_ms,
+                                  int32_t* n_out);
 /* bytes of device scratch the plan holds (plan arrays, optional backpointers, and -- only once a call has
  * needed them -- the packed records of the k_pack path) */
 SGB_API int64_t sgb_plan_scratch_bytes(const sgb_plan* plan);
@@ -116,7 +125,7 @@ SGB_API int64_t sgb_plan_scratch_bytes(const sgb_plan* plan);
  * 2 = the caller's columns were read in place (binomial models, uint8 cn, n/x 16-byte and cn 4-byte aligned:
  * 2 kernels per call, k_setup + k_decode), 3 = in place after narrowing an int32 cn column to uint8 (k_setup +
  * k_narrow_cn + k_decode), 1 / 0 = through k_pack's packed records (TMA / plain loads: 3 kernels per call),
- * -1 = no call yet. */
+ * 4 = split schedule (k_emit + k_recur: the columns are read in place by k_emit, any element type), -1 = no call yet. */
 SGB_API int sgb_plan_last_staging(const sgb_plan* plan);
 
 /* ---- the two Rcpp exports ---------------------------------------------------------------- */

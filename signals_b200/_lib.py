@@ -39,6 +39,8 @@ SIGNATURES = {
     "sgb_plan_create": (ctypes.c_int, [_i64, _i64, _vp, _i32, _i32, ctypes.POINTER(_vp)]),
     "sgb_plan_destroy": (ctypes.c_int, [_vp]),
     "sgb_plan_reserve_packed": (ctypes.c_int, [_vp]),
+    "sgb_plan_reserve_split": (ctypes.c_int, [_vp]),
+    "sgb_plan_read_timing3": (ctypes.c_int, [_vp, _i32, _vp, _vp, _vp, ctypes.POINTER(_i32)]),
     "sgb_hmm_decode_device": (ctypes.c_int, [_PP, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "sgb_plan_check": (ctypes.c_int, [_vp, _vp]),
     "sgb_plan_scratch_bytes": (_i64, [_vp]),

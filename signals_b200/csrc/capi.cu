@@ -85,6 +85,83 @@ struct PinBuf {
     }
 };
 
+// device scratch of the split schedule (k_emit + k_recur) for one plan / one chunk slot: grow-only
+struct SplitWork {
+    DevBuf cls, perm, part, g_npl, g_tmax, g_eoff, g_size, misc, E;
+    int reserve(const SgbSplitSizes& z)
+    {
+        return cls.reserve(z.cls) || perm.reserve(z.perm) || part.reserve(z.part) || g_npl.reserve(z.g_i32) ||
+               g_tmax.reserve(z.g_i32) || g_eoff.reserve(z.g_i64) || g_size.reserve(z.g_i64) || misc.reserve(64) ||
+               E.reserve(z.e_bytes);
+    }
+    SgbSplitDev dev(const SgbSplitSizes& z) const
+    {
+        SgbSplitDev W;
+        W.cls = (uint8_t*)cls.p; W.perm = (int*)perm.p; W.part = (unsigned int*)part.p; W.g_npl = (int*)g_npl.p;
+        W.g_tmax = (int*)g_tmax.p; W.g_eoff = (long long*)g_eoff.p; W.g_size = (unsigned long long*)g_size.p;
+        W.ngroups = (int*)misc.p; W.counters = (unsigned int*)misc.p + 4;
+        W.E = (double*)E.p; W.e_cap_sectors = (long long)(z.e_bytes / 32); W.gcap = z.gcap; W.ntile = z.ntile;
+        return W;
+    }
+    size_t bytes() const
+    {
+        return cls.cap + perm.cap + part.cap + g_npl.cap + g_tmax.cap + g_eoff.cap + g_size.cap + misc.cap + E.cap;
+    }
+    void release()
+    {
+        cls.release(); perm.release(); part.release(); g_npl.release(); g_tmax.release(); g_eoff.release();
+        g_size.release(); misc.release(); E.release();
+    }
+};
+
+// Slices of a length-descending plan for the split schedule: each [q0, q1) range of plan entries keeps the emission
+// tiles under `budget` bytes (the whole batch is one slice unless it is very large).
+struct SplitSlice {
+    long long q0, q1, rows;
+    int maxlen;
+};
+std::vector<SplitSlice> split_slices(const std::vector<int>& len, int S, size_t budget)
+{
+    std::vector<SplitSlice> out;
+    const long long n = (long long)len.size();
+    long long q0 = 0;
+    while (q0 < n) {
+        long long q1 = q0, rows = 0;
+        const int maxlen = len[(size_t)q0];              // entries are sorted longest first (padding entries have length 0)
+        int mx = maxlen;
+        while (q1 < n) {
+            const long long step = std::min<long long>(n - q1, 32 * 64);
+            long long add = 0;
+            for (long long i = q1; i < q1 + step; i++) { add += len[(size_t)i]; if (len[(size_t)i] > mx) mx = len[(size_t)i]; }
+            if (q1 > q0 && sgbk_split_sizes(q1 + step - q0, rows + add, mx, S).e_bytes > budget) break;
+            rows += add;
+            q1 += step;
+        }
+        out.push_back({q0, q1, rows, mx});
+        q0 = q1;
+    }
+    return out;
+}
+
+size_t split_budget_bytes()
+{
+    const char* e = getenv("SGB_E_BUDGET_MB");
+    long long mb = e ? atoll(e) : 0;
+    if (mb <= 0) mb = 8192;
+    return (size_t)mb << 20;
+}
+
+// which schedule a decode = reference call takes: 1 = split (k_emit + k_recur), 0 = fused k_decode
+int want_split(const SgbModelArgs& m, long long nseq)
+{
+    if (m.decode != SGB_DECODE_REFERENCE) return 0;          // chained decode keeps the fused kernel + k_backtrace
+    const char* e = getenv("SGB_SCHED");
+    if (e && !strcmp(e, "fused")) return 0;
+    if (e && !strcmp(e, "split")) return 1;
+    (void)nseq;
+    return 1;
+}
+
 // host-side description of a batch of sequences, sorted by length (longest first)
 struct HostPlan {
     std::vector<long long> goff, ostart;       // goff: per group of 32 sequences, ostart: per sequence
@@ -165,6 +242,7 @@ int build_host_plan(const int64_t* seg_off, int64_t s0, int64_t s1, int64_t row_
 struct Slot {
     cudaStream_t st = nullptr;
     DevBuf n, x, cn, cn8, out, packed, bp, last_state, goff, ostart, len, loglik;
+    SplitWork split;
     unsigned int* counter = nullptr;
     HostPlan hp;
     PinBuf pin;                 // page-locked copy of hp's arrays for the upload
@@ -251,7 +329,35 @@ const char* err_bits_text(int bits)
     if (bits & SGB_ERR_NEGATIVE_COUNT) return "negative read count in totalcounts / alleleB";
     if (bits & SGB_ERR_COUNT_TOO_LARGE) return "read count >= 2^28 is not supported";
     if (bits & SGB_ERR_BAD_CN) return "copy-number state outside 0..255";
+    if (bits & SGB_ERR_NOT_INTEGER) return "a numeric (double) column holds NA / NaN or a value that is not an integer";
+    if (bits & SGB_ERR_INTERNAL) return "internal error: emission tile bound exceeded";
     return "unknown input error";
+}
+
+// split schedule over a whole (length-descending) plan: slices, scratch reservation, launches
+int run_split(SplitWork& W, std::vector<SplitSlice>& slices, const HostPlan& hp, const SgbPlanDev& pd0, const SgbColsIn& in,
+              const SgbDevTables* d_tabs, const SgbModelArgs& m, uint8_t* d_state_out, int sm_count, cudaStream_t st,
+              cudaEvent_t ev_prep, cudaEvent_t ev_mid)
+{
+    if (slices.empty()) slices = split_slices(hp.len, m.S, split_budget_bytes());
+    SgbSplitSizes zmax = sgbk_split_sizes(0, 0, 0, m.S);
+    for (const SplitSlice& sl : slices) {
+        const SgbSplitSizes z = sgbk_split_sizes(sl.q1 - sl.q0, sl.rows, sl.maxlen, m.S);
+        zmax.cls = std::max(zmax.cls, z.cls); zmax.perm = std::max(zmax.perm, z.perm); zmax.part = std::max(zmax.part, z.part);
+        zmax.g_i32 = std::max(zmax.g_i32, z.g_i32); zmax.g_i64 = std::max(zmax.g_i64, z.g_i64);
+        zmax.e_bytes = std::max(zmax.e_bytes, z.e_bytes);
+    }
+    if (W.reserve(zmax)) return 1;           // grow-only: allocates on the first call of a plan / slot
+    bool first = true;
+    for (const SplitSlice& sl : slices) {
+        const SgbSplitSizes z = sgbk_split_sizes(sl.q1 - sl.q0, sl.rows, sl.maxlen, m.S);
+        SgbPlanDev pd = pd0;
+        pd.ostart += sl.q0; pd.len += sl.q0; pd.nseq = sl.q1 - sl.q0;
+        SGB_CUDA(sgbk_split_decode(pd, sl.q1 - sl.q0, in, d_tabs, m, W.dev(z), d_state_out, sm_count, st,
+                                   first ? ev_prep : nullptr, first ? ev_mid : nullptr));
+        first = false;
+    }
+    return 0;
 }
 
 int upload_plan(Slot& S, cudaStream_t st, SgbPlanDev& pd)
@@ -324,7 +430,10 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
         SGB_CUDA(cudaStreamSynchronize(st));          // slot buffers (and its host plan) are free again
         const int64_t r0 = seg_off[s0], r1 = seg_off[s1];
         const long long rows = (long long)(r1 - r0);
-        if (build_host_plan(seg_off, s0, s1, r0, SL.hp, (long long)C->sm_count * 16, C->group_hint)) return 1;
+        const int use_split = want_split(m, s1 - s0);
+        if (build_host_plan(seg_off, s0, s1, r0, SL.hp, (long long)C->sm_count * 16,
+                            C->group_hint ? C->group_hint : (use_split ? 32 : 0)))
+            return 1;
         if (rows > 0) {
             if (SL.n.reserve((size_t)rows * 4) || SL.x.reserve((size_t)rows * 4) ||
                 SL.cn.reserve((size_t)rows * cn_itemsize) || SL.out.reserve((size_t)rows))
@@ -341,6 +450,12 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
                                      cudaMemcpyHostToDevice, st));
             SGB_CUDA(cudaStreamWaitEvent(st, C->ev_setup, 0));
             SgbRawIn raw = {(const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, rows, C->d_err};
+            if (use_split) {
+                const SgbColsIn in = {SL.n.p, SL.x.p, SL.cn.p, cn_itemsize == 4 ? SGB_IN_I32_I32 : SGB_IN_I32_U8, rows, C->d_err};
+                std::vector<SplitSlice> slices;
+                if (run_split(SL.split, slices, SL.hp, pd, in, C->d_tabs, m, (uint8_t*)SL.out.p, C->sm_count, st, nullptr, nullptr))
+                    return 1;
+            } else {
             if (cn_itemsize == 4) {
                 // an int32 cn column (R integers) is narrowed to uint8 on the device when that lets k_decode read in place
                 SgbRawIn probe = raw;
@@ -360,6 +475,7 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
                                  (uint8_t*)SL.bp.p, (int*)SL.last_state.p, SL.counter, C->sm_count, stage, st));
             if (m.decode == SGB_DECODE_CHAINED)
                 SGB_CUDA(sgbk_backtrace(pd, (const uint8_t*)SL.bp.p, (const int*)SL.last_state.p, S, (uint8_t*)SL.out.p, st));
+            }
             SGB_CUDA(cudaMemcpyAsync(state_out + r0, SL.out.p, (size_t)rows, cudaMemcpyDeviceToHost, st));
             if (loglik_out) {
                 SGB_CUDA(sgbk_loglik((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, pd,
@@ -435,6 +551,7 @@ int sgb_shutdown(void)
             if (s.st) { cudaStreamSynchronize(s.st); cudaStreamDestroy(s.st); }
             s.n.release(); s.x.release(); s.cn.release(); s.cn8.release(); s.out.release(); s.packed.release(); s.bp.release();
             s.last_state.release(); s.pin.release(); s.goff.release(); s.ostart.release(); s.len.release(); s.loglik.release();
+            s.split.release();
             if (s.counter) cudaFree(s.counter);
         }
         c->scratch_a.release(); c->scratch_b.release(); c->scratch_c.release(); c->scratch_d.release();
@@ -510,14 +627,17 @@ struct sgb_plan {
     int n_states = 0, decode = 0;
     HostPlan hp;
     DevBuf goff, ostart, len, packed, cn8, bp, last_state;
+    SplitWork split;                        // split schedule scratch (reserved by the first call that takes it)
+    std::vector<SplitSlice> slices;
     unsigned int* counter = nullptr;
     int* d_err = nullptr;
     SgbDevTables* d_tabs = nullptr;
     SgbPlanDev pd;
-    // optional per-call kernel timing: ring of event triples (before pack, after pack, after decode)
+    // optional per-call kernel timing: ring of event quadruples (start, after pack / split preparation, after k_emit,
+    // after k_decode / k_recur)
     bool timing = false;
     static const int kRing = 64;
-    cudaEvent_t ev[kRing][3];
+    cudaEvent_t ev[kRing][4];
     bool ev_ready = false;
     long long calls = 0;
     int last_stage = -1;
@@ -535,7 +655,13 @@ int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_s
     if (get_ctx(&C)) return 1;
     sgb_plan* pl = new sgb_plan();
     pl->device = C->device; pl->N = N; pl->n_states = n_states; pl->decode = decode;
-    if (build_host_plan(seg_off, 0, nseg, 0, pl->hp, (long long)C->sm_count * 16, C->group_hint)) { delete pl; return 1; }
+    {
+        // the split schedule (the default for decode = reference) wants full groups of 32: its emission kernel is not
+        // starved by small batches, and narrow groups would only add empty plan entries
+        SgbModelArgs probe; probe.decode = decode;
+        const int hint = C->group_hint ? C->group_hint : (want_split(probe, nseg) ? 32 : 0);
+        if (build_host_plan(seg_off, 0, nseg, 0, pl->hp, (long long)C->sm_count * 16, hint)) { delete pl; return 1; }
+    }
     size_t ns = (size_t)pl->hp.nseq;
     size_t ng = pl->hp.goff.size();
     // the narrowed-cn buffer (1 B per cell-bin) is always reserved; the packed-record buffer (8 B per cell-bin) is only
@@ -575,7 +701,8 @@ int sgb_plan_destroy(sgb_plan* pl)
     if (!pl) return 0;
     if (pl->ev_ready)
         for (int i = 0; i < sgb_plan::kRing; i++)
-            for (int j = 0; j < 3; j++) cudaEventDestroy(pl->ev[i][j]);
+            for (int j = 0; j < 4; j++) cudaEventDestroy(pl->ev[i][j]);
+    pl->split.release();
     pl->goff.release(); pl->ostart.release(); pl->len.release(); pl->packed.release(); pl->cn8.release(); pl->bp.release();
     pl->last_state.release();
     if (pl->counter) cudaFree(pl->counter);
@@ -597,7 +724,7 @@ int sgb_plan_reserve_packed(sgb_plan* pl)
 int64_t sgb_plan_scratch_bytes(const sgb_plan* pl)
 {
     if (!pl) return 0;
-    return (int64_t)(pl->packed.cap + pl->cn8.cap + pl->bp.cap + pl->last_state.cap + pl->goff.cap + pl->ostart.cap + pl->len.cap);
+    return (int64_t)(pl->split.bytes() + pl->packed.cap + pl->cn8.cap + pl->bp.cap + pl->last_state.cap + pl->goff.cap + pl->ostart.cap + pl->len.cap);
 }
 
 int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t* d_n, const int32_t* d_x,
@@ -620,6 +747,18 @@ int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t*
     SGB_CUDA(sgbk_setup(pl->d_tabs, m, params->eps, params->Abias, params->selftransitionprob, st));
     const int slot = (int)(pl->calls % sgb_plan::kRing);
     if (pl->timing) SGB_CUDA(cudaEventRecord(pl->ev[slot][0], st));
+    if (want_split(m, pl->hp.nseq)) {
+        // ---- split schedule: k_emit (lanes over bins) + k_recur (lane per sequence), sliced if the batch is huge
+        const SgbColsIn in = {d_n, d_x, d_cn, cn_itemsize == 4 ? SGB_IN_I32_I32 : SGB_IN_I32_U8, (long long)pl->N, pl->d_err};
+        if (run_split(pl->split, pl->slices, pl->hp, pl->pd, in, pl->d_tabs, m, d_state_out, C->sm_count, st,
+                      pl->timing ? pl->ev[slot][1] : nullptr, pl->timing ? pl->ev[slot][2] : nullptr))
+            return 1;
+        pl->last_stage = 4;
+        if (pl->timing) { SGB_CUDA(cudaEventRecord(pl->ev[slot][3], st)); pl->calls++; }
+        if (d_loglik_out)
+            SGB_CUDA(sgbk_loglik(d_n, d_x, d_cn, cn_itemsize, pl->pd, pl->d_tabs, m, d_loglik_out, st));
+        return 0;
+    }
     SgbRawIn raw = {d_n, d_x, d_cn, cn_itemsize, (long long)pl->N, pl->d_err};
     bool narrowed = false;
     if (cn_itemsize == 4 && ((unsigned long long)d_cn & 15ull) == 0) {
@@ -636,10 +775,10 @@ int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t*
     pl->last_stage = (stage == 2 && narrowed) ? 3 : stage;
     if (stage != 2)
         SGB_CUDA(sgbk_pack(d_n, d_x, d_cn, cn_itemsize, pl->pd, (unsigned long long*)pl->packed.p, pl->d_err, st));
-    if (pl->timing) SGB_CUDA(cudaEventRecord(pl->ev[slot][1], st));
+    if (pl->timing) { SGB_CUDA(cudaEventRecord(pl->ev[slot][1], st)); SGB_CUDA(cudaEventRecord(pl->ev[slot][2], st)); }
     SGB_CUDA(sgbk_decode(pl->pd, (const unsigned long long*)pl->packed.p, raw, pl->d_tabs, m, d_state_out,
                          (uint8_t*)pl->bp.p, (int*)pl->last_state.p, pl->counter, C->sm_count, stage, st));
-    if (pl->timing) { SGB_CUDA(cudaEventRecord(pl->ev[slot][2], st)); pl->calls++; }
+    if (pl->timing) { SGB_CUDA(cudaEventRecord(pl->ev[slot][3], st)); pl->calls++; }
     if (m.decode == SGB_DECODE_CHAINED)
         SGB_CUDA(sgbk_backtrace(pl->pd, (const uint8_t*)pl->bp.p, (const int*)pl->last_state.p, m.S, d_state_out, st));
     if (d_loglik_out)
@@ -654,7 +793,7 @@ int sgb_plan_enable_timing(sgb_plan* pl, int32_t on)
     if (!pl) return fail("plan is NULL");
     if (on && !pl->ev_ready) {
         for (int i = 0; i < sgb_plan::kRing; i++)
-            for (int j = 0; j < 3; j++) SGB_CUDA(cudaEventCreate(&pl->ev[i][j]));
+            for (int j = 0; j < 4; j++) SGB_CUDA(cudaEventCreate(&pl->ev[i][j]));
         pl->ev_ready = true;
     }
     pl->timing = on != 0;
@@ -662,21 +801,48 @@ int sgb_plan_enable_timing(sgb_plan* pl, int32_t on)
     return 0;
 }
 
-int sgb_plan_read_timing(sgb_plan* pl, int32_t max_records, float* pack_ms, float* decode_ms, int32_t* n_out)
+int sgb_plan_read_timing3(sgb_plan* pl, int32_t max_records, float* prep_ms, float* emit_ms, float* decode_ms, int32_t* n_out)
 {
-    if (!pl || !pack_ms || !decode_ms || !n_out) return fail("NULL pointer");
+    if (!pl || !prep_ms || !emit_ms || !decode_ms || !n_out) return fail("NULL pointer");
     *n_out = 0;
     if (!pl->ev_ready) return 0;
     long long have = pl->calls < sgb_plan::kRing ? pl->calls : sgb_plan::kRing;
     if (have > max_records) have = max_records;
     for (long long i = 0; i < have; i++) {
         int slot = (int)((pl->calls - have + i) % sgb_plan::kRing);
-        SGB_CUDA(cudaEventSynchronize(pl->ev[slot][2]));
-        SGB_CUDA(cudaEventElapsedTime(&pack_ms[i], pl->ev[slot][0], pl->ev[slot][1]));
-        SGB_CUDA(cudaEventElapsedTime(&decode_ms[i], pl->ev[slot][1], pl->ev[slot][2]));
+        SGB_CUDA(cudaEventSynchronize(pl->ev[slot][3]));
+        SGB_CUDA(cudaEventElapsedTime(&prep_ms[i], pl->ev[slot][0], pl->ev[slot][1]));
+        SGB_CUDA(cudaEventElapsedTime(&emit_ms[i], pl->ev[slot][1], pl->ev[slot][2]));
+        SGB_CUDA(cudaEventElapsedTime(&decode_ms[i], pl->ev[slot][2], pl->ev[slot][3]));
     }
     *n_out = (int32_t)have;
     return 0;
+}
+
+int sgb_plan_read_timing(sgb_plan* pl, int32_t max_records, float* pack_ms, float* decode_ms, int32_t* n_out)
+{
+    if (!pl || !pack_ms || !decode_ms || !n_out) return fail("NULL pointer");
+    std::vector<float> em((size_t)(max_records > 0 ? max_records : 1));
+    if (sgb_plan_read_timing3(pl, max_records, pack_ms, em.data(), decode_ms, n_out)) return 1;
+    for (int i = 0; i < *n_out; i++) decode_ms[i] += em[(size_t)i];          // two-phase view: preparation | kernels
+    return 0;
+}
+
+int sgb_plan_reserve_split(sgb_plan* pl)
+{
+    if (!pl) return fail("plan is NULL");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    if (C->device != pl->device) return fail("plan belongs to another device");
+    if (pl->slices.empty()) pl->slices = split_slices(pl->hp.len, pl->n_states, split_budget_bytes());
+    SgbSplitSizes zmax = sgbk_split_sizes(0, 0, 0, pl->n_states);
+    for (const SplitSlice& sl : pl->slices) {
+        const SgbSplitSizes z = sgbk_split_sizes(sl.q1 - sl.q0, sl.rows, sl.maxlen, pl->n_states);
+        zmax.cls = std::max(zmax.cls, z.cls); zmax.perm = std::max(zmax.perm, z.perm); zmax.part = std::max(zmax.part, z.part);
+        zmax.g_i32 = std::max(zmax.g_i32, z.g_i32); zmax.g_i64 = std::max(zmax.g_i64, z.g_i64);
+        zmax.e_bytes = std::max(zmax.e_bytes, z.e_bytes);
+    }
+    return pl->split.reserve(zmax);
 }
 
 int sgb_plan_check(sgb_plan* pl, void* stream)

@@ -574,3 +574,79 @@ SGB_HD void sgb_seq_step_chained(SgbSeqState<SMAX>& st, const double* e, int S, 
     for (int i = 0; i < SMAX; i++) st.T1[i] = Tn[i];
     sgb_top2<SMAX>(st, S);
 }
+
+// ------------------------------------------------------------------ register-resident recursion (split schedule)
+// The split schedule (k_emit + k_recur) hands every lane the emissions of its sequence's bin as NL doubles, NL a
+// multiple of 4 that bounds the live states of the WHOLE sequence (states >= NL are -Inf in every bin and therefore
+// in every forward column).  Same arithmetic, in the same order, as sgb_seq_init_mem / sgb_seq_step_mem_nl above, with
+// the forward column in registers.
+template <int NL>
+SGB_HD void sgb_seq_init_r(double (&T1)[NL], const double (&e)[NL], double init, double& m1)
+{
+    double best = -sgb_inf();
+#pragma unroll
+    for (int i = 0; i < NL; i++) {
+        const double v = sgb_add(init, e[i]);        // e[i] = -Inf for masked states and for states >= S
+        T1[i] = v;
+        best = (v > best) ? v : best;
+    }
+    m1 = best;
+}
+
+template <int NL>
+SGB_HD int sgb_seq_step_r(double (&T1)[NL], const double (&e)[NL], double& m1io, double tr_self, double tr_off)
+{
+    double Tn[NL];
+    const double u1 = sgb_add(m1io, tr_off);
+#pragma unroll
+    for (int i = 0; i < NL; i++) {
+        const double td = sgb_add(T1[i], tr_self);
+        Tn[i] = sgb_add((td > u1) ? td : u1, e[i]);
+    }
+    double tv[NL];
+    int ti[NL];
+#pragma unroll
+    for (int i = 0; i < NL; i++) { tv[i] = Tn[i]; ti[i] = i; }
+#pragma unroll
+    for (int stride = 1; stride < NL; stride *= 2) {
+#pragma unroll
+        for (int i = 0; i + stride < NL; i += 2 * stride) {
+            const bool gt = tv[i + stride] > tv[i];
+            tv[i] = gt ? tv[i + stride] : tv[i];
+            ti[i] = gt ? ti[i + stride] : ti[i];
+        }
+    }
+    const double m1 = tv[0];
+    const int i1 = ti[0];
+    int back = i1;
+    double ej = e[0];
+#pragma unroll
+    for (int i = 1; i < NL; i++) ej = (i == i1) ? e[i] : ej;
+    if (m1 == sgb_add(u1, ej)) {
+        // see sgb_seq_step_mem_nl: first k with (T1[k] + tr[k,i1]) + e[i1] == m1 (src/code.cpp:29-31)
+        double tj = T1[0];
+#pragma unroll
+        for (int i = 1; i < NL; i++) tj = (i == i1) ? T1[i] : tj;
+        unsigned int pm = 0;
+#pragma unroll
+        for (int k = 0; k < NL; k++) {
+            const double val = sgb_add(sgb_add(T1[k], tr_off), ej);
+            pm |= (val == m1) ? (1u << k) : 0u;
+        }
+        const double wd = sgb_add(sgb_add(tj, tr_self), ej);
+        pm = (pm & ~(1u << i1)) | ((wd == m1) ? (1u << i1) : 0u);
+        back = sgb_ffs32(pm) - 1;
+    }
+#pragma unroll
+    for (int i = 0; i < NL; i++) T1[i] = Tn[i];
+    m1io = m1;
+    return back;
+}
+
+// number of 4-state planes a sequence whose largest live-state count is L needs; the recursion kernels are compiled
+// for 1, 2, 3, 4, 6 and 8 planes
+SGB_HD int sgb_planes_for(int L)
+{
+    const int p = (L + 3) >> 2;
+    return p <= 4 ? p : (p <= 6 ? 6 : 8);
+}

@@ -762,6 +762,8 @@ cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_pack
     return cudaErrorInvalidValue;
 }
 
+#include "split_kernels.cuh"
+
 // ------------------------------------------------------------------ k_backtrace (decode = chained)
 __global__ void k_backtrace(SgbPlanDev plan, const uint8_t* __restrict__ bp, const int* __restrict__ last_state,
                             int S, uint8_t* __restrict__ state_out)

@@ -44,6 +44,8 @@ struct SgbModelArgs {
 #define SGB_ERR_NEGATIVE_COUNT 1
 #define SGB_ERR_COUNT_TOO_LARGE 2
 #define SGB_ERR_BAD_CN 4
+#define SGB_ERR_NOT_INTEGER 8          // a double-typed column holds NaN or a non-integer value
+#define SGB_ERR_INTERNAL 16            // a scratch-size bound was violated (a bug, never an input problem)
 
 cudaError_t sgbk_setup(SgbDevTables* d_tabs, const SgbModelArgs& m, double eps, double Abias, double stp,
                        cudaStream_t st);
@@ -82,5 +84,44 @@ cudaError_t sgbk_postprocess(const void* d_cn, int cn_itemsize, const uint8_t* d
 cudaError_t sgbk_pass_stats(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,
                             const uint8_t* d_path, long long N, int S, unsigned long long* d_out, cudaStream_t st);
 size_t sgbk_viterbi_bp_bytes(long long T, int S);
+
+// ---- split schedule (split_kernels.cuh): k_emit (lanes over bins) + k_recur (lane per sequence, TMA-fed) ----
+#define SGB_IN_I32_U8 0                   // n, x int32; cn uint8
+#define SGB_IN_I32_I32 1                  // n, x, cn int32 (R integer columns)
+#define SGB_IN_U16_U8 2                   // n, x uint16; cn uint8 (host-narrowed staging)
+#define SGB_IN_F64 3                      // n, x, cn double (R numeric columns); must be integer valued
+struct SgbColsIn {
+    const void* n;
+    const void* x;
+    const void* cn;
+    int kind;
+    long long rows;
+    int* err;
+};
+struct SgbSplitDev {
+    uint8_t* cls;              // [nseq] planes needed by host-plan sequence i (0 = empty)
+    int* perm;                 // [gcap * 32] partitioned position -> host-plan sequence, -1 = empty lane
+    unsigned int* part;        // [ntile * 9] per-tile class histograms, then bases
+    int* g_npl;                // [gcap]
+    int* g_tmax;               // [gcap]
+    long long* g_eoff;         // [gcap] first 32-byte sector of the group's tile
+    unsigned long long* g_size;// [gcap] tile size in sectors
+    int* ngroups;              // [1]
+    unsigned int* counters;    // [2] dynamic work counters (k_emit, k_recur)
+    double* E;                 // emission tiles
+    long long e_cap_sectors;
+    int gcap;
+    int ntile;
+};
+// scratch sizes for a range of `nseq` plan entries whose lengths sum to `rows` and whose longest has `maxlen` bins
+struct SgbSplitSizes {
+    size_t cls, perm, part, g_i32, g_i64, e_bytes;
+    int gcap, ntile;
+};
+SgbSplitSizes sgbk_split_sizes(long long nseq, long long rows, int maxlen, int S);
+// plan entries [0, nseq) of `plan` (len-descending order); d_tabs must already hold the call's constants
+cudaError_t sgbk_split_decode(const SgbPlanDev& plan, long long nseq, const SgbColsIn& in, const SgbDevTables* d_tabs,
+                              const SgbModelArgs& m, const SgbSplitDev& W, uint8_t* d_state_out, int sm_count,
+                              cudaStream_t st, cudaEvent_t ev_prep, cudaEvent_t ev_mid);
 void sgb_internal_set_error(const char* msg);      // sets the calling thread's sgb_last_error() text (capi.cu)
 cudaError_t sgbk_fp64_peak(int iters, int sm_count, cudaStream_t st, double* tflops);

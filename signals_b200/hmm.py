@@ -195,11 +195,23 @@ class DevicePlan:
         check(self._lib.sgb_plan_read_timing(self._h, max_records, _ptr(pk), _ptr(dc), ctypes.byref(k)))
         return pk[: k.value].copy(), dc[: k.value].copy()
 
+    def read_timing3(self, max_records=64):
+        """(prep_ms[], emit_ms[], decode_ms[]): preparation (k_pack or the split schedule's partition kernels), k_emit
+        (0 on the fused schedule), k_decode / k_recur -- CUDA events on the launch stream"""
+        a = np.zeros(max_records, np.float32); b = np.zeros(max_records, np.float32); c = np.zeros(max_records, np.float32)
+        k = ctypes.c_int32(0)
+        check(self._lib.sgb_plan_read_timing3(self._h, max_records, _ptr(a), _ptr(b), _ptr(c), ctypes.byref(k)))
+        return a[: k.value].copy(), b[: k.value].copy(), c[: k.value].copy()
+
+    def reserve_split(self):
+        check(self._lib.sgb_plan_reserve_split(self._h))
+
     def scratch_bytes(self):
         return int(self._lib.sgb_plan_scratch_bytes(self._h))
 
     def last_staging(self):
-        """2 = the last decode read the caller's columns in place, 1 / 0 = via k_pack's records, -1 = no call yet"""
+        """4 = split schedule (k_emit + k_recur), 2 / 3 = fused kernel reading the caller's columns in place, 1 / 0 = fused
+        kernel via k_pack's records, -1 = no call yet"""
         return int(self._lib.sgb_plan_last_staging(self._h))
 
     def close(self):

@@ -114,3 +114,83 @@ extern "C" int emu_decode_sequence(int model, int lik, int S, int decode, double
     return 0;
 }
 
+
+// ---- the split schedule's per-lane work: emissions of the live states as k_emit writes them (planes of 4 states, -Inf
+// beyond the bin's live states), then the register-resident recursion of k_recur with NL = 4 x planes_for(largest live
+// count of the sequence) states.
+template <int NPL, int MODEL, int LIKBB>
+static void run_split(int S, double loherror, double eps, double rho, double Abias, double stp, long T, const int* n,
+                      const int* x, const int* cn, unsigned char* out)
+{
+    constexpr int NL = 4 * NPL;
+    const int lik = LIKBB ? SGB_LIK_BETABINOMIAL : SGB_LIK_BINOMIAL;
+    SgbScalars sp = sgb_scalars(S, eps, Abias, stp, LIKBB ? rho : 0.0, LT);
+    std::vector<double> tLP(SGB_CN_TABLE * S), tLQ(SGB_CN_TABLE * S), tA(SGB_CN_TABLE * S), tB(SGB_CN_TABLE * S), tL0(SGB_CN_TABLE * S);
+    std::vector<int> tK(SGB_CN_TABLE * S);
+    std::vector<double> tG((size_t)SGB_CN_TABLE * S * 2 * SGB_LGK, 0.0);
+    for (int c = 0; c < SGB_CN_TABLE; c++)
+        for (int m = 0; m < S; m++) {
+            SgbStateConst sc = sgb_state_const(c, m, loherror, lik, rho, sp.bb_s, LT);
+            int i = c * S + m;
+            tLP[i] = sc.lp; tLQ[i] = sc.lq; tA[i] = sc.a; tB[i] = sc.b; tL0[i] = sc.l0; tK[i] = sc.kind;
+            if (LIKBB && sc.kind == SGB_KIND_NORMAL)
+                for (int k = 0; k < SGB_LGK; k++) {
+                    tG[(size_t)i * 2 * SGB_LGK + k] = sgb_lgamma_pos(sgb_add(sc.a, (double)k), LT);
+                    tG[(size_t)i * 2 * SGB_LGK + SGB_LGK + k] = sgb_lgamma_pos(sgb_add(sc.b, (double)k), LT);
+                }
+        }
+    SgbTables TB;
+    TB.LT = LT; TB.ET = ET; TB.LP = tLP.data(); TB.LQ = tLQ.data(); TB.pstride = 1; TB.A = tA.data(); TB.B = tB.data();
+    TB.L0 = tL0.data(); TB.LGK = tG.data(); TB.KIND = tK.data(); TB.S = S; TB.lik = lik; TB.loherror = loherror; TB.rho = rho;
+    double T1[NL], m1 = 0.0;
+    SgbSeqState<NL> st;
+    const int Seff = S < NL ? S : NL;
+    for (long t = 0; t < T; t++) {
+        SgbBin b = sgb_bin_prepare(MODEL, LIKBB, n[t], x[t], cn[t], sp.bb_s, LF, LT);
+        const int L = sgb_live_states(MODEL, b.cprime, S);
+        double e[NL];
+        for (int m = 0; m < NL; m++)
+            e[m] = m < L ? sgb_emit_item<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, m, TB, sp)
+                         : -sgb_inf();
+        int back = 0;
+        if (sp.diag_dominant) {
+            if (t == 0) sgb_seq_init_r<NL>(T1, e, sp.init, m1);
+            else back = sgb_seq_step_r<NL>(T1, e, m1, sp.tr_self, sp.tr_off);
+        } else {
+            if (t == 0) sgb_seq_init<NL>(st, e, Seff, sp.init);
+            else back = sgb_seq_step_general<NL>(st, e, Seff, sp.tr_self, sp.tr_off);
+        }
+        if (t > 0) out[t - 1] = (unsigned char)back;
+    }
+    out[T - 1] = (T > 1) ? out[T - 2] : 0;
+}
+
+template <int NPL>
+static void run_split_s(int model, int lik_bb, int S, double loherror, double eps, double rho, double Abias, double stp, long T,
+                        const int* n, const int* x, const int* cn, unsigned char* out)
+{
+    if (model == 0 && !lik_bb) run_split<NPL, 0, 0>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out);
+    else if (model == 0) run_split<NPL, 0, 1>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out);
+    else if (!lik_bb) run_split<NPL, 1, 0>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out);
+    else run_split<NPL, 1, 1>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out);
+}
+
+extern "C" int emu_decode_sequence_split(int model, int lik, int S, double loherror, double eps, double rho, double Abias,
+                                         double stp, long T, const int* n, const int* x, const int* cn, unsigned char* out)
+{
+    if (T <= 0) return 0;
+    if (S < 1 || S > 32) return -1;
+    const int lik_bb = (lik == SGB_LIK_BETABINOMIAL) && rho > 0.0;
+    int mx = 0;
+    for (long t = 0; t < T; t++) { int c = cn[t] < 0 ? 0 : (cn[t] > 255 ? 255 : cn[t]); if (c > mx) mx = c; }
+    const int npl = sgb_planes_for(sgb_live_states(model, sgb_cprime(model, mx), S));
+    switch (npl) {
+    case 1: run_split_s<1>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
+    case 2: run_split_s<2>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
+    case 3: run_split_s<3>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
+    case 4: run_split_s<4>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
+    case 6: run_split_s<6>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
+    default: run_split_s<8>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
+    }
+    return 0;
+}

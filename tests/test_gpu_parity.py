@@ -29,6 +29,13 @@ def _bits(a):
     return np.ascontiguousarray(a, dtype=np.float64).view(np.uint64)
 
 
+@pytest.fixture(params=["split", "fused"])
+def sched(request, monkeypatch):
+    """both schedules of the reference decode: "split" (k_emit + k_recur, the default) and "fused" (k_decode)"""
+    monkeypatch.setenv("SGB_SCHED", request.param)
+    return request.param
+
+
 def test_device_math_bits_equal_host_bits(oracle):
     """the deterministic math gives the same bits on the device as on the host, function by function"""
     rng = np.random.default_rng(1)
@@ -67,7 +74,7 @@ def test_logspace_addcpp_scalar(oracle):
 
 
 @pytest.mark.parametrize("ps", cases.PARAM_SETS, ids=IDS)
-def test_edge_sequences_bit_exact(oracle, ps):
+def test_edge_sequences_bit_exact(oracle, ps, sched):
     g = np.load(GOLD)
     n, x, cn, seg = g["edge_n"], g["edge_x"], g["edge_cn"], g["edge_seg"]
     P = oracle.params(**cases.param_dict(ps))
@@ -94,7 +101,7 @@ def test_edge_sequences_bit_exact(oracle, ps):
 
 
 @pytest.mark.parametrize("ps", cases.PARAM_SETS[:5], ids=IDS[:5])
-def test_small_cohort_bit_exact_vs_golden(oracle, ps):
+def test_small_cohort_bit_exact_vs_golden(oracle, ps, sched):
     g = np.load(GOLD)
     d = cases.small_cohort("betabinomial" if ps[2] == "betabinomial" else "binomial")
     got = hmm.decode_arrays(d["n"], d["x"], d["cn"], d["seg_off"], **_kw(ps))
@@ -116,7 +123,7 @@ def test_libm_oracle_differs_only_at_structural_ties(oracle):
     assert (d["cn"][diff] == 0).all()       # mirror-image likelihoods at CN 0: exact ties decided by rounding
 
 
-def test_chunked_pipeline_is_invariant(oracle, monkeypatch):
+def test_chunked_pipeline_is_invariant(oracle, monkeypatch, sched):
     d = cases.small_cohort("binomial", n_cells=30, seed=8)
     ps = cases.PARAM_SETS[0]
     ref = hmm.decode_arrays(d["n"], d["x"], d["cn"], d["seg_off"], **_kw(ps))
@@ -127,7 +134,7 @@ def test_chunked_pipeline_is_invariant(oracle, monkeypatch):
     monkeypatch.delenv("SGB_CHUNK_BINS")
 
 
-def test_empty_and_degenerate_inputs():
+def test_empty_and_degenerate_inputs(sched):
     ps = cases.PARAM_SETS[0]
     e = np.zeros(0, np.int32)
     out = hmm.decode_arrays(e, e, e, np.zeros(1, np.int64), **_kw(ps))
@@ -139,7 +146,7 @@ def test_empty_and_degenerate_inputs():
     assert out.tolist() == [1, 1, 0]        # T=2 sequence repeats its first call; T=1 sequence yields 0
 
 
-def test_input_validation_errors():
+def test_input_validation_errors(sched):
     ps = cases.PARAM_SETS[0]
     n = np.array([10, 12], np.int32); x = np.array([5, 6], np.int32); cn = np.array([2, 2], np.int32)
     seg = np.array([0, 2], np.int64)
@@ -283,7 +290,7 @@ def test_r_level_mirror_end_to_end(oracle):
     assert "state_min" in a1.columns and len(a1) == len(cell)
 
 
-def test_device_resident_api_matches_host_api(oracle):
+def test_device_resident_api_matches_host_api(oracle, sched):
     import torch
     d = cases.small_cohort("binomial", n_cells=50, seed=12)
     ps = cases.PARAM_SETS[0]
@@ -316,10 +323,11 @@ def test_device_resident_api_matches_host_api(oracle):
     plan.close()
 
 
-def test_in_place_and_packed_staging_agree(oracle):
-    """k_decode reads 16-byte aligned uint8-cn columns in place; anything else goes through k_pack's packed
+def test_in_place_and_packed_staging_agree(oracle, monkeypatch):
+    """(fused schedule) k_decode reads 16-byte aligned uint8-cn columns in place; anything else goes through k_pack's packed
     records.  Same rows at aligned and misaligned addresses, ragged lengths, column end inside a 4-bin block."""
     import torch
+    monkeypatch.setenv("SGB_SCHED", "fused")
     d = cases.small_cohort("binomial", n_cells=40, seed=21)
     keep = d["seg_off"][-2] + 3                      # cut the last sequence to 3 bins: N is not a multiple of 4
     seg = d["seg_off"].copy(); seg[-1] = keep
@@ -359,7 +367,7 @@ def test_in_place_and_packed_staging_agree(oracle):
 
 
 @pytest.mark.parametrize("seed", range(cases.N_RANDOM_CASES))
-def test_randomised_models_and_inputs_bit_exact(oracle, seed):
+def test_randomised_models_and_inputs_bit_exact(oracle, seed, sched):
     """random state counts (all three kernel buckets), transition regimes, eps / Abias / loherror settings, total copy
     numbers beyond the tables and the state space, counts on both sides of every log-factorial branch, counts
     outside the support, 1-bin sequences; uint8 (in place) and int32 (narrowed) copy-number columns"""
@@ -445,7 +453,7 @@ def test_full_size_properties(oracle, model, lik, rho):
 
 @pytest.mark.parametrize("model,lik,rho", [("hscn", "binomial", 0.0), ("ascn", "betabinomial", 0.02),
                                            ("ascn", "binomial", 0.0), ("hscn", "betabinomial", 0.02)])
-def test_long_sequences_30000_bin_grid(oracle, model, lik, rho):
+def test_long_sequences_30000_bin_grid(oracle, model, lik, rho, sched):
     """BASELINE.json configs[4] geometry (23 sequences of 476..2,463 bins per cell), 200 cells = 6 M cell-bins, against the
     oracle: reference and chained decode, uint8 and int32 copy-number columns through the host API, and 16-byte
     aligned / one-element-offset device columns through the device API (in-place ring vs packed records)."""

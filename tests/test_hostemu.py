@@ -33,6 +33,15 @@ def _emu_decode(E, d, kw, decode):
         a, b = int(so[s]), int(so[s + 1])
         if b == a:
             continue
+        if decode == "split":
+            # the split schedule (k_emit + k_recur): plane-padded emissions + register-resident recursion
+            rc = E.emu_decode_sequence_split(1 if kw["model"] == "ascn" else 0, 1 if kw["likelihood"] == "betabinomial" else 0,
+                                             kw["S"], D(kw["loherror"]), D(kw["eps"]), D(kw["rho"]), D(kw["Abias"]),
+                                             D(kw["selftransitionprob"]), ctypes.c_long(b - a),
+                                             n[a:b].ctypes.data_as(ctypes.c_void_p), x[a:b].ctypes.data_as(ctypes.c_void_p),
+                                             cn[a:b].ctypes.data_as(ctypes.c_void_p), out[a:b].ctypes.data_as(ctypes.c_void_p))
+            assert rc == 0
+            continue
         rc = E.emu_decode_sequence(1 if kw["model"] == "ascn" else 0, 1 if kw["likelihood"] == "betabinomial" else 0,
                                    kw["S"], decode, D(kw["loherror"]), D(kw["eps"]), D(kw["rho"]), D(kw["Abias"]),
                                    D(kw["selftransitionprob"]), ctypes.c_long(b - a),
@@ -50,11 +59,11 @@ def test_core_bit_exact_vs_oracle(oracle, emu, ps):
     d = cases.small_cohort("betabinomial" if kw["likelihood"] == "betabinomial" else "binomial", n_cells=4, seed=3)
     n = np.concatenate((n, d["n"])); x = np.concatenate((x, d["x"])); cn = np.concatenate((cn, d["cn"].astype(np.int32)))
     seg = np.concatenate((seg, seg[-1] + d["seg_off"][1:]))
-    for decode, dname in ((0, "reference"), (1, "chained")):
+    for decode, dname in ((0, "reference"), (1, "chained"), ("split", "reference")):
         P = oracle.params(**kw, decode=dname)
         ref = oracle.decode_batch(n, x, cn, seg, P, oracle.MATH_DET)
         got = _emu_decode(emu, (n, x, cn, seg), kw, decode)
-        assert np.array_equal(ref, got), (ps[0], dname, int((ref != got).sum()))
+        assert np.array_equal(ref, got), (ps[0], decode, int((ref != got).sum()))
 
 
 @pytest.mark.parametrize("seed", range(cases.N_RANDOM_CASES))
@@ -64,7 +73,7 @@ def test_core_bit_exact_on_randomised_cases(oracle, emu, seed):
     kw = dict(model=g["model"], likelihood=g["likelihood"], S=g["n_states"], loherror=g["loherror"], eps=g["eps"],
               rho=g["rho"], Abias=g["Abias"], selftransitionprob=g["selftransitionprob"])
     cn = cn.astype(np.int32)
-    for decode, dname in ((0, "reference"), (1, "chained")):
+    for decode, dname in ((0, "reference"), (1, "chained"), ("split", "reference")):
         ref = oracle.decode_batch(n, x, cn, seg, oracle.params(**kw, decode=dname), oracle.MATH_DET)
         got = _emu_decode(emu, (n, x, cn, seg), kw, decode)
-        assert np.array_equal(ref, got), (kw, dname, np.nonzero(ref != got)[0][:8])
+        assert np.array_equal(ref, got), (kw, decode, np.nonzero(ref != got)[0][:8])
