@@ -103,6 +103,9 @@ SGB_API int sgb_plan_reserve_packed(sgb_plan* plan);
  * 4-state plane (96 B for maxCN = 11, usually ~41), capped at SGB_E_BUDGET_MB (default 8192) by decoding very large
  * batches in slices.  It is allocated by the first decode call of a plan, or up front by sgb_plan_reserve_split. */
 SGB_API int sgb_plan_reserve_split(sgb_plan* plan);
+/* diagnostic: after a split-schedule call, the number of 32-sequence groups and the bytes of emission tiles that
+ * k_emit wrote and k_recur read (of the last slice); zeros after a fused-schedule call */
+SGB_API int sgb_plan_split_info(sgb_plan* plan, void* stream, int64_t* ngroups_out, int64_t* e_bytes_out);
 SGB_API int sgb_plan_destroy(sgb_plan* plan);
 SGB_API int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* plan, const int32_t* d_n, const int32_t* d_x,
                           const void* d_cn, int32_t cn_itemsize, uint8_t* d_state_out, double* d_loglik_out,

@@ -40,6 +40,7 @@ SIGNATURES = {
     "sgb_plan_destroy": (ctypes.c_int, [_vp]),
     "sgb_plan_reserve_packed": (ctypes.c_int, [_vp]),
     "sgb_plan_reserve_split": (ctypes.c_int, [_vp]),
+    "sgb_plan_split_info": (ctypes.c_int, [_vp, _vp, ctypes.POINTER(_i64), ctypes.POINTER(_i64)]),
     "sgb_plan_read_timing3": (ctypes.c_int, [_vp, _i32, _vp, _vp, _vp, ctypes.POINTER(_i32)]),
     "sgb_hmm_decode_device": (ctypes.c_int, [_PP, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "sgb_plan_check": (ctypes.c_int, [_vp, _vp]),

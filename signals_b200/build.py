@@ -11,8 +11,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libsignals_b200.so")
-SOURCES = ["hmm_kernels.cu", "capi.cu", "noalloc.cu"]
-HEADERS = ["sgb_math.h", "sgb_tables.h", "hmm_core.cuh", "kernels.h", os.path.join("..", "..", "include", "signals_b200.h")]
+SOURCES = ["hmm_kernels.cu", "split_kernels.cu", "capi.cu", "noalloc.cu"]
+HEADERS = ["sgb_math.h", "sgb_tables.h", "hmm_core.cuh", "kernels.h", "sgb_async.cuh", os.path.join("..", "..", "include", "signals_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -151,15 +151,20 @@ size_t split_budget_bytes()
     return (size_t)mb << 20;
 }
 
-// which schedule a decode = reference call takes: 1 = split (k_emit + k_recur), 0 = fused k_decode
+// Which schedule a decode = reference call takes: 1 = split (k_emit + k_recur), 0 = fused k_decode.
+// The fused kernel has one lane per sequence and needs ~75,000 sequences to fill a B200; below that the split schedule
+// (emission parallel over bins) is up to 1.7x faster, above it the two are within a few per cent and the fused kernel
+// needs no emission scratch.  SGB_SCHED=split|fused forces one; SGB_SPLIT_MAX_SEQ moves the switch-over point.
 int want_split(const SgbModelArgs& m, long long nseq)
 {
     if (m.decode != SGB_DECODE_REFERENCE) return 0;          // chained decode keeps the fused kernel + k_backtrace
     const char* e = getenv("SGB_SCHED");
     if (e && !strcmp(e, "fused")) return 0;
     if (e && !strcmp(e, "split")) return 1;
-    (void)nseq;
-    return 1;
+    long long lim = 60000;
+    const char* t = getenv("SGB_SPLIT_MAX_SEQ");
+    if (t && atoll(t) > 0) lim = atoll(t);
+    return nseq < lim;
 }
 
 // host-side description of a batch of sequences, sorted by length (longest first)
@@ -625,6 +630,7 @@ struct sgb_plan {
     int device = 0;
     int64_t N = 0;
     int n_states = 0, decode = 0;
+    int64_t nseg = 0;
     HostPlan hp;
     DevBuf goff, ostart, len, packed, cn8, bp, last_state;
     SplitWork split;                        // split schedule scratch (reserved by the first call that takes it)
@@ -654,7 +660,7 @@ int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_s
     Ctx* C;
     if (get_ctx(&C)) return 1;
     sgb_plan* pl = new sgb_plan();
-    pl->device = C->device; pl->N = N; pl->n_states = n_states; pl->decode = decode;
+    pl->device = C->device; pl->N = N; pl->n_states = n_states; pl->decode = decode; pl->nseg = nseg;
     {
         // the split schedule (the default for decode = reference) wants full groups of 32: its emission kernel is not
         // starved by small batches, and narrow groups would only add empty plan entries
@@ -747,7 +753,7 @@ int sgb_hmm_decode_device(const sgb_params* params, sgb_plan* pl, const int32_t*
     SGB_CUDA(sgbk_setup(pl->d_tabs, m, params->eps, params->Abias, params->selftransitionprob, st));
     const int slot = (int)(pl->calls % sgb_plan::kRing);
     if (pl->timing) SGB_CUDA(cudaEventRecord(pl->ev[slot][0], st));
-    if (want_split(m, pl->hp.nseq)) {
+    if (want_split(m, pl->nseg)) {
         // ---- split schedule: k_emit (lanes over bins) + k_recur (lane per sequence), sliced if the batch is huge
         const SgbColsIn in = {d_n, d_x, d_cn, cn_itemsize == 4 ? SGB_IN_I32_I32 : SGB_IN_I32_U8, (long long)pl->N, pl->d_err};
         if (run_split(pl->split, pl->slices, pl->hp, pl->pd, in, pl->d_tabs, m, d_state_out, C->sm_count, st,
@@ -825,6 +831,26 @@ int sgb_plan_read_timing(sgb_plan* pl, int32_t max_records, float* pack_ms, floa
     std::vector<float> em((size_t)(max_records > 0 ? max_records : 1));
     if (sgb_plan_read_timing3(pl, max_records, pack_ms, em.data(), decode_ms, n_out)) return 1;
     for (int i = 0; i < *n_out; i++) decode_ms[i] += em[(size_t)i];          // two-phase view: preparation | kernels
+    return 0;
+}
+
+int sgb_plan_split_info(sgb_plan* pl, void* stream, int64_t* ngroups_out, int64_t* e_bytes_out)
+{
+    if (!pl || !ngroups_out || !e_bytes_out) return fail("NULL pointer");
+    *ngroups_out = 0; *e_bytes_out = 0;
+    if (pl->last_stage != 4 || pl->slices.empty() || !pl->split.misc.p) return 0;
+    SGB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    // the device-side tables describe the LAST slice the plan decoded
+    int ng = 0;
+    SGB_CUDA(cudaMemcpy(&ng, pl->split.misc.p, sizeof(int), cudaMemcpyDeviceToHost));
+    if (ng > 0) {
+        long long off = 0;
+        unsigned long long sz = 0;
+        SGB_CUDA(cudaMemcpy(&off, (long long*)pl->split.g_eoff.p + (ng - 1), 8, cudaMemcpyDeviceToHost));
+        SGB_CUDA(cudaMemcpy(&sz, (unsigned long long*)pl->split.g_size.p + (ng - 1), 8, cudaMemcpyDeviceToHost));
+        *e_bytes_out = (int64_t)((unsigned long long)off + sz) * 32;
+    }
+    *ngroups_out = ng;
     return 0;
 }
 

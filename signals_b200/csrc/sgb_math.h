@@ -27,12 +27,23 @@
 #include "sgb_tables.h"
 
 #if defined(__CUDACC__)
-#define SGB_HD __host__ __device__ __forceinline__
+#define SGB_HD static __host__ __device__ __forceinline__
 #else
 #define SGB_HD static inline __attribute__((always_inline))
 #endif
 
 #define SGB_SHIFT (0x1.8p52)
+
+// Where entry j of the exp table / pair i of the log table sits relative to the pointer a function is given.  The
+// default is the plain packed layout.  A translation unit may define both before including this header to read
+// lane-private, bank-conflict-free copies of the tables in shared memory (split_kernels.cu): the VALUES read are the
+// same, so the results are the same bits.
+#ifndef SGB_ETI
+#define SGB_ETI(j) (j)
+#endif
+#ifndef SGB_LTI
+#define SGB_LTI(i) (2 * (i))
+#endif
 
 // Scalar constants: host code uses the hex-float literals; device code reads the same values from
 // the constant bank (operand-folded into DFMA/DADD instead of two 32-bit immediate moves per use).
@@ -127,7 +138,7 @@ SGB_HD double sgb_exp_core(double x, const double* __restrict__ ET)
     r = sgb_fma(kd, -SGB_C(LN2N_LO), r);
     int32_t j = k & (SGB_NEXP - 1);
     int64_t q = (int64_t)(k >> 6);
-    double s = sgb_u2d(sgb_d2u(ET[j]) + ((uint64_t)q << 52));
+    double s = sgb_u2d(sgb_d2u(ET[SGB_ETI(j)]) + ((uint64_t)q << 52));
     // Estrin evaluation (3 dependent levels instead of 6): 1 + C2 r + ... + C6 r^5
     double r2 = sgb_mul(r, r);
     double p01 = sgb_fma(r, SGB_C(EXPC2), 1.0);
@@ -156,7 +167,7 @@ SGB_HD double sgb_log_core(uint64_t ix, int32_t kadj, const double* __restrict__
     uint64_t m = ix & 0x000fffffffffffffULL;
     int32_t i = (int32_t)(m >> 45);
     double w = sgb_u2d(m | 0x3ff0000000000000ULL);
-    double invc = LT[2 * i], logc = LT[2 * i + 1];
+    double invc = LT[SGB_LTI(i)], logc = LT[SGB_LTI(i) + 1];
     if (rcp_seed) *rcp_seed = sgb_u2d(sgb_d2u(invc) - ((uint64_t)(int64_t)k << 52));
     double r = sgb_fma(w, invc, -1.0);
     double kd = (double)(k + kadj);
@@ -224,7 +235,7 @@ SGB_HD double sgb_log1p01_core(double u, double w, const double* __restrict__ LT
 {
     double c = sgb_sub(u, sgb_sub(w, 1.0));          // exact rounding residual of 1+u
     int32_t i = (int32_t)(((uint32_t)(sgb_d2u(w) >> 32) - 0x3ff00000u) >> 13);     // top 7 mantissa bits (w == 2 -> 128)
-    double invc = LT[2 * i], logc = LT[2 * i + 1];
+    double invc = LT[SGB_LTI(i)], logc = LT[SGB_LTI(i) + 1];
     double r = sgb_fma(w, invc, -1.0);
     // Estrin evaluation of C2 + C3 r + ... + C9 r^7 (3 dependent levels instead of 7)
     double r2 = sgb_mul(r, r);

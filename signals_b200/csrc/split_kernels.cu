@@ -1,9 +1,9 @@
-// split_kernels.cuh -- the SPLIT schedule of the HSCN / ASCN decode (included by hmm_kernels.cu).
+// split_kernels.cu -- the SPLIT schedule of the HSCN / ASCN decode (the default for decode = reference).
 //
-// The fused k_decode gives every (cell, chromosome) sequence ONE lane, so a batch of n sequences offers n/32 warps and
-// every warp walks a dependent chain of emission + recursion steps: batches below ~75,000 sequences cannot fill a
-// B200 (148 SMs x 16+ resident warps).  The emission log-likelihoods (R/callHSCN.R:48-80, R/callASCN.R:50-81) are
-// independent per bin; only the max-plus recursion (src/code.cpp:27-33) is sequential.  So:
+// The fused k_decode (hmm_kernels.cu) gives every (cell, chromosome) sequence ONE lane, so a batch of n sequences offers
+// n/32 warps and every warp walks a dependent chain of emission + recursion steps: batches below ~75,000 sequences
+// cannot fill a B200 (148 SMs x 16+ resident warps).  The emission log-likelihoods (R/callHSCN.R:48-80,
+// R/callASCN.R:50-81) are independent per bin; only the max-plus recursion (src/code.cpp:27-33) is sequential.  So:
 //
 //   k_split_class    one warp per sequence: largest total copy number -> number of 4-state "planes" the sequence needs
 //   k_split_scan / k_split_scatter   stable partition of the sequences by plane count (descending), so that the 32
@@ -12,15 +12,32 @@
 //   k_emit           one warp per sequence, LANES OVER BINS: coalesced loads of the caller's columns (any of the
 //                    accepted element types), all live states of a bin evaluated by the lane that owns the bin
 //                    (copy number is piecewise constant along a chromosome, so a warp is branch-uniform), emissions
-//                    written as 32-byte sectors into the group's tile  E[bin][plane][lane][4]
+//                    written as 32-byte sectors into the group's tile
 //   k_recur          one warp per group, one lane per sequence: the tile is streamed through a shared-memory ring by
-//                    1-D TMA bulk copies (cp.async.bulk + mbarrier, several bins ahead), the forward column lives
-//                    in registers, per bin the O(S) step of hmm_core.cuh and the reference's decode rule
+//                    1-D TMA bulk copies (cp.async.bulk + mbarrier, 4 bins x 32 sequences per copy, several copies
+//                    ahead), the forward column lives in registers, per bin the O(S) step of hmm_core.cuh and the
+//                    reference's decode rule
 //
-// k_emit is FP64 / issue bound and has N x L-way parallelism; k_recur is HBM-bound (reads 32 B per cell-bin and
-// plane) and its dependent chain per bin is ~50 instructions instead of a whole emission.  Same arithmetic functions
-// as the fused kernel (sgb_emit_item, the max-plus step), hence the same bits.
-#pragma once
+// Tile of a group with P planes: chunks of 4 bins, 4 P KB each, contiguous (one TMA copy); inside a chunk the 4 P sectors
+// of one sequence (4 bins x P planes) are contiguous -- a k_emit warp therefore writes whole 128-byte lines -- and are
+// rotated by the lane number so that the 32 lanes of k_recur read them from different shared-memory banks:
+//     sector(chunk c, lane l, bin b, plane p) = c * 128 P + l * 4 P + (b * P + p + l) mod 4 P
+//
+// Both kernels read the exp / log tables from lane-private copies in shared memory (entry j of lane l at column l mod 16,
+// resp. pair i at column l mod 8), so a table look-up with 32 unrelated indices is free of bank conflicts; the values,
+// and so the bits of every result, are those of the packed tables.  Same arithmetic functions as the fused kernel
+// (sgb_emission_fast*, sgb_emit_item_slow, the max-plus step), hence the same bits.
+#define SGB_ETI(j) ((j) * 16)             // exp table: 16 lane-private columns of doubles
+#define SGB_LTI(i) ((i) * 16)             // log table: 8 lane-private columns of {1/c, log c} pairs
+#include "kernels.h"
+#include "sgb_async.cuh"
+
+static __device__ const double gs_logtab[SGB_LOGTAB_LEN] = SGB_LOGTAB_INIT;
+static __device__ const double gs_exptab[SGB_EXPTAB_LEN] = SGB_EXPTAB_INIT;
+static __device__ const double gs_lftab[SGB_LFTAB_LEN] = SGB_LFTAB_INIT;
+
+#define SGB_FULL 0xffffffffu
+
 
 #define SGB_NCLS 9                        // plane classes 0 (empty sequence) .. 8
 #define SGB_PART_TILE 1024                // sequences per partition tile
@@ -187,10 +204,45 @@ struct SgbEmitArgs {
 
 #define SGB_EMIT_THREADS 256
 #define SGB_EMIT_LF 1024
+#define SGB_LTP_LEN (((SGB_LOGTAB_LEN + 1) / 2) * 16)      // lane-private log table: pairs x 8 columns x 2 doubles
+#define SGB_ETP_LEN (SGB_EXPTAB_LEN * 16)                   // lane-private exp table: entries x 16 columns
+#ifndef SGB_PAIR_OK
+#define SGB_PAIR_OK(likbb) (!(likbb))      // beta-binomial: one item at a time (instruction-cache footprint, see hmm_kernels.cu)
+#endif
 static inline size_t emit_smem_bytes(int S, int lik_bb)
 {
-    size_t d = SGB_LOGTAB_LEN + SGB_EXPTAB_LEN + SGB_EMIT_LF + (size_t)SGB_CN_TABLE * S * (lik_bb ? 5 : 2);
-    return d * sizeof(double) + (size_t)SGB_CN_TABLE * S * sizeof(int);
+    size_t d = SGB_LTP_LEN + SGB_ETP_LEN + SGB_EMIT_LF + (size_t)SGB_CN_TABLE * S * (lik_bb ? 5 : 2);
+    return d * sizeof(double) + ((size_t)SGB_CN_TABLE * S + SGB_CN_TABLE) * sizeof(int);
+}
+
+// one row of the caller's columns, whatever their element type; returns validation bits
+__device__ __forceinline__ int sgb_load_row(const SgbColsIn& in, long long row, int& n, int& x, int& cnv)
+{
+    int bad = 0;
+    if (in.kind == SGB_IN_U16_U8) {
+        n = (int)__ldg((const uint16_t*)in.n + row); x = (int)__ldg((const uint16_t*)in.x + row);
+        cnv = (int)__ldg((const uint8_t*)in.cn + row);
+    } else if (in.kind == SGB_IN_F64) {
+        const double dn = __ldg((const double*)in.n + row), dx = __ldg((const double*)in.x + row);
+        const double dc = __ldg((const double*)in.cn + row);
+        const double lim = (double)(1 << SGB_COUNT_BITS);
+        if (dn != dn || dx != dx || dc != dc) bad |= SGB_ERR_NOT_INTEGER;
+        else if (dn < 0.0 || dx < 0.0) bad |= SGB_ERR_NEGATIVE_COUNT;
+        else if (dn >= lim || dx >= lim) bad |= SGB_ERR_COUNT_TOO_LARGE;
+        else if (dc < 0.0 || dc > 255.0) bad |= SGB_ERR_BAD_CN;
+        else if (dn != rint(dn) || dx != rint(dx) || dc != rint(dc)) bad |= SGB_ERR_NOT_INTEGER;
+        n = bad ? 0 : (int)dn; x = bad ? 0 : (int)dx; cnv = bad ? 0 : (int)dc;
+    } else {
+        n = __ldg((const int32_t*)in.n + row); x = __ldg((const int32_t*)in.x + row);
+        cnv = in.kind == SGB_IN_I32_I32 ? __ldg((const int32_t*)in.cn + row) : (int)__ldg((const uint8_t*)in.cn + row);
+    }
+    // the checks of the fused path: a bad bin is neutralised, the call fails afterwards
+    if ((unsigned)(n | x) >> SGB_COUNT_BITS) {
+        bad |= (n | x) < 0 ? SGB_ERR_NEGATIVE_COUNT : SGB_ERR_COUNT_TOO_LARGE;
+        n = 0; x = 0; cnv = 0;
+    }
+    if ((unsigned)cnv > 255u) { bad |= SGB_ERR_BAD_CN; n = 0; x = 0; cnv = 0; }
+    return bad;
 }
 
 template <int MODEL, int LIKBB>
@@ -199,17 +251,28 @@ __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmi
     extern __shared__ __align__(16) double smem[];
     const int S = A.S;
     const int CTS = SGB_CN_TABLE * S;
-    double* sLT = smem;
-    double* sET = sLT + SGB_LOGTAB_LEN;
-    double* sLF = sET + SGB_EXPTAB_LEN;
+    double* sLTp = smem;                                   // lane-private log table
+    double* sETp = sLTp + SGB_LTP_LEN;                     // lane-private exp table
+    double* sLF = sETp + SGB_ETP_LEN;
     double* sLP = sLF + SGB_EMIT_LF;
     double* sA = sLP + 2 * CTS;
     double* sB = sA + (LIKBB ? CTS : 0);
     double* sL0 = sB + (LIKBB ? CTS : 0);
     int* sKind = (int*)(sL0 + (LIKBB ? CTS : 0));
-    for (int i = threadIdx.x; i < SGB_LOGTAB_LEN; i += blockDim.x) sLT[i] = g_logtab[i];
-    for (int i = threadIdx.x; i < SGB_EXPTAB_LEN; i += blockDim.x) sET[i] = g_exptab[i];
-    for (int i = threadIdx.x; i < SGB_EMIT_LF; i += blockDim.x) sLF[i] = g_lftab[i];
+    int* sKM = sKind + CTS;                 // per total-CN bit mask of the states on the lean path
+    if (threadIdx.x < SGB_CN_TABLE) {
+        unsigned mask = 0;
+        for (int st = 0; st < S; st++)
+            if (A.tabs->kind[threadIdx.x * SGB_MAX_STATES + st] == SGB_KIND_NORMAL) mask |= 1u << st;
+        sKM[threadIdx.x] = (int)mask;
+    }
+    for (int i = threadIdx.x; i < SGB_LTP_LEN; i += blockDim.x) {
+        const int pair = i >> 4, w = i & 1;                // (pair, column, word): column = (i >> 1) & 7
+        const int src = 2 * pair + w;
+        sLTp[i] = src < SGB_LOGTAB_LEN ? gs_logtab[src] : 0.0;
+    }
+    for (int i = threadIdx.x; i < SGB_ETP_LEN; i += blockDim.x) sETp[i] = gs_exptab[i >> 4];
+    for (int i = threadIdx.x; i < SGB_EMIT_LF; i += blockDim.x) sLF[i] = gs_lftab[i];
     for (int i = threadIdx.x; i < CTS; i += blockDim.x) {
         const int c = i / S, s = i - c * S, src = c * SGB_MAX_STATES + s;
         sLP[2 * i] = A.tabs->lp[src];
@@ -218,18 +281,16 @@ __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmi
         if (LIKBB) { sA[i] = A.tabs->a[src]; sB[i] = A.tabs->b[src]; sL0[i] = A.tabs->l0[src]; }
     }
     __shared__ SgbScalars s_sp;
-    __shared__ SgbTables s_TB;
-    if (threadIdx.x == 0) {
-        s_sp = A.tabs->sp;
-        s_TB.LT = sLT; s_TB.ET = sET; s_TB.LP = sLP; s_TB.LQ = sLP + 1; s_TB.pstride = 2; s_TB.A = sA; s_TB.B = sB; s_TB.L0 = sL0;
-        s_TB.LGK = A.tabs->lgk; s_TB.KIND = sKind; s_TB.S = S; s_TB.lik = A.lik; s_TB.loherror = A.loherror; s_TB.rho = A.rho;
-    }
+    if (threadIdx.x == 0) s_sp = A.tabs->sp;
     __syncthreads();
     const SgbScalars& sp = s_sp;
-    const SgbTables& TB = s_TB;
     const int lane = threadIdx.x & 31;
+    const double* LT = sLTp + 2 * (lane & 7);              // this lane's columns of the two tables
+    const double* ET = sETp + (lane & 15);
+    SgbTables TB;                                          // per thread: the table pointers are lane-private
+    TB.LT = LT; TB.ET = ET; TB.LP = sLP; TB.LQ = sLP + 1; TB.pstride = 2; TB.A = sA; TB.B = sB; TB.L0 = sL0;
+    TB.LGK = A.tabs->lgk; TB.KIND = sKind; TB.S = S; TB.lik = A.lik; TB.loherror = A.loherror; TB.rho = A.rho;
     const double NEG_INF = -sgb_inf();
-    const int kind = A.in.kind;
     const long long nslots = (long long)(*A.W.ngroups) * 32;
     int bad = 0;
     for (;;) {
@@ -243,66 +304,89 @@ __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmi
         const long long o = A.plan.ostart[idx];
         const int g = (int)(r >> 5), lr = (int)(r & 31);
         const int npl = A.W.g_npl[g];
-        double* tile = A.W.E + (A.W.g_eoff[g] * 4 + lr * 4);          // + (t * npl + p) * 128 doubles
+        const int run = 4 * npl;                                          // sectors of one sequence inside a chunk
+        const int lrm = lr % run;
+        double* tile = A.W.E + (A.W.g_eoff[g] + (long long)lr * run) * 4;  // + chunk * 128 npl sectors + rotated position
+        int n = 0, x = 0, cnv = 0;
+        if (lane < len) bad |= sgb_load_row(A.in, o + lane, n, x, cnv);
         for (int t0 = 0; t0 < len; t0 += 32) {
             const int t = t0 + lane;
             const bool act = t < len;
-            int n = 0, x = 0, cnv = 0;
-            if (act) {
-                const long long row = o + t;
-                if (kind == SGB_IN_U16_U8) {
-                    n = (int)__ldg((const uint16_t*)A.in.n + row); x = (int)__ldg((const uint16_t*)A.in.x + row);
-                    cnv = (int)__ldg((const uint8_t*)A.in.cn + row);
-                } else if (kind == SGB_IN_F64) {
-                    const double dn = __ldg((const double*)A.in.n + row), dx = __ldg((const double*)A.in.x + row);
-                    const double dc = __ldg((const double*)A.in.cn + row);
-                    const double lim = (double)(1 << SGB_COUNT_BITS);
-                    if (!(dn >= 0.0) || !(dx >= 0.0)) bad |= (dn != dn || dx != dx) ? SGB_ERR_NOT_INTEGER : SGB_ERR_NEGATIVE_COUNT;
-                    else if (dn >= lim || dx >= lim) bad |= SGB_ERR_COUNT_TOO_LARGE;
-                    else if (dn != rint(dn) || dx != rint(dx)) bad |= SGB_ERR_NOT_INTEGER;
-                    if (!(dc >= 0.0 && dc <= 255.0)) bad |= (dc != dc) ? SGB_ERR_NOT_INTEGER : SGB_ERR_BAD_CN;
-                    else if (dc != rint(dc)) bad |= SGB_ERR_NOT_INTEGER;
-                    const bool ok = dn >= 0.0 && dx >= 0.0 && dn < lim && dx < lim && dn == rint(dn) && dx == rint(dx) &&
-                                    dc >= 0.0 && dc <= 255.0 && dc == rint(dc);
-                    n = ok ? (int)dn : 0; x = ok ? (int)dx : 0; cnv = ok ? (int)dc : 0;
-                } else {
-                    n = __ldg((const int32_t*)A.in.n + row); x = __ldg((const int32_t*)A.in.x + row);
-                    cnv = kind == SGB_IN_I32_I32 ? __ldg((const int32_t*)A.in.cn + row) : (int)__ldg((const uint8_t*)A.in.cn + row);
-                }
-                // the checks of the fused path: a bad bin is neutralised, the call fails afterwards
-                if ((unsigned)(n | x) >> SGB_COUNT_BITS) {
-                    bad |= (n | x) < 0 ? SGB_ERR_NEGATIVE_COUNT : SGB_ERR_COUNT_TOO_LARGE;
-                    n = 0; x = 0; cnv = 0;
-                }
-                if ((unsigned)cnv > 255u) { bad |= SGB_ERR_BAD_CN; n = 0; x = 0; cnv = 0; }
-            }
-            const int cprime = sgb_cprime(MODEL, cnv);
-            const int ins = x <= n;
+            const int nc = n, xc = x, cc = cnv;
+            // next tile's row: in flight while this one is evaluated
+            n = 0; x = 0; cnv = 0;
+            if (t + 32 < len) bad |= sgb_load_row(A.in, o + t + 32, n, x, cnv);
+            const int cprime = sgb_cprime(MODEL, cc);
+            const int ins = xc <= nc;
             const int L = act ? sgb_live_states(MODEL, cprime, S) : 0;
             double lcx = 0.0, lcy = 0.0, lgs = 0.0;
             if (act && ins) {
                 double fn, fx, fy;
-                if (n < SGB_EMIT_LF) { fn = sLF[n]; fx = sLF[x]; fy = sLF[n - x]; }
-                else if (n < SGB_NLF) { fn = g_lftab[n]; fx = g_lftab[x]; fy = g_lftab[n - x]; }
-                else { fn = sgb_logfact(n, g_lftab, sLT); fx = sgb_logfact(x, g_lftab, sLT); fy = sgb_logfact(n - x, g_lftab, sLT); }
+                if (nc < SGB_EMIT_LF) { fn = sLF[nc]; fx = sLF[xc]; fy = sLF[nc - xc]; }
+                else if (nc < SGB_NLF) { fn = gs_lftab[nc]; fx = gs_lftab[xc]; fy = gs_lftab[nc - xc]; }
+                else { fn = sgb_logfact(nc, gs_lftab, LT); fx = sgb_logfact(xc, gs_lftab, LT); fy = sgb_logfact(nc - xc, gs_lftab, LT); }
                 lcx = sgb_sub(sgb_sub(fn, fx), fy);
                 if (MODEL == SGB_MODEL_ASCN) lcy = sgb_sub(sgb_sub(fn, fy), fx);
-                if (LIKBB) lgs = sgb_lgamma_pos(sgb_add(sp.bb_s, (double)n), sLT);
+                if (LIKBB) lgs = sgb_lgamma_pos(sgb_add(sp.bb_s, (double)nc), LT);
             }
-            const double kd = (double)x, nkd = (double)(n - x);
-            double* dst = tile + (long long)t * npl * 128;
+            const double kd = (double)xc, nkd = (double)(nc - xc);
+            double* chunk = tile + (long long)(t >> 2) * (128 * npl) * 4;
+            const int rot = (t & 3) * npl + lrm;                           // + plane, mod run (lrm = lr mod run)
             const int Lw = __reduce_max_sync(SGB_FULL, L);
+            // lean path for the whole warp: every live state of every lane's bin is an ordinary one (tabulated total CN,
+            // 0 < p < 1, count inside the support, default eps / no Abias) -- the usual case.  Idle lanes ride along on
+            // harmless operands.  Otherwise the general per-item function (same bits where both apply).
+            const unsigned needm = L >= 32 ? 0xffffffffu : (1u << L) - 1u;
+            const bool lean = !act || (cprime < SGB_CN_TABLE && ins && sp.fast_ok && ((unsigned)sKM[cprime < SGB_CN_TABLE ? cprime : 0] & needm) == needm);
+            const bool warp_lean = __all_sync(SGB_FULL, lean);
+            const int trow = (act && cprime < SGB_CN_TABLE ? cprime : 1) * S;      // idle lanes: any valid row
+            const int Lc = L > 0 ? L - 1 : 0;                                       // states beyond L are computed on row Lc and dropped
             for (int p = 0; p < npl; p++) {
                 double e0 = NEG_INF, e1 = NEG_INF, e2 = NEG_INF, e3 = NEG_INF;
                 if (4 * p < Lw) {
-                    if (4 * p + 0 < L) e0 = sgb_emit_item<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, 4 * p + 0, TB, sp);
-                    if (4 * p + 1 < L) e1 = sgb_emit_item<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, 4 * p + 1, TB, sp);
-                    if (4 * p + 2 < L) e2 = sgb_emit_item<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, 4 * p + 2, TB, sp);
-                    if (4 * p + 3 < L) e3 = sgb_emit_item<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, 4 * p + 3, TB, sp);
+                    if (warp_lean) {
+#define SGB_TI(m) (trow + ((m) < Lc ? (m) : Lc))
+#define SGB_LEAN2(ma, mb, ra, rb) do {                                                                                  \
+                            const int ta_ = SGB_TI(ma), tb_ = SGB_TI(mb);                                                  \
+                            const double2 pa_ = ((const double2*)sLP)[ta_], pb_ = ((const double2*)sLP)[tb_];            \
+                            sgb_emission_fast2<MODEL, LIKBB>(kd, nkd, lcx, lcy, lgs, pa_.x, pa_.y, LIKBB ? sA[ta_] : 0.0,  \
+                                LIKBB ? sB[ta_] : 0.0, LIKBB ? sL0[ta_] : 0.0, kd, nkd, lcx, lcy, lgs, pb_.x, pb_.y,        \
+                                LIKBB ? sA[tb_] : 0.0, LIKBB ? sB[tb_] : 0.0, LIKBB ? sL0[tb_] : 0.0,                      \
+                                LIKBB ? TB.LGK + (long)ta_ * 2 * SGB_LGK : LT, LIKBB ? TB.LGK + (long)tb_ * 2 * SGB_LGK : LT, \
+                                sp, LT, ET, ra, rb); } while (0)
+#define SGB_LEAN1(ma, ra) do {                                                                                          \
+                            const int ta_ = SGB_TI(ma);                                                                    \
+                            const double2 pa_ = ((const double2*)sLP)[ta_];                                               \
+                            ra = sgb_emission_fast<MODEL, LIKBB>(kd, nkd, lcx, lcy, lgs, pa_.x, pa_.y, LIKBB ? sA[ta_] : 0.0, \
+                                LIKBB ? sB[ta_] : 0.0, LIKBB ? sL0[ta_] : 0.0, LIKBB ? TB.LGK + (long)ta_ * 2 * SGB_LGK : LT, \
+                                sp, LT, ET); } while (0)
+                        if (SGB_PAIR_OK(LIKBB)) {
+                            if (4 * p + 1 < Lw) SGB_LEAN2(4 * p, 4 * p + 1, e0, e1); else SGB_LEAN1(4 * p, e0);
+                            if (4 * p + 2 < Lw) { if (4 * p + 3 < Lw) SGB_LEAN2(4 * p + 2, 4 * p + 3, e2, e3); else SGB_LEAN1(4 * p + 2, e2); }
+                        } else {
+                            SGB_LEAN1(4 * p, e0);
+                            if (4 * p + 1 < Lw) SGB_LEAN1(4 * p + 1, e1);
+                            if (4 * p + 2 < Lw) SGB_LEAN1(4 * p + 2, e2);
+                            if (4 * p + 3 < Lw) SGB_LEAN1(4 * p + 3, e3);
+                        }
+#undef SGB_LEAN1
+#undef SGB_LEAN2
+#undef SGB_TI
+                        e0 = 4 * p + 0 < L ? e0 : NEG_INF; e1 = 4 * p + 1 < L ? e1 : NEG_INF;
+                        e2 = 4 * p + 2 < L ? e2 : NEG_INF; e3 = 4 * p + 3 < L ? e3 : NEG_INF;
+                    } else {
+                        if (4 * p + 0 < L) e0 = sgb_emit_item_slow<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, 4 * p + 0, TB, sp);
+                        if (4 * p + 1 < L) e1 = sgb_emit_item_slow<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, 4 * p + 1, TB, sp);
+                        if (4 * p + 2 < L) e2 = sgb_emit_item_slow<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, 4 * p + 2, TB, sp);
+                        if (4 * p + 3 < L) e3 = sgb_emit_item_slow<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, 4 * p + 3, TB, sp);
+                    }
                 }
                 if (act) {
-                    __stcg((double2*)(dst + p * 128), make_double2(e0, e1));
-                    __stcg((double2*)(dst + p * 128 + 2), make_double2(e2, e3));
+                    int pos = rot + p;                  // < 2 run
+                    pos = pos >= run ? pos - run : pos;
+                    double* dst = chunk + pos * 4;
+                    __stcg((double2*)dst, make_double2(e0, e1));
+                    __stcg((double2*)(dst + 2), make_double2(e2, e3));
                 }
             }
         }
@@ -319,47 +403,55 @@ struct SgbRecurArgs {
     int S;
 };
 
-#define SGB_RECUR_WARPS 4
-#define SGB_RECUR_STAGES 4
+#define SGB_RECUR_WARPS 4               // per CTA when at most 3 planes (maxCN <= 11); 2 for the 8-plane kernel
+#define SGB_RECUR_NWARPS(maxnpl) ((maxnpl) <= 3 ? SGB_RECUR_WARPS : 2)
+#define SGB_RECUR_MAXDEPTH 16            // ring slots per warp: one mbarrier each, phases kept in a bit mask
 
+// One group of 32 sequences with NPL planes.  Chunk c of its tile (4 bins, 4 NPL KB, contiguous) is one 1-D TMA bulk copy
+// into the next slot of the warp's ring, `depth` chunks ahead of the recursion.
 // DD = 1: diagonal-dominant transition (every realistic selftransitionprob), forward column in registers, O(S) step.
 // DD = 0: selftransitionprob below 1/S -- the two-maxima variant, kept out of line so that it does not set the hot
 // path's register count.
-template <int NPL, int STAGE_BYTES, int DD>
+template <int NPL, int DD>
 __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbScalars& sp, unsigned char* ring, unsigned long long* bar,
-                                              unsigned& phases, int lane, int Tmax, long long eoff, int len, long long ostart)
+                                              unsigned& phases, int depth, int lane, int Tmax, long long eoff, int len,
+                                              long long ostart)
 {
     constexpr int NL = 4 * NPL;
-    constexpr int BPS = (STAGE_BYTES / (NPL * 1024)) > 0 ? (STAGE_BYTES / (NPL * 1024)) : 1;   // bins per stage
-    constexpr unsigned CHUNK = BPS * NPL * 1024;
+    constexpr int RUN = 4 * NPL;                       // sectors of one sequence inside a chunk
+    constexpr unsigned SLOT = NPL * 4096;
     const unsigned char* src = (const unsigned char*)A.W.E + eoff * 32;
-    const int nchunks = (Tmax + BPS - 1) / BPS;
-    auto issue = [&](int c) {
+    const int nchunks = (Tmax + 3) >> 2;
+    auto issue = [&](int c, int s) {
         if (lane == 0) {
-            const int s = c % SGB_RECUR_STAGES;
-            sgb_mbar_expect_tx(&bar[s], CHUNK);
-            sgb_tma_load_1d(ring + s * STAGE_BYTES, src + (long long)c * CHUNK, CHUNK, &bar[s]);
+            sgb_mbar_expect_tx(&bar[s], SLOT);
+            sgb_tma_load_1d(ring + s * SLOT, src + (long long)c * SLOT, SLOT, &bar[s]);
         }
     };
-    for (int c = 0; c < SGB_RECUR_STAGES && c < nchunks; c++) issue(c);
+    for (int c = 0; c < depth && c < nchunks; c++) issue(c, c);
     double T1[DD ? NL : 1];
     double m1 = 0.0;
     SgbSeqState<DD ? 1 : NL> st;
     const int Seff = A.S < NL ? A.S : NL;
     const double tr_self = sp.tr_self, tr_off = sp.tr_off, init = sp.init;
+    uint8_t* outp = A.state_out + ostart;
+    int s = 0;
     for (int c = 0; c < nchunks; c++) {
-        const int s = c % SGB_RECUR_STAGES;
         sgb_mbar_wait(&bar[s], (phases >> s) & 1u);
         phases ^= 1u << s;
+        const unsigned char* mine = ring + s * SLOT + lane * (RUN * 32);
+        const int lrm = lane % RUN;
 #pragma unroll
-        for (int b = 0; b < BPS; b++) {
-            const int t = c * BPS + b;
+        for (int b = 0; b < 4; b++) {
+            const int t = 4 * c + b;
             if (t < len) {
                 double e[NL];
-                const double2* row = (const double2*)(ring + s * STAGE_BYTES + b * NPL * 1024 + lane * 32);
 #pragma unroll
                 for (int p = 0; p < NPL; p++) {
-                    const double2 v0 = row[p * 64], v1 = row[p * 64 + 1];
+                    int pos = b * NPL + p + lrm;        // < 2 RUN
+                    pos = pos >= RUN ? pos - RUN : pos;
+                    const double2* q = (const double2*)(mine + pos * 32);
+                    const double2 v0 = q[0], v1 = q[1];
                     e[4 * p] = v0.x; e[4 * p + 1] = v0.y; e[4 * p + 2] = v1.x; e[4 * p + 3] = v1.y;
                 }
                 int back = 0;
@@ -371,52 +463,54 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
                     else back = sgb_seq_step_general<NL>(*(SgbSeqState<NL>*)&st, e, Seff, tr_self, tr_off);
                 }
                 if (t == 0) {
-                    if (len == 1) A.state_out[ostart] = 0;
+                    if (len == 1) outp[0] = 0;
                 } else {
-                    A.state_out[ostart + t - 1] = (uint8_t)back;
-                    if (t == len - 1) A.state_out[ostart + t] = (uint8_t)back;
+                    outp[t - 1] = (uint8_t)back;
+                    if (t == len - 1) outp[t] = (uint8_t)back;
                 }
             }
         }
-        __syncwarp();
-        if (c + SGB_RECUR_STAGES < nchunks) issue(c + SGB_RECUR_STAGES);
+        __syncwarp();                       // every lane has read slot s: it can be refilled
+        if (c + depth < nchunks) issue(c + depth, s);
+        s = (s + 1 == depth) ? 0 : s + 1;
     }
 }
 
-template <int NPL, int STAGE_BYTES>
+template <int NPL>
 __device__ __noinline__ void recur_group_general(const SgbRecurArgs& A, const SgbScalars& sp, unsigned char* ring, unsigned long long* bar,
-                                                 unsigned& phases, int lane, int Tmax, long long eoff, int len, long long ostart)
+                                                 unsigned& phases, int depth, int lane, int Tmax, long long eoff, int len,
+                                                 long long ostart)
 {
-    recur_group_t<NPL, STAGE_BYTES, 0>(A, sp, ring, bar, phases, lane, Tmax, eoff, len, ostart);
+    recur_group_t<NPL, 0>(A, sp, ring, bar, phases, depth, lane, Tmax, eoff, len, ostart);
 }
 
-template <int NPL, int STAGE_BYTES>
+template <int NPL>
 __device__ __forceinline__ void recur_group(const SgbRecurArgs& A, const SgbScalars& sp, unsigned char* ring, unsigned long long* bar,
-                                            unsigned& phases, int lane, int Tmax, long long eoff, int len, long long ostart)
+                                            unsigned& phases, int ring_bytes, int lane, int Tmax, long long eoff, int len,
+                                            long long ostart)
 {
-    if (sp.diag_dominant) recur_group_t<NPL, STAGE_BYTES, 1>(A, sp, ring, bar, phases, lane, Tmax, eoff, len, ostart);
-    else recur_group_general<NPL, STAGE_BYTES>(A, sp, ring, bar, phases, lane, Tmax, eoff, len, ostart);
+    int depth = ring_bytes / (NPL * 4096);
+    depth = depth > SGB_RECUR_MAXDEPTH ? SGB_RECUR_MAXDEPTH : depth;
+    if (sp.diag_dominant) recur_group_t<NPL, 1>(A, sp, ring, bar, phases, depth, lane, Tmax, eoff, len, ostart);
+    else recur_group_general<NPL>(A, sp, ring, bar, phases, depth, lane, Tmax, eoff, len, ostart);
 }
 
 template <int MAXNPL>
-__global__ void __launch_bounds__(SGB_RECUR_WARPS * 32, MAXNPL <= 3 ? 3 : 1) k_recur(SgbRecurArgs A)
+__global__ void __launch_bounds__(SGB_RECUR_NWARPS(MAXNPL) * 32, MAXNPL <= 3 ? 2 : 1) k_recur(SgbRecurArgs A, int ring_bytes)
 {
-    constexpr int STAGE_BYTES = MAXNPL <= 3 ? 4096 : 8192;
     extern __shared__ __align__(128) unsigned char rsm[];
-    __shared__ __align__(8) unsigned long long bars[SGB_RECUR_WARPS][SGB_RECUR_STAGES];
+    __shared__ __align__(8) unsigned long long bars[SGB_RECUR_WARPS][SGB_RECUR_MAXDEPTH];
     __shared__ SgbScalars s_sp;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    unsigned char* ring = rsm + (size_t)wid * SGB_RECUR_STAGES * STAGE_BYTES;
+    unsigned char* ring = rsm + (size_t)wid * ring_bytes;
     unsigned long long* bar = bars[wid];
     if (threadIdx.x == 0) s_sp = A.tabs->sp;
-    if (lane == 0) {
-        for (int s = 0; s < SGB_RECUR_STAGES; s++) sgb_mbar_init(&bar[s], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async;" ::: "memory");
-    }
+    if (lane < SGB_RECUR_MAXDEPTH) sgb_mbar_init(&bar[lane], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async;" ::: "memory");
     __syncthreads();
     const SgbScalars& sp = s_sp;
-    unsigned phases = 0;              // bit s: parity of the next completed phase of stage s's barrier
+    unsigned phases = 0;              // bit s: parity of the next completed phase of slot s's barrier
     const int ng = *A.W.ngroups;
     for (;;) {
         int g = 0;
@@ -431,7 +525,7 @@ __global__ void __launch_bounds__(SGB_RECUR_WARPS * 32, MAXNPL <= 3 ? 3 : 1) k_r
         long long ostart = 0;
         if (idx >= 0) { len = A.plan.len[idx]; ostart = A.plan.ostart[idx]; }
         if (Tmax <= 0 || npl <= 0) continue;
-#define SGB_RG(N) recur_group<N, STAGE_BYTES>(A, sp, ring, bar, phases, lane, Tmax, eoff, len, ostart)
+#define SGB_RG(N) recur_group<N>(A, sp, ring, bar, phases, ring_bytes, lane, Tmax, eoff, len, ostart)
         if (npl == 1) SGB_RG(1);
         else if (npl == 2) SGB_RG(2);
         else if (npl == 3) SGB_RG(3);
@@ -465,14 +559,16 @@ SgbSplitSizes sgbk_split_sizes(long long nseq, long long rows, int maxlen, int S
     return z;
 }
 
+// smem_max: the largest dynamic shared-memory size any call of this kernel uses (the attribute is a per-device LIMIT:
+// it is set once, to the maximum, so that calls with different table sizes never lower it under one another)
 template <typename K>
-static int split_occupancy(K kern, int threads, size_t smem, int* cache)
+static int split_occupancy(K kern, int threads, size_t smem, size_t smem_max, int* cache)
 {
     int dev = 0;
     cudaGetDevice(&dev);
     int& slot = cache[dev & 63];
     if (slot > 0) return slot;
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max) != cudaSuccess) { cudaGetLastError(); return 0; }
     int occ = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
     slot = occ;
@@ -488,7 +584,7 @@ static cudaError_t launch_emit(const SgbEmitArgs& A, long long nseq, int sm_coun
     cudaGetDevice(&dev);
     const size_t smem = emit_smem_bytes(A.S, LIKBB);
     flat[dev & 63] = cache[dev & 63][A.S];
-    const int occ = split_occupancy(k_emit<MODEL, LIKBB>, SGB_EMIT_THREADS, smem, flat);
+    const int occ = split_occupancy(k_emit<MODEL, LIKBB>, SGB_EMIT_THREADS, smem, emit_smem_bytes(SGB_MAX_STATES, LIKBB), flat);
     cache[dev & 63][A.S] = occ;
     if (occ < 1) return cudaErrorInvalidConfiguration;
     long long blocks = (nseq + 7) / 8;
@@ -501,14 +597,22 @@ static cudaError_t launch_emit(const SgbEmitArgs& A, long long nseq, int sm_coun
 template <int MAXNPL>
 static cudaError_t launch_recur(const SgbRecurArgs& A, int gcap, int sm_count, cudaStream_t st)
 {
-    static int cache[64];
-    const size_t smem = (size_t)SGB_RECUR_WARPS * SGB_RECUR_STAGES * (MAXNPL <= 3 ? 4096 : 8192);
-    const int occ = split_occupancy(k_recur<MAXNPL>, SGB_RECUR_WARPS * 32, smem, cache);
+    // Ring size per warp: the TMA copies must run far enough ahead of the recursion to cover the memory latency (~1 us)
+    // at ~100-250 cycles per bin, i.e. >= 8 bins whatever the plane count (a chunk is 4 bins x planes KB).  Small
+    // batches (few warps per SM; the chain latency is all that matters) get deep rings, large ones trade depth for
+    // resident warps (HBM-bound: what counts is the number of bytes in flight per SM).
+    static int cache[2][64];
+    constexpr int NW = SGB_RECUR_NWARPS(MAXNPL);
+    const int big = MAXNPL <= 3 ? 48 : 96, small = MAXNPL <= 3 ? 24 : 64;
+    const int ci = gcap <= sm_count * NW ? 0 : 1;
+    const int ring_kb = ci == 0 ? big : small;
+    const size_t smem = (size_t)NW * ring_kb * 1024;
+    const int occ = split_occupancy(k_recur<MAXNPL>, NW * 32, smem, (size_t)NW * big * 1024, cache[ci]);
     if (occ < 1) return cudaErrorInvalidConfiguration;
-    long long blocks = ((long long)gcap + SGB_RECUR_WARPS - 1) / SGB_RECUR_WARPS;
+    long long blocks = ((long long)gcap + NW - 1) / NW;
     if (blocks > (long long)sm_count * occ) blocks = (long long)sm_count * occ;
     if (blocks < 1) blocks = 1;
-    k_recur<MAXNPL><<<(unsigned)blocks, SGB_RECUR_WARPS * 32, smem, st>>>(A);
+    k_recur<MAXNPL><<<(unsigned)blocks, NW * 32, smem, st>>>(A, ring_kb * 1024);
     return cudaGetLastError();
 }
 

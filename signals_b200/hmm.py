@@ -203,6 +203,12 @@ class DevicePlan:
         check(self._lib.sgb_plan_read_timing3(self._h, max_records, _ptr(a), _ptr(b), _ptr(c), ctypes.byref(k)))
         return a[: k.value].copy(), b[: k.value].copy(), c[: k.value].copy()
 
+    def split_info(self, stream=0):
+        """(groups, emission-tile bytes) of the last split-schedule call; (0, 0) after a fused one"""
+        a = ctypes.c_int64(0); b = ctypes.c_int64(0)
+        check(self._lib.sgb_plan_split_info(self._h, ctypes.c_void_p(stream), ctypes.byref(a), ctypes.byref(b)))
+        return int(a.value), int(b.value)
+
     def reserve_split(self):
         check(self._lib.sgb_plan_reserve_split(self._h))
 
