@@ -422,8 +422,45 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         nseq = d["seg_off"].size - 1
         res["e2e"] = dict(value=N * world / (e2e_ms * 1e-3), unit="cell-bins/s", ms_per_step=e2e_ms,
                           h2d_bytes_per_step=int(N * (8 + cn_host.dtype.itemsize) + nseq * 20), d2h_bytes_per_step=int(N), steps=e2e_steps,
-                          api="sgb_hmm_decode (host buffers, pinned, chunked copy/compute overlap)")
+                          api="sgb_hmm_decode (host buffers: page-locked int32 columns in, uint8 states out; chunked, staged + "
+                              "narrowed to 5 B/cell-bin by worker threads unless SGB_HOST_NARROW=0)",
+                          bytes_note="h2d/d2h = bytes of the caller's tensors consumed / produced per step; the staged path moves "
+                                     "5 B per cell-bin over PCIe (uint16 counts + uint8 state), the direct path all of them")
         assert int(hout.to(torch.int64).sum().item()) == res["checksum"], "host-API and device-API results differ"
+        if want_e2e == "all" and world == 1:
+            # the same call as an R session makes it: PAGEABLE vectors, INTSXP (int32) or REALSXP (double) columns, states
+            # returned as doubles (state_min is numeric in the reference, R/callHSCN.R:169) -- sgb_hmm_decode_typed
+            variants = {}
+            so_ = d["seg_off"]
+            for label, dt_in, dt_out in (("pageable_int32_in_uint8_out", np.int32, np.uint8),
+                                         ("pageable_int32_in_double_out", np.int32, np.float64),
+                                         ("pageable_double_in_double_out", np.float64, np.float64)):
+                pn, px, pc = d["n"].astype(dt_in), d["x"].astype(dt_in), d["cn"].astype(dt_in)
+                po = np.zeros(N, dtype=dt_out)
+                code = {np.int32: _lib.T_I32, np.float64: _lib.T_F64, np.uint8: _lib.T_U8}
+                targs = (ctypes.byref(P), N, pn.ctypes.data, code[dt_in], px.ctypes.data, code[dt_in], pc.ctypes.data, code[dt_in],
+                         so_.size - 1, so_.ctypes.data, po.ctypes.data, code[dt_out], 1)
+                for _ in range(2):
+                    hmm.check(lib.sgb_hmm_decode_typed(*targs))
+                t0 = time.perf_counter()
+                for _ in range(3):
+                    hmm.check(lib.sgb_hmm_decode_typed(*targs))
+                ms = (time.perf_counter() - t0) / 3 * 1e3
+                assert int(po.astype(np.int64).sum()) == res["checksum"], label
+                variants[label] = dict(value=N / (ms * 1e-3), ms_per_step=ms,
+                                       h2d_bytes_per_step=int(N * 3 * np.dtype(dt_in).itemsize), d2h_bytes_per_step=int(N * np.dtype(dt_out).itemsize))
+                del pn, px, pc, po
+            os.environ["SGB_HOST_NARROW"] = "0"
+            for _ in range(2):
+                hmm.check(lib.sgb_hmm_decode(*args))
+            t0 = time.perf_counter()
+            for _ in range(3):
+                hmm.check(lib.sgb_hmm_decode(*args))
+            ms = (time.perf_counter() - t0) / 3 * 1e3
+            del os.environ["SGB_HOST_NARROW"]
+            variants["pinned_int32_direct_no_staging"] = dict(value=N / (ms * 1e-3), ms_per_step=ms,
+                                                              h2d_bytes_per_step=int(N * (8 + cn_host.dtype.itemsize)), d2h_bytes_per_step=int(N))
+            res["e2e"]["variants"] = variants
     for pl in plans:
         pl.close()
     del tn, tx, tc, out, hn, hx, hc, hout
@@ -503,7 +540,7 @@ def main():
     sampler.start()
 
     d = make_data(a.workload, rank, strong)
-    main_res = gpu_measure(a.workload, d, a.steps, a.warmup, rank, world, dist, sampler)
+    main_res = gpu_measure(a.workload, d, a.steps, a.warmup, rank, world, dist, sampler, want_e2e="all")
     fe = flop_eq(d, model, lik)
     clocks = sampler.summary()
     peak = ctypes.c_double(0.0)

@@ -86,6 +86,20 @@ SGB_API int sgb_hmm_decode_multi(const sgb_params* params, int32_t n_devices, in
                          const int32_t* x, const void* cn, int32_t cn_itemsize, int64_t nseg,
                          const int64_t* seg_off, uint8_t* state_out);
 
+/* The same batched decode for columns of ANY element type, one type code per column -- what an R caller holds:
+ * INTSXP columns are SGB_T_I32, REALSXP columns SGB_T_F64 (integer-valued doubles; NA / NaN / fractions are an error),
+ * and state_out can be written as doubles directly (the reference returns state_min as numeric, R/callHSCN.R:169).
+ * n_devices > 1 shards like sgb_hmm_decode_multi.  Pageable memory is fine: worker threads stage every chunk through
+ * page-locked buffers, narrowing counts to uint16 (int32 when a value does not fit) and states to uint8, so 5 bytes per
+ * cell-bin cross PCIe whatever the caller's types are.  Replaces the same reference lines as sgb_hmm_decode. */
+#define SGB_T_U8 1
+#define SGB_T_U16 2
+#define SGB_T_I32 4
+#define SGB_T_F64 8
+SGB_API int sgb_hmm_decode_typed(const sgb_params* params, int64_t N, const void* n, int32_t n_type, const void* x,
+                                 int32_t x_type, const void* cn, int32_t cn_type, int64_t nseg, const int64_t* seg_off,
+                                 void* state_out, int32_t out_type, int32_t n_devices);
+
 /* Device-resident variant: inputs and outputs are device pointers on the current device.
  * sgb_plan_create sorts the sequences by length on the host, uploads the index and reserves the
  * packed-record scratch; the plan can be reused for any inputs with the same seg_off.

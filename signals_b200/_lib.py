@@ -14,6 +14,7 @@ SO_PATH = os.path.join(_HERE, "libsignals_b200.so")
 MODEL_HSCN, MODEL_ASCN = 0, 1
 LIK_BINOMIAL, LIK_BETABINOMIAL = 0, 1
 DECODE_REFERENCE, DECODE_CHAINED = 0, 1
+T_U8, T_U16, T_I32, T_F64 = 1, 2, 4, 8
 
 
 class SgbParams(ctypes.Structure):
@@ -36,6 +37,7 @@ SIGNATURES = {
     "sgb_device_count": (ctypes.c_int, []),
     "sgb_hmm_decode": (ctypes.c_int, [_PP, _i64, _vp, _vp, _vp, _i32, _i64, _vp, _vp, _vp]),
     "sgb_hmm_decode_multi": (ctypes.c_int, [_PP, _i32, _i64, _vp, _vp, _vp, _i32, _i64, _vp, _vp]),
+    "sgb_hmm_decode_typed": (ctypes.c_int, [_PP, _i64, _vp, _i32, _vp, _i32, _vp, _i32, _i64, _vp, _vp, _i32, _i32]),
     "sgb_plan_create": (ctypes.c_int, [_i64, _i64, _vp, _i32, _i32, ctypes.POINTER(_vp)]),
     "sgb_plan_destroy": (ctypes.c_int, [_vp]),
     "sgb_plan_reserve_packed": (ctypes.c_int, [_vp]),

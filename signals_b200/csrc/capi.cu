@@ -6,7 +6,9 @@
 // There is no CPU execution path here -- if CUDA is unusable every entry point fails loudly.
 #include "../../include/signals_b200.h"
 #include "kernels.h"
+#include "host_stage.h"
 #include <algorithm>
+#include <memory>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -250,6 +252,8 @@ struct Slot {
     SplitWork split;
     unsigned int* counter = nullptr;
     HostPlan hp;
+    PinBuf stage_in, stage_out;   // page-locked staging of the chunk's (narrowed) columns / decoded states
+    int64_t pend_r0 = 0, pend_rows = 0;      // decoded states waiting in stage_out for the copy into the caller's buffer
     PinBuf pin;                 // page-locked copy of hp's arrays for the upload
     // pending device->host copy bookkeeping is implicit: copies are enqueued on st
 };
@@ -266,6 +270,7 @@ struct Ctx {
     SgbDevTables* d_tabs = nullptr;
     int* d_err = nullptr;
     DevBuf scratch_a, scratch_b, scratch_c, scratch_d;   // small utilities (viterbi, logspace_add, ...)
+    std::unique_ptr<SgbPool> pool;                       // host staging workers (created on first use)
 };
 
 std::mutex g_mu;
@@ -402,26 +407,102 @@ long long chunk_bins_target()
     return 8ll << 20;
 }
 
+// the caller's host columns, each with its own element type (SGB_T_*), and where the decoded states go
+struct HostCols {
+    const void* n; int n_type;
+    const void* x; int x_type;
+    const void* cn; int cn_type;
+    void* out; int out_type;
+};
+
+bool host_ptr_is_pinned(const void* p)
+{
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost;
+}
+
+int host_threads_default(int share)
+{
+    const char* e = getenv("SGB_HOST_THREADS");
+    int v = e ? atoi(e) : 0;
+    if (v <= 0) {
+        v = (int)std::thread::hardware_concurrency();
+        if (v <= 0) v = 4;
+        if (v > 16) v = 16;
+    }
+    v /= (share > 1 ? share : 1);
+    return v < 1 ? 1 : v;
+}
+
 // Decode sequences [s_begin, s_end) of a host-resident batch on the current device.
-int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const int32_t* n, const int32_t* x,
-                      const void* cn, int cn_itemsize, const int64_t* seg_off, int64_t s_begin, int64_t s_end,
-                      uint8_t* state_out, double* loglik_out)
+//
+// Chunks of the batch stream through two slots (copy / compute overlap).  Two ways of feeding a chunk:
+//   direct  cudaMemcpyAsync straight from the caller's columns (int32 counts, int32 / uint8 states): right when they are
+//           page-locked and host memory bandwidth is the scarce resource (several ranks on one node)
+//   staged  worker threads copy the chunk into the slot's page-locked buffers, narrowing counts to uint16 (int32 if a
+//           value does not fit) and states to uint8 -- 5 instead of 12-24 bytes per cell-bin over PCIe -- and convert
+//           the decoded states into the caller's element type afterwards.  The only way for pageable memory (R vectors)
+//           and for double / uint16 columns.  SGB_HOST_STAGE=always|never|auto (auto: staged unless direct is possible
+//           AND the columns are page-locked AND SGB_HOST_NARROW=0).
+int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const HostCols& H, const int64_t* seg_off,
+                      int64_t s_begin, int64_t s_end, double* loglik_out, int share)
 {
     if (s_end <= s_begin) return 0;
+    const bool direct_types = H.n_type == SGB_T_I32 && H.x_type == SGB_T_I32 && (H.cn_type == SGB_T_I32 || H.cn_type == SGB_T_U8) &&
+                              H.out_type == SGB_T_U8;
+    bool staged = true;
+    {
+        const char* e = getenv("SGB_HOST_STAGE");
+        const char* nw = getenv("SGB_HOST_NARROW");
+        const bool pinned = direct_types && host_ptr_is_pinned(H.n) && host_ptr_is_pinned(H.x) && host_ptr_is_pinned(H.cn) &&
+                            host_ptr_is_pinned(H.out);
+        if (e && !strcmp(e, "never")) staged = !direct_types;
+        else if (e && !strcmp(e, "always")) staged = true;
+        else staged = !(pinned && nw && !strcmp(nw, "0"));
+    }
+    if (loglik_out && !direct_types) return fail("loglik_out needs int32 count columns and uint8 output");
+    // the `l` matrix kernel and the chained decode read int32 counts: no narrowing for them
+    const bool narrow_ok = staged && !loglik_out && m.decode == SGB_DECODE_REFERENCE;
+    if (staged && !C->pool) C->pool.reset(new SgbPool(host_threads_default(share)));
+    const int cn_itemsize = H.cn_type == SGB_T_I32 ? 4 : 1;
+
     SGB_CUDA(cudaMemsetAsync(C->d_err, 0, sizeof(int), C->main));
     SGB_CUDA(sgbk_setup(C->d_tabs, m, P->eps, P->Abias, P->selftransitionprob, C->main));
     SGB_CUDA(cudaEventRecord(C->ev_setup, C->main));
-    const long long target = chunk_bins_target();
+    const long long target_full = chunk_bins_target();
     const bool explicit_chunk = getenv("SGB_CHUNK_BINS") != nullptr;      // tests pin the chunk size exactly
     const int S = m.S;
+    int host_bits = 0;
+    C->slot[0].pend_rows = 0; C->slot[1].pend_rows = 0;
+    // copies the decoded states a slot holds in its staging buffer into the caller's array (all workers)
+    auto unstage = [&](Slot& SL) {
+        if (SL.pend_rows <= 0) return;
+        const int64_t rows = SL.pend_rows, r0 = SL.pend_r0;
+        const uint8_t* src = (const uint8_t*)SL.stage_out.p;
+        C->pool->run([&](int w, int nw) {
+            const int64_t a = rows * w / nw, b = rows * (w + 1) / nw;
+            if (b > a) sgb_unstage_states(src + a, b - a, H.out, H.out_type, r0 + a);
+        });
+        SL.pend_rows = 0;
+    };
     int k = 0;
     int64_t s0 = s_begin;
+    const int64_t row_end = seg_off[s_end];
     while (s0 < s_end) {
         int64_t s1 = s0;
         long long bins = 0;
         // a chunk should (a) be big enough to amortise launches and (b) hold enough sequences to give every
-        // resident warp of the device a group (long sequences need more bins for that), within a memory cap
-        const long long seq_target = explicit_chunk ? 0 : (long long)C->sm_count * 8 * 32;      // half a wave of warps
+        // resident warp of the device a group (long sequences need more bins for that), within a memory cap;
+        // the first chunks ramp up (1/8, 1/4, 1/2 of the target) and the last ones ramp down so that little of the
+        // pipeline's fill and drain time is exposed
+        long long target = target_full;
+        if (!explicit_chunk) {
+            if (k < 3) target = target_full >> (3 - k);
+            const long long remaining = (long long)(row_end - seg_off[s0]);
+            if (remaining < 2 * target) target = std::max<long long>(remaining / 2, target_full >> 3);
+        }
+        const long long seq_target = explicit_chunk ? 0 : (k < 3 ? 0 : (long long)C->sm_count * 8 * 32);
         const long long bins_cap = explicit_chunk ? target : (128ll << 20);
         while (s1 < s_end) {
             const long long L = seg_off[s1 + 1] - seg_off[s1];
@@ -435,9 +516,9 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
         SGB_CUDA(cudaStreamSynchronize(st));          // slot buffers (and its host plan) are free again
         const int64_t r0 = seg_off[s0], r1 = seg_off[s1];
         const long long rows = (long long)(r1 - r0);
-        const int use_split = want_split(m, s1 - s0);
+        const int use_split0 = want_split(m, s1 - s0);
         if (build_host_plan(seg_off, s0, s1, r0, SL.hp, (long long)C->sm_count * 16,
-                            C->group_hint ? C->group_hint : (use_split ? 32 : 0)))
+                            C->group_hint ? C->group_hint : ((use_split0 || narrow_ok) ? 32 : 0)))
             return 1;
         if (rows > 0) {
             if (SL.n.reserve((size_t)rows * 4) || SL.x.reserve((size_t)rows * 4) ||
@@ -449,41 +530,96 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
             if (loglik_out && SL.loglik.reserve((size_t)rows * S * 8)) return 1;
             SgbPlanDev pd;
             if (upload_plan(SL, st, pd)) return 1;
-            SGB_CUDA(cudaMemcpyAsync(SL.n.p, n + r0, (size_t)rows * 4, cudaMemcpyHostToDevice, st));
-            SGB_CUDA(cudaMemcpyAsync(SL.x.p, x + r0, (size_t)rows * 4, cudaMemcpyHostToDevice, st));
-            SGB_CUDA(cudaMemcpyAsync(SL.cn.p, (const char*)cn + (size_t)r0 * cn_itemsize, (size_t)rows * cn_itemsize,
-                                     cudaMemcpyHostToDevice, st));
+            int kind = cn_itemsize == 4 ? SGB_IN_I32_I32 : SGB_IN_I32_U8;
+            int dev_cn_itemsize = cn_itemsize;
+            if (staged) {
+                const size_t off_x = ((size_t)rows * 4 + 255) & ~(size_t)255, off_c = 2 * off_x;
+                if (SL.stage_in.reserve(off_c + (size_t)rows + 256) || SL.stage_out.reserve((size_t)rows + 256)) return 1;
+                char* base = (char*)SL.stage_in.p;
+                std::atomic<int> bits(0);
+                bool narrow = narrow_ok;
+                // one pass of all workers: the states waiting in this slot go out to the caller, this chunk comes in
+                const int64_t prows = SL.pend_rows, pr0 = SL.pend_r0;
+                const uint8_t* psrc = (const uint8_t*)SL.stage_out.p;
+                C->pool->run([&](int w, int nw) {
+                    if (prows > 0) {
+                        const int64_t a = prows * w / nw, b = prows * (w + 1) / nw;
+                        if (b > a) sgb_unstage_states(psrc + a, b - a, H.out, H.out_type, pr0 + a);
+                    }
+                    const int64_t a = r0 + rows * w / nw, b = r0 + rows * (w + 1) / nw;
+                    if (b <= a) return;
+                    int bb = 0;
+                    if (narrow) {
+                        bb |= sgb_stage_count_u16(H.n, H.n_type, a, b, (uint16_t*)base + (a - r0));
+                        bb |= sgb_stage_count_u16(H.x, H.x_type, a, b, (uint16_t*)(base + off_x) + (a - r0));
+                    } else {
+                        bb |= sgb_stage_count_i32(H.n, H.n_type, a, b, (int32_t*)base + (a - r0));
+                        bb |= sgb_stage_count_i32(H.x, H.x_type, a, b, (int32_t*)(base + off_x) + (a - r0));
+                    }
+                    bb |= sgb_stage_cn_u8(H.cn, H.cn_type, a, b, (uint8_t*)(base + off_c) + (a - r0));
+                    if (bb) bits.fetch_or(bb);
+                });
+                SL.pend_rows = 0;
+                if (narrow && (bits.load() & SGB_STG_WIDE)) {
+                    // a count beyond uint16 (or negative): this chunk goes over as int32 and the device validates it
+                    narrow = false;
+                    C->pool->run([&](int w, int nw) {
+                        const int64_t a = r0 + rows * w / nw, b = r0 + rows * (w + 1) / nw;
+                        if (b <= a) return;
+                        sgb_stage_count_i32(H.n, H.n_type, a, b, (int32_t*)base + (a - r0));
+                        sgb_stage_count_i32(H.x, H.x_type, a, b, (int32_t*)(base + off_x) + (a - r0));
+                    });
+                }
+                host_bits |= bits.load() & (SGB_STG_NOT_INT | SGB_STG_BAD_CN);
+                const size_t esz = narrow ? 2 : 4;
+                SGB_CUDA(cudaMemcpyAsync(SL.n.p, base, (size_t)rows * esz, cudaMemcpyHostToDevice, st));
+                SGB_CUDA(cudaMemcpyAsync(SL.x.p, base + off_x, (size_t)rows * esz, cudaMemcpyHostToDevice, st));
+                SGB_CUDA(cudaMemcpyAsync(SL.cn.p, base + off_c, (size_t)rows, cudaMemcpyHostToDevice, st));
+                kind = narrow ? SGB_IN_U16_U8 : SGB_IN_I32_U8;
+                dev_cn_itemsize = 1;
+            } else {
+                SGB_CUDA(cudaMemcpyAsync(SL.n.p, (const int32_t*)H.n + r0, (size_t)rows * 4, cudaMemcpyHostToDevice, st));
+                SGB_CUDA(cudaMemcpyAsync(SL.x.p, (const int32_t*)H.x + r0, (size_t)rows * 4, cudaMemcpyHostToDevice, st));
+                SGB_CUDA(cudaMemcpyAsync(SL.cn.p, (const char*)H.cn + (size_t)r0 * cn_itemsize, (size_t)rows * cn_itemsize,
+                                         cudaMemcpyHostToDevice, st));
+            }
             SGB_CUDA(cudaStreamWaitEvent(st, C->ev_setup, 0));
-            SgbRawIn raw = {(const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, rows, C->d_err};
+            const int use_split = (m.decode == SGB_DECODE_REFERENCE) && (use_split0 || kind == SGB_IN_U16_U8);
             if (use_split) {
-                const SgbColsIn in = {SL.n.p, SL.x.p, SL.cn.p, cn_itemsize == 4 ? SGB_IN_I32_I32 : SGB_IN_I32_U8, rows, C->d_err};
+                const SgbColsIn in = {SL.n.p, SL.x.p, SL.cn.p, kind, rows, C->d_err};
                 std::vector<SplitSlice> slices;
                 if (run_split(SL.split, slices, SL.hp, pd, in, C->d_tabs, m, (uint8_t*)SL.out.p, C->sm_count, st, nullptr, nullptr))
                     return 1;
             } else {
-            if (cn_itemsize == 4) {
-                // an int32 cn column (R integers) is narrowed to uint8 on the device when that lets k_decode read in place
-                SgbRawIn probe = raw;
-                probe.cn = nullptr; probe.cn_itemsize = 1;
-                if (sgbk_resolve_stage(m, C->stage, probe) == 2) {
-                    if (SL.cn8.reserve((size_t)rows + 16)) return 1;
-                    SGB_CUDA(sgbk_narrow_cn((const int32_t*)SL.cn.p, rows, (uint8_t*)SL.cn8.p, C->d_err, st));
-                    raw.cn = SL.cn8.p; raw.cn_itemsize = 1;
+                SgbRawIn raw = {(const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, dev_cn_itemsize, rows, C->d_err};
+                if (dev_cn_itemsize == 4) {
+                    // an int32 cn column (R integers) is narrowed to uint8 on the device when that lets k_decode read in place
+                    SgbRawIn probe = raw;
+                    probe.cn = nullptr; probe.cn_itemsize = 1;
+                    if (sgbk_resolve_stage(m, C->stage, probe) == 2) {
+                        if (SL.cn8.reserve((size_t)rows + 16)) return 1;
+                        SGB_CUDA(sgbk_narrow_cn((const int32_t*)SL.cn.p, rows, (uint8_t*)SL.cn8.p, C->d_err, st));
+                        raw.cn = SL.cn8.p; raw.cn_itemsize = 1;
+                    }
                 }
+                const int stage = sgbk_resolve_stage(m, C->stage, raw);
+                if (stage != 2 && SL.packed.reserve((size_t)SL.hp.packed_len * 8 + 16)) return 1;    // packed records: only off the RAW path
+                if (stage != 2)
+                    SGB_CUDA(sgbk_pack((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, dev_cn_itemsize, pd,
+                                       (unsigned long long*)SL.packed.p, C->d_err, st));
+                SGB_CUDA(sgbk_decode(pd, (const unsigned long long*)SL.packed.p, raw, C->d_tabs, m, (uint8_t*)SL.out.p,
+                                     (uint8_t*)SL.bp.p, (int*)SL.last_state.p, SL.counter, C->sm_count, stage, st));
+                if (m.decode == SGB_DECODE_CHAINED)
+                    SGB_CUDA(sgbk_backtrace(pd, (const uint8_t*)SL.bp.p, (const int*)SL.last_state.p, S, (uint8_t*)SL.out.p, st));
             }
-            const int stage = sgbk_resolve_stage(m, C->stage, raw);
-            if (stage != 2 && SL.packed.reserve((size_t)SL.hp.packed_len * 8 + 16)) return 1;    // packed records: only off the RAW path
-            if (stage != 2)
-                SGB_CUDA(sgbk_pack((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, pd,
-                                   (unsigned long long*)SL.packed.p, C->d_err, st));
-            SGB_CUDA(sgbk_decode(pd, (const unsigned long long*)SL.packed.p, raw, C->d_tabs, m, (uint8_t*)SL.out.p,
-                                 (uint8_t*)SL.bp.p, (int*)SL.last_state.p, SL.counter, C->sm_count, stage, st));
-            if (m.decode == SGB_DECODE_CHAINED)
-                SGB_CUDA(sgbk_backtrace(pd, (const uint8_t*)SL.bp.p, (const int*)SL.last_state.p, S, (uint8_t*)SL.out.p, st));
+            if (staged) {
+                SGB_CUDA(cudaMemcpyAsync(SL.stage_out.p, SL.out.p, (size_t)rows, cudaMemcpyDeviceToHost, st));
+                SL.pend_r0 = r0; SL.pend_rows = rows;
+            } else {
+                SGB_CUDA(cudaMemcpyAsync((uint8_t*)H.out + r0, SL.out.p, (size_t)rows, cudaMemcpyDeviceToHost, st));
             }
-            SGB_CUDA(cudaMemcpyAsync(state_out + r0, SL.out.p, (size_t)rows, cudaMemcpyDeviceToHost, st));
             if (loglik_out) {
-                SGB_CUDA(sgbk_loglik((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, cn_itemsize, pd,
+                SGB_CUDA(sgbk_loglik((const int32_t*)SL.n.p, (const int32_t*)SL.x.p, SL.cn.p, dev_cn_itemsize, pd,
                                      C->d_tabs, m, (double*)SL.loglik.p, st));
                 SGB_CUDA(cudaMemcpyAsync(loglik_out + (size_t)r0 * S, SL.loglik.p, (size_t)rows * S * 8,
                                          cudaMemcpyDeviceToHost, st));
@@ -492,26 +628,17 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
         s0 = s1;
         k++;
     }
-    SGB_CUDA(cudaStreamSynchronize(C->slot[0].st));
-    SGB_CUDA(cudaStreamSynchronize(C->slot[1].st));
+    // drain in slot order: the older slot's states go out while the younger one still computes
+    for (int j = 0; j < 2; j++) {
+        Slot& SL = C->slot[(k + j) & 1];
+        SGB_CUDA(cudaStreamSynchronize(SL.st));
+        if (staged) unstage(SL);
+    }
     int bits = 0;
     SGB_CUDA(cudaMemcpy(&bits, C->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (host_bits & SGB_STG_NOT_INT) bits |= SGB_ERR_NOT_INTEGER;
+    if (host_bits & SGB_STG_BAD_CN) bits |= SGB_ERR_BAD_CN;
     if (bits) return fail(err_bits_text(bits));
-    return 0;
-}
-
-int check_batch_args(int64_t N, const int32_t* n, const int32_t* x, const void* cn, int32_t cn_itemsize,
-                     int64_t nseg, const int64_t* seg_off, const uint8_t* state_out)
-{
-    if (N < 0 || nseg < 0) return fail("negative size");
-    if (cn_itemsize != 1 && cn_itemsize != 4) return fail("cn_itemsize must be 1 (uint8) or 4 (int32)");
-    if (nseg > 0 && !seg_off) return fail("seg_off is NULL");
-    if (N > 0 && (!n || !x || !cn || !state_out)) return fail("NULL data pointer");
-    if (nseg > 0) {
-        if (seg_off[0] < 0 || seg_off[nseg] > N) return fail("seg_off out of range");
-        for (int64_t s = 0; s < nseg; s++)
-            if (seg_off[s + 1] < seg_off[s]) return fail("seg_off must be non-decreasing");
-    }
     return 0;
 }
 
@@ -556,7 +683,7 @@ int sgb_shutdown(void)
             if (s.st) { cudaStreamSynchronize(s.st); cudaStreamDestroy(s.st); }
             s.n.release(); s.x.release(); s.cn.release(); s.cn8.release(); s.out.release(); s.packed.release(); s.bp.release();
             s.last_state.release(); s.pin.release(); s.goff.release(); s.ostart.release(); s.len.release(); s.loglik.release();
-            s.split.release();
+            s.split.release(); s.stage_in.release(); s.stage_out.release();
             if (s.counter) cudaFree(s.counter);
         }
         c->scratch_a.release(); c->scratch_b.release(); c->scratch_c.release(); c->scratch_d.release();
@@ -571,27 +698,30 @@ int sgb_shutdown(void)
     return 0;
 }
 
-int sgb_hmm_decode(const sgb_params* params, int64_t N, const int32_t* n, const int32_t* x, const void* cn,
-                   int32_t cn_itemsize, int64_t nseg, const int64_t* seg_off, uint8_t* state_out,
-                   double* loglik_out)
+static int decode_typed(const sgb_params* params, int64_t N, const HostCols& H, int64_t nseg, const int64_t* seg_off,
+                        double* loglik_out, int32_t n_devices)
 {
     SgbModelArgs m;
     if (check_params(params, m)) return 1;
-    if (check_batch_args(N, n, x, cn, cn_itemsize, nseg, seg_off, state_out)) return 1;
-    Ctx* C;
-    if (get_ctx(&C)) return 1;
-    return decode_host_range(C, params, m, n, x, cn, cn_itemsize, seg_off, 0, nseg, state_out, loglik_out);
-}
-
-int sgb_hmm_decode_multi(const sgb_params* params, int32_t n_devices, int64_t N, const int32_t* n,
-                         const int32_t* x, const void* cn, int32_t cn_itemsize, int64_t nseg,
-                         const int64_t* seg_off, uint8_t* state_out)
-{
-    SgbModelArgs m;
-    if (check_params(params, m)) return 1;
-    if (check_batch_args(N, n, x, cn, cn_itemsize, nseg, seg_off, state_out)) return 1;
+    if (N < 0 || nseg < 0) return fail("negative size");
+    if (!sgb_type_size(H.n_type) || !sgb_type_size(H.x_type) || !sgb_type_size(H.cn_type))
+        return fail("column element type must be one of SGB_T_U8, SGB_T_U16, SGB_T_I32, SGB_T_F64");
+    if (!sgb_type_size(H.out_type)) return fail("state_out element type must be one of SGB_T_U8, SGB_T_U16, SGB_T_I32, SGB_T_F64");
+    if (nseg > 0 && !seg_off) return fail("seg_off is NULL");
+    if (N > 0 && (!H.n || !H.x || !H.cn || !H.out)) return fail("NULL data pointer");
+    if (nseg > 0) {
+        if (seg_off[0] < 0 || seg_off[nseg] > N) return fail("seg_off out of range");
+        for (int64_t s = 0; s < nseg; s++)
+            if (seg_off[s + 1] < seg_off[s]) return fail("seg_off must be non-decreasing");
+    }
+    if (n_devices <= 1) {
+        Ctx* C;
+        if (get_ctx(&C)) return 1;
+        return decode_host_range(C, params, m, H, seg_off, 0, nseg, loglik_out, 1);
+    }
+    if (loglik_out) return fail("loglik_out is single-device only");
     int avail = sgb_device_count();
-    if (n_devices < 1 || n_devices > avail) return fail("n_devices must be between 1 and the number of visible CUDA devices");
+    if (n_devices > avail) return fail("n_devices must be between 1 and the number of visible CUDA devices");
     if (nseg == 0) return 0;
     // contiguous blocks of sequences, balanced by bins
     std::vector<int64_t> cut((size_t)n_devices + 1, nseg);
@@ -613,8 +743,7 @@ int sgb_hmm_decode_multi(const sgb_params* params, int32_t n_devices, int64_t N,
             if (cudaSetDevice(d) != cudaSuccess) { rc[(size_t)d] = 1; msg[(size_t)d] = "cudaSetDevice failed"; return; }
             Ctx* C;
             if (get_ctx(&C)) { rc[(size_t)d] = 1; msg[(size_t)d] = t_err; return; }
-            rc[(size_t)d] = decode_host_range(C, params, m, n, x, cn, cn_itemsize, seg_off, cut[(size_t)d],
-                                              cut[(size_t)d + 1], state_out, nullptr);
+            rc[(size_t)d] = decode_host_range(C, params, m, H, seg_off, cut[(size_t)d], cut[(size_t)d + 1], nullptr, n_devices);
             if (rc[(size_t)d]) msg[(size_t)d] = t_err;
         });
     }
@@ -623,6 +752,34 @@ int sgb_hmm_decode_multi(const sgb_params* params, int32_t n_devices, int64_t N,
     for (int d = 0; d < n_devices; d++)
         if (rc[(size_t)d]) return fail("device " + std::to_string(d) + ": " + msg[(size_t)d]);
     return 0;
+}
+
+int sgb_hmm_decode(const sgb_params* params, int64_t N, const int32_t* n, const int32_t* x, const void* cn,
+                   int32_t cn_itemsize, int64_t nseg, const int64_t* seg_off, uint8_t* state_out,
+                   double* loglik_out)
+{
+    if (cn_itemsize != 1 && cn_itemsize != 4) return fail("cn_itemsize must be 1 (uint8) or 4 (int32)");
+    const HostCols H = {n, SGB_T_I32, x, SGB_T_I32, cn, cn_itemsize == 4 ? SGB_T_I32 : SGB_T_U8, state_out, SGB_T_U8};
+    return decode_typed(params, N, H, nseg, seg_off, loglik_out, 1);
+}
+
+int sgb_hmm_decode_multi(const sgb_params* params, int32_t n_devices, int64_t N, const int32_t* n,
+                         const int32_t* x, const void* cn, int32_t cn_itemsize, int64_t nseg,
+                         const int64_t* seg_off, uint8_t* state_out)
+{
+    if (cn_itemsize != 1 && cn_itemsize != 4) return fail("cn_itemsize must be 1 (uint8) or 4 (int32)");
+    if (n_devices < 1) return fail("n_devices must be between 1 and the number of visible CUDA devices");
+    const HostCols H = {n, SGB_T_I32, x, SGB_T_I32, cn, cn_itemsize == 4 ? SGB_T_I32 : SGB_T_U8, state_out, SGB_T_U8};
+    return decode_typed(params, N, H, nseg, seg_off, nullptr, n_devices);
+}
+
+int sgb_hmm_decode_typed(const sgb_params* params, int64_t N, const void* n, int32_t n_type, const void* x, int32_t x_type,
+                         const void* cn, int32_t cn_type, int64_t nseg, const int64_t* seg_off, void* state_out,
+                         int32_t out_type, int32_t n_devices)
+{
+    if (n_devices < 1) return fail("n_devices must be between 1 and the number of visible CUDA devices");
+    const HostCols H = {n, n_type, x, x_type, cn, cn_type, state_out, out_type};
+    return decode_typed(params, N, H, nseg, seg_off, nullptr, n_devices);
 }
 
 // ---------------------------------------------------------------- device-resident path

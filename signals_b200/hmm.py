@@ -94,32 +94,54 @@ def viterbiR(emission, transition, observations):
 
 
 # ---------------------------------------------------------------------------------- array-level batch
+_TYPE_CODE = {np.dtype(np.uint8): _lib.T_U8, np.dtype(np.uint16): _lib.T_U16, np.dtype(np.int32): _lib.T_I32,
+              np.dtype(np.float64): _lib.T_F64}
+
+
+def _as_column(a, name):
+    """a contiguous array in one of the element types the library takes as is (uint8, uint16, int32, float64); other
+    integer types are converted to int32 (range-checked), other floats to float64"""
+    a = np.asarray(a)
+    if a.dtype in _TYPE_CODE:
+        return np.ascontiguousarray(a)
+    if a.dtype.kind == "f":
+        return np.ascontiguousarray(a, dtype=np.float64)
+    return _as_counts(a, name)
+
+
 def decode_arrays(n, x, cn, seg_off, model="hscn", likelihood="binomial", n_states=12, loherror=0.02, eps=1e-12,
                   rho=0.0, Abias=0.0, selftransitionprob=0.999, decode="reference", want_loglik=False,
-                  n_devices=1):
-    """Decode every sequence of a sorted long table given as flat arrays.  Returns uint8 states
-    (and the per-sequence column-major `l` blocks when want_loglik)."""
+                  n_devices=1, out_dtype=np.uint8):
+    """Decode every sequence of a sorted long table given as flat arrays.  Returns the states (uint8 unless out_dtype
+    says otherwise; and the per-sequence column-major `l` blocks when want_loglik).  Columns may be int32, float64
+    (integer valued: R numeric vectors), uint16 or uint8, each on its own."""
     lib = _lib.load()
-    n = _as_counts(n, "totalcounts"); x = _as_counts(x, "alleleB")
-    cn = np.asarray(cn)
-    if cn.dtype != np.uint8:
-        cn = _as_counts(cn, "state")
-    cn = np.ascontiguousarray(cn)
     seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+    P = make_params(model, likelihood, n_states, loherror, eps, rho, Abias, selftransitionprob, decode)
+    if want_loglik:
+        # the `l` matrix path takes int32 counts
+        n = _as_counts(n, "totalcounts"); x = _as_counts(x, "alleleB")
+        cn = np.asarray(cn)
+        if cn.dtype != np.uint8:
+            cn = _as_counts(cn, "state")
+        cn = np.ascontiguousarray(cn)
+        if not (n.size == x.size == cn.size):
+            raise ValueError("n, x and cn must have the same length")
+        if n_devices > 1:
+            raise ValueError("want_loglik is single-device only")
+        out = np.zeros(n.size, dtype=np.uint8)
+        ll = np.empty(n.size * int(n_states), dtype=np.float64)
+        check(lib.sgb_hmm_decode(ctypes.byref(P), n.size, _ptr(n), _ptr(x), _ptr(cn), cn.dtype.itemsize,
+                                 seg_off.size - 1, _ptr(seg_off), _ptr(out), _ptr(ll)))
+        return out, ll
+    n = _as_column(n, "totalcounts"); x = _as_column(x, "alleleB"); cn = _as_column(cn, "state")
     if not (n.size == x.size == cn.size):
         raise ValueError("n, x and cn must have the same length")
-    P = make_params(model, likelihood, n_states, loherror, eps, rho, Abias, selftransitionprob, decode)
-    out = np.zeros(n.size, dtype=np.uint8)
-    ll = np.empty(n.size * int(n_states), dtype=np.float64) if want_loglik else None
-    if n_devices > 1:
-        if want_loglik:
-            raise ValueError("want_loglik is single-device only")
-        check(lib.sgb_hmm_decode_multi(ctypes.byref(P), int(n_devices), n.size, _ptr(n), _ptr(x), _ptr(cn),
-                                       cn.dtype.itemsize, seg_off.size - 1, _ptr(seg_off), _ptr(out)))
-    else:
-        check(lib.sgb_hmm_decode(ctypes.byref(P), n.size, _ptr(n), _ptr(x), _ptr(cn), cn.dtype.itemsize,
-                                 seg_off.size - 1, _ptr(seg_off), _ptr(out), _ptr(ll) if want_loglik else None))
-    return (out, ll) if want_loglik else out
+    out = np.zeros(n.size, dtype=np.dtype(out_dtype))
+    check(lib.sgb_hmm_decode_typed(ctypes.byref(P), n.size, _ptr(n), _TYPE_CODE[n.dtype], _ptr(x), _TYPE_CODE[x.dtype],
+                                   _ptr(cn), _TYPE_CODE[cn.dtype], seg_off.size - 1, _ptr(seg_off), _ptr(out),
+                                   _TYPE_CODE[out.dtype], int(n_devices)))
+    return out
 
 
 def postprocess_arrays(cn, path):

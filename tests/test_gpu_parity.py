@@ -513,3 +513,57 @@ def test_tables_identical_across_math_flavours_and_gpu(oracle, model, lik, rho):
                 assert np.array_equal(gpu_tab[k], tab[k]), (flavour, k, int((gpu_tab[k] != tab[k]).sum()))
     if model == "hscn":
         assert n_path_diff > 0                      # the test would be vacuous if rounding never decided a tie
+
+
+def test_typed_columns_pageable_and_pinned(oracle, monkeypatch):
+    """sgb_hmm_decode_typed: every column in its own element type (R hands over INTSXP = int32 or REALSXP = double
+    vectors, pageable), states returned as uint8 or as doubles, staged through page-locked buffers by worker threads
+    (narrowed to uint16 / uint8) or copied directly; all must give the oracle's paths."""
+    import torch
+    d = cases.small_cohort("binomial", n_cells=120, seed=33)
+    n, x, cn, so = d["n"], d["x"], d["cn"], d["seg_off"]
+    ps = cases.PARAM_SETS[0]
+    ref = oracle.decode_batch(n, x, cn.astype(np.int32), so, oracle.params(**cases.param_dict(ps)), oracle.MATH_DET, nthreads=4)
+    monkeypatch.setenv("SGB_CHUNK_BINS", "70000")          # several chunks, so the slot staging is reused
+    combos = [(np.int32, np.int32, np.int32), (np.float64, np.float64, np.float64), (np.float64, np.int32, np.uint8),
+              (np.uint16, np.uint16, np.uint8), (np.int32, np.float64, np.float64)]
+    for tn, tx, tc in combos:
+        for out_dtype in (np.uint8, np.float64, np.int32):
+            got = hmm.decode_arrays(n.astype(tn), x.astype(tx), cn.astype(tc), so, out_dtype=out_dtype, **_kw(ps))
+            assert got.dtype == np.dtype(out_dtype) and np.array_equal(got.astype(np.uint8), ref), (tn, tx, tc, out_dtype)
+    # page-locked int32 columns: staged (default) and direct (SGB_HOST_STAGE=never) feeds agree
+    hn = torch.from_numpy(n).pin_memory(); hx = torch.from_numpy(x).pin_memory()
+    hc = torch.from_numpy(cn.astype(np.int32)).pin_memory(); ho = torch.zeros(n.size, dtype=torch.uint8).pin_memory()
+    lib = _lib.load()
+    P = hmm.make_params(**_kw(ps))
+    import ctypes
+    for mode in ("auto", "never", "always"):
+        monkeypatch.setenv("SGB_HOST_STAGE", mode)
+        ho.zero_()
+        hmm.check(lib.sgb_hmm_decode(ctypes.byref(P), n.size, hn.data_ptr(), hx.data_ptr(), hc.data_ptr(), 4, so.size - 1,
+                                     so.ctypes.data, ho.data_ptr(), None))
+        assert np.array_equal(ho.numpy(), ref), mode
+    monkeypatch.delenv("SGB_HOST_STAGE")
+    # a chunk with a count beyond uint16 goes over as int32 (same answer as the oracle); the other chunks stay narrow
+    n2 = n.copy(); x2 = x.copy()
+    n2[100000] = 70000; x2[100000] = 35000
+    ref2 = oracle.decode_batch(n2, x2, cn.astype(np.int32), so, oracle.params(**cases.param_dict(ps)), oracle.MATH_DET, nthreads=4)
+    assert np.array_equal(hmm.decode_arrays(n2, x2, cn, so, **_kw(ps)), ref2)
+    assert np.array_equal(hmm.decode_arrays(n2.astype(np.float64), x2.astype(np.float64), cn, so, **_kw(ps)), ref2)
+    # what the reference would turn into NaN / -Inf rows is an error here, with a message that names the problem
+    bad = n.astype(np.float64); bad[7] = np.nan
+    with pytest.raises(hmm.SignalsB200Error, match="not an integer"):
+        hmm.decode_arrays(bad, x, cn, so, **_kw(ps))
+    bad = x.astype(np.float64); bad[7] = 2.5
+    with pytest.raises(hmm.SignalsB200Error, match="not an integer"):
+        hmm.decode_arrays(n, bad, cn, so, **_kw(ps))
+    bad = cn.astype(np.float64); bad[7] = 300.0
+    with pytest.raises(hmm.SignalsB200Error, match="copy-number"):
+        hmm.decode_arrays(n, x, bad, so, **_kw(ps))
+    bad = n.astype(np.float64); bad[7] = -3.0
+    with pytest.raises(hmm.SignalsB200Error, match="negative"):
+        hmm.decode_arrays(bad, x, cn, so, **_kw(ps))
+    bad = n.astype(np.float64); bad[7] = 2.0 ** 40
+    with pytest.raises(hmm.SignalsB200Error, match="not an integer|2\\^28"):
+        hmm.decode_arrays(bad, x, cn, so, **_kw(ps))
+    assert np.array_equal(hmm.decode_arrays(n, x, cn, so, **_kw(ps)), ref)       # and the library still works
