@@ -216,7 +216,9 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
     N = d["n"].size
     # pinned host buffers (e2e inputs / outputs) and resident device copies (value)
     hn = torch.from_numpy(d["n"]).pin_memory(); hx = torch.from_numpy(d["x"]).pin_memory()
-    cn_host = d["cn"] if os.environ.get("BENCH_CN8") == "1" else d["cn"].astype(np.int32)   # R hands int32 states over (default)
+    # the state column as uint8 (comparable with round 1; what a caller that keeps narrow arrays passes) unless BENCH_CN32=1;
+    # the int32 column R's INTSXP vectors give is measured beside it (value_int32_state, e2e.variants)
+    cn_host = d["cn"].astype(np.int32) if os.environ.get("BENCH_CN32") == "1" else d["cn"]
     hc = torch.from_numpy(cn_host).pin_memory()
     hout = torch.zeros(N, dtype=torch.uint8).pin_memory()
     tn, tx, tc = hn.to(dev), hx.to(dev), hc.to(dev)
@@ -422,10 +424,9 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         nseq = d["seg_off"].size - 1
         res["e2e"] = dict(value=N * world / (e2e_ms * 1e-3), unit="cell-bins/s", ms_per_step=e2e_ms,
                           h2d_bytes_per_step=int(N * (8 + cn_host.dtype.itemsize) + nseq * 20), d2h_bytes_per_step=int(N), steps=e2e_steps,
-                          api="sgb_hmm_decode (host buffers: page-locked int32 columns in, uint8 states out; chunked, staged + "
-                              "narrowed to 5 B/cell-bin by worker threads unless SGB_HOST_NARROW=0)",
-                          bytes_note="h2d/d2h = bytes of the caller's tensors consumed / produced per step; the staged path moves "
-                                     "5 B per cell-bin over PCIe (uint16 counts + uint8 state), the direct path all of them")
+                          api="sgb_hmm_decode (host buffers: page-locked int32 counts + %s state in, uint8 states out; chunked "
+                              "copy / compute overlap, copied directly)" % cn_host.dtype,
+                          bytes_note="h2d/d2h = bytes of the caller's tensors consumed / produced per step")
         assert int(hout.to(torch.int64).sum().item()) == res["checksum"], "host-API and device-API results differ"
         if want_e2e == "all" and world == 1:
             # the same call as an R session makes it: PAGEABLE vectors, INTSXP (int32) or REALSXP (double) columns, states
@@ -450,16 +451,21 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                 variants[label] = dict(value=N / (ms * 1e-3), ms_per_step=ms,
                                        h2d_bytes_per_step=int(N * 3 * np.dtype(dt_in).itemsize), d2h_bytes_per_step=int(N * np.dtype(dt_out).itemsize))
                 del pn, px, pc, po
-            os.environ["SGB_HOST_NARROW"] = "0"
-            for _ in range(2):
-                hmm.check(lib.sgb_hmm_decode(*args))
-            t0 = time.perf_counter()
-            for _ in range(3):
-                hmm.check(lib.sgb_hmm_decode(*args))
-            ms = (time.perf_counter() - t0) / 3 * 1e3
-            del os.environ["SGB_HOST_NARROW"]
-            variants["pinned_int32_direct_no_staging"] = dict(value=N / (ms * 1e-3), ms_per_step=ms,
-                                                              h2d_bytes_per_step=int(N * (8 + cn_host.dtype.itemsize)), d2h_bytes_per_step=int(N))
+            hc32 = torch.from_numpy(d["cn"].astype(np.int32)).pin_memory()
+            a32 = (ctypes.byref(P), N, hn.data_ptr(), hx.data_ptr(), hc32.data_ptr(), 4, d["seg_off"].size - 1,
+                   d["seg_off"].ctypes.data, hout.data_ptr(), None)
+            for label, env in (("pinned_int32_state_direct", None), ("pinned_int32_state_staged_narrowed", "1")):
+                if env:
+                    os.environ["SGB_HOST_NARROW"] = env
+                for _ in range(2):
+                    hmm.check(lib.sgb_hmm_decode(*a32))
+                t0 = time.perf_counter()
+                for _ in range(3):
+                    hmm.check(lib.sgb_hmm_decode(*a32))
+                ms = (time.perf_counter() - t0) / 3 * 1e3
+                os.environ.pop("SGB_HOST_NARROW", None)
+                variants[label] = dict(value=N / (ms * 1e-3), ms_per_step=ms, h2d_bytes_per_step=int(N * 12), d2h_bytes_per_step=int(N))
+            del hc32
             res["e2e"]["variants"] = variants
     for pl in plans:
         pl.close()
@@ -494,7 +500,7 @@ def main():
               "l2": "inputs (%d MB per GPU) %s" % (n_cells * bins_per_cell * 12 // 1000000,
                                                    "larger than L2; no explicit flush" if n_cells * bins_per_cell * 12 > 200e6
                                                    else "fit in L2: 256 MB flush write between individually timed steps"),
-              "columns": "totalcounts, alleleB, state as int32 (R integer vectors)",
+              "columns": "totalcounts, alleleB int32; state uint8 (int32-state and pageable / double variants are reported beside the headline)",
               # best-effort NUMA binding of the ranks' pinned buffers is applied when world > 1 (both arms carry the key)
               "host_numa_binding": bool(world > 1 and os.environ.get("BENCH_NUMA", "1") == "1")}
 
@@ -604,6 +610,12 @@ def main():
                           "kernel_ms": km, "schedule": "split" if r["staging"] == 4 else "fused", "e2e_value": r["e2e"]["value"],
                           "fp64_frac": f2 / (km * 1e-3) / 1e12 / fp64_peak, "flop_eq_per_cell_bin": f2 / r["N"]}
             del dd
+        # the headline workload with the state column as the int32 vector R holds (k_narrow_cn joins the step)
+        os.environ["BENCH_CN32"] = "1"
+        r = gpu_measure(a.workload, d, max(5, a.steps // 2), 3, 0, 1, None, sampler, want_e2e=False)
+        os.environ.pop("BENCH_CN32", None)
+        others["%s_int32_state" % a.workload] = {"value": r["value"], "ms_per_step": r["ms_per_step"], "kernels": r["kernels"],
+                                                 "kernel_ms": r["pack_ms"] + r["emit_ms"] + r["decode_ms"]}
         line["other_workloads"] = others
         cb, _, _ = cpu_reference_run(d, model, lik, rho, 12.0, 1, 0, one_thread_seconds=6.0)
         line["cpu_baseline"] = cb
