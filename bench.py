@@ -466,6 +466,30 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                 os.environ.pop("SGB_HOST_NARROW", None)
                 variants[label] = dict(value=N / (ms * 1e-3), ms_per_step=ms, h2d_bytes_per_step=int(N * 12), d2h_bytes_per_step=int(N))
             del hc32
+            # through the .Call shim itself (rpkg/src/r_shim.c compiled against the mock of R's C API, tests/r_mock): the call
+            # an R session makes, on pageable INTSXP / REALSXP vectors, numeric state_min back
+            shim_so = os.path.join(ROOT, "tests", "r_mock", "libshimtest.so")
+            if os.path.exists(shim_so):
+                try:
+                    sh = ctypes.CDLL(shim_so)
+                    sh.drv_decode_batch_timed.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long,
+                                                          ctypes.c_void_p, ctypes.c_long, ctypes.c_char_p, ctypes.c_int] + \
+                        [ctypes.c_double] * 5 + [ctypes.c_int] * 3 + [ctypes.POINTER(ctypes.c_double)] * 2 + [ctypes.c_char_p]
+                    cn32 = d["cn"].astype(np.int32)
+                    segd = so_.astype(np.float64)
+                    for label, asd in (("r_shim_call_pageable_INTSXP", 0), ("r_shim_call_pageable_REALSXP", 1)):
+                        ms_ = ctypes.c_double(0.0); cs_ = ctypes.c_double(0.0); eb = ctypes.create_string_buffer(1024)
+                        rc = sh.drv_decode_batch_timed(1 if model == "ascn" else 0, d["n"].ctypes.data, d["x"].ctypes.data, cn32.ctypes.data,
+                                                       N, segd.ctypes.data, segd.size - 1, lik.encode(), PARAMS["n_states"] - 1,
+                                                       PARAMS["loherror"], PARAMS["eps"], rho, PARAMS["Abias"], PARAMS["selftransitionprob"],
+                                                       asd, 1, 3, ctypes.byref(ms_), ctypes.byref(cs_), eb)
+                        if rc == 0 and int(cs_.value) == res["checksum"]:
+                            variants[label] = dict(value=N / (ms_.value * 1e-3), ms_per_step=ms_.value,
+                                                   h2d_bytes_per_step=int(N * 3 * (8 if asd else 4)), d2h_bytes_per_step=int(N * 8))
+                        else:
+                            variants[label] = dict(error=eb.value.decode() or "checksum mismatch")
+                except Exception as ex:
+                    variants["r_shim_call"] = dict(error=str(ex))
             res["e2e"]["variants"] = variants
     for pl in plans:
         pl.close()

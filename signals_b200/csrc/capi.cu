@@ -336,7 +336,7 @@ int check_params(const sgb_params* P, SgbModelArgs& m)
 
 const char* err_bits_text(int bits)
 {
-    if (bits & SGB_ERR_NEGATIVE_COUNT) return "negative read count in totalcounts / alleleB";
+    if (bits & SGB_ERR_NEGATIVE_COUNT) return "negative read count (or NA_integer_) in totalcounts / alleleB";
     if (bits & SGB_ERR_COUNT_TOO_LARGE) return "read count >= 2^28 is not supported";
     if (bits & SGB_ERR_BAD_CN) return "copy-number state outside 0..255";
     if (bits & SGB_ERR_NOT_INTEGER) return "a numeric (double) column holds NA / NaN or a value that is not an integer";
@@ -571,8 +571,9 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
                     C->pool->run([&](int w, int nw) {
                         const int64_t a = r0 + rows * w / nw, b = r0 + rows * (w + 1) / nw;
                         if (b <= a) return;
-                        sgb_stage_count_i32(H.n, H.n_type, a, b, (int32_t*)base + (a - r0));
-                        sgb_stage_count_i32(H.x, H.x_type, a, b, (int32_t*)(base + off_x) + (a - r0));
+                        const int bb = sgb_stage_count_i32(H.n, H.n_type, a, b, (int32_t*)base + (a - r0)) |
+                                       sgb_stage_count_i32(H.x, H.x_type, a, b, (int32_t*)(base + off_x) + (a - r0));
+                        if (bb) bits.fetch_or(bb);
                     });
                 }
                 host_bits |= bits.load() & (SGB_STG_NOT_INT | SGB_STG_BAD_CN);

@@ -35,32 +35,38 @@ def shim():
                                 ctypes.c_void_p, ctypes.c_char_p]
     lib.drv_decode_batch.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long,
                                      ctypes.c_void_p, ctypes.c_long, ctypes.c_char_p, ctypes.c_int] + [ctypes.c_double] * 5 + \
-                                    [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_char_p]
+                                    [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_char_p]
+    lib.drv_logspace_add_vec.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p, ctypes.c_char_p]
+    lib.drv_postprocess.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_char_p]
+    lib.drv_pass_stats.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_long, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_char_p]
+    lib.drv_device_count.argtypes = [ctypes.POINTER(ctypes.c_int), ctypes.c_char_p]
     return lib
 
 
 def _decode(shim, model, n, x, cn, seg, lik="binomial", maxCN=11, loh=0.02, eps=1e-12, rho=0.0, abias=0.0, stp=0.95,
-            want_l=False, as_double=False):
+            want_l=False, as_double=False, ngpus=1):
     n = np.ascontiguousarray(n, np.int32); x = np.ascontiguousarray(x, np.int32); cn = np.ascontiguousarray(cn, np.int32)
     segd = np.ascontiguousarray(seg, np.float64)
     path = np.zeros(max(n.size, 1), np.float64)
     ll = np.zeros(max(n.size * (maxCN + 1), 1), np.float64)
     err = ctypes.create_string_buffer(1024)
     rc = shim.drv_decode_batch(model, n.ctypes.data, x.ctypes.data, cn.ctypes.data, n.size, segd.ctypes.data, segd.size - 1,
-                               lik.encode(), maxCN, loh, eps, rho, abias, stp, int(want_l), int(as_double),
+                               lik.encode(), maxCN, loh, eps, rho, abias, stp, int(want_l), int(as_double), int(ngpus),
                                path.ctypes.data, ll.ctypes.data, err)
     return rc, err.value.decode(), path[: n.size], ll[: n.size * (maxCN + 1)]
 
 
 def test_shim_compiles_and_registers_the_reference_routines(shim):
     names = ctypes.create_string_buffer(512)
-    nargs = (ctypes.c_int * 8)()
+    nargs = (ctypes.c_int * 16)()
     dyn = ctypes.c_int(-1)
-    k = shim.drv_registered(names, 512, nargs, 8, ctypes.byref(dyn))
+    k = shim.drv_registered(names, 512, nargs, 16, ctypes.byref(dyn))
     got = dict(zip(names.value.decode().strip(";").split(";"), list(nargs)[:k]))
     # src/RcppExports.cpp:39-48 registers these two names with these arities; R/RcppExports.R calls them by name
     assert got["_signals_logspace_addcpp"] == 2 and got["_signals_viterbi"] == 3
-    assert got["_signals_hmm_decode_batch"] == 13
+    assert got["_signals_hmm_decode_batch"] == 14
+    assert got["_signals_logspace_add_vec"] == 2 and got["_signals_postprocess"] == 2 and got["_signals_pass_stats"] == 5
+    assert got["_signals_device_count"] == 0
     assert dyn.value == 0                         # R_useDynamicSymbols(dll, FALSE), as the reference does
 
 
@@ -78,31 +84,75 @@ def test_shim_argument_errors_unwind_like_rf_error(shim):
 
 
 @pytest.mark.gpu
-def test_shim_results_equal_the_python_mirror(shim):
+def test_shim_results_equal_the_oracle(shim, oracle):
+    """every .Call routine of the shim, driven the way R would drive it, against the CPU oracle (not against the Python
+    mirror, which goes through the same library)"""
     d = cases.small_cohort("betabinomial", n_cells=12, seed=31)
     n, x, cn, seg = d["n"], d["x"], d["cn"], d["seg_off"]
+    cn32 = cn.astype(np.int32)
     for model, lik, rho in ((0, "binomial", 0.0), (1, "betabinomial", 0.02)):
-        ref, lref = hmm.decode_arrays(n, x, cn, seg, model="ascn" if model else "hscn", likelihood=lik, rho=rho,
-                                      n_states=12, loherror=0.02, eps=1e-12, selftransitionprob=0.95, want_loglik=True)
+        P = oracle.params(model="ascn" if model else "hscn", likelihood=lik, S=12, loherror=0.02, eps=1e-12, rho=rho,
+                          selftransitionprob=0.95)
+        ref = oracle.decode_batch(n, x, cn32, seg, P, oracle.MATH_DET).astype(np.float64)
         for as_double in (False, True):
+            # the batched path (INTSXP or REALSXP columns handed over as they are, numeric states back)
+            rc, msg, path, _ = _decode(shim, model, n, x, cn, seg, lik=lik, rho=rho, as_double=as_double)
+            assert rc == 0, msg
+            assert np.array_equal(path, ref), (model, as_double)
+            # the `l` matrix of HaplotypeHMM / alleleHMM, per sequence column-major, bit-exact vs the deterministic oracle
             rc, msg, path, ll = _decode(shim, model, n, x, cn, seg, lik=lik, rho=rho, want_l=True, as_double=as_double)
             assert rc == 0, msg
-            assert np.array_equal(path, ref.astype(np.float64))
-            assert np.array_equal(np.isinf(ll), np.isinf(lref)) and np.array_equal(ll[np.isfinite(lref)], lref[np.isfinite(lref)])
-    # non-integer counts are refused before anything reaches the device (the shim's own check)
-    # -- and device-side validation comes back through Rf_error
+            assert np.array_equal(path, ref)
+            for s_ in range(0, seg.size - 1, 37):
+                a, b = int(seg[s_]), int(seg[s_ + 1])
+                lm = oracle.emission(n[a:b], x[a:b], cn32[a:b], P, oracle.MATH_DET)
+                blk = ll[a * 12: b * 12].reshape(12, b - a).T
+                assert np.array_equal(np.isinf(blk), np.isinf(lm)) and np.array_equal(blk[np.isfinite(lm)], lm[np.isfinite(lm)])
+        # ncores / options(signals.gpus) beyond what the box has is capped, not an error
+        rc, msg, path, _ = _decode(shim, model, n, x, cn, seg, lik=lik, rho=rho, ngpus=64)
+        assert rc == 0 and np.array_equal(path, ref), msg
+    # device-side validation comes back through Rf_error; NA_integer_ is INT_MIN and named in the message
     bad = n.copy(); bad[3] = -1
     rc, msg, _, _ = _decode(shim, 0, bad, x, cn, seg)
     assert rc == 1 and msg.startswith("signals_b200: ") and "negative" in msg
-    # logspace_addcpp and viterbi under their original .Call names
-    out = ctypes.c_double(0.0); err = ctypes.create_string_buffer(1024)
+    bad[3] = -2 ** 31
+    rc, msg, _, _ = _decode(shim, 0, bad, x, cn, seg)
+    assert rc == 1 and "NA_integer_" in msg
+    # logspace_addcpp, its vector twin and viterbi
+    err = ctypes.create_string_buffer(1024)
+    out = ctypes.c_double(0.0)
     assert shim.drv_logspace_add(-3.0, math.log(1e-12), ctypes.byref(out), err) == 0
-    assert out.value == hmm.logspace_addcpp(-3.0, math.log(1e-12))
+    assert out.value == oracle.logspace_add(-3.0, math.log(1e-12), oracle.MATH_DET)
     rng = np.random.default_rng(5)
+    a_ = -rng.uniform(0, 300, 5000); b_ = -rng.uniform(0, 40, 5000)
+    o_ = np.zeros(5000)
+    assert shim.drv_logspace_add_vec(a_.ctypes.data, b_.ctypes.data, 5000, o_.ctypes.data, err) == 0, err.value
+    assert np.array_equal(o_, oracle.math_eval(5, a_, b_, oracle.MATH_DET))
     T, S = 40, 12
     em = np.asfortranarray(np.log(rng.random((T, S))))
     tr = np.asfortranarray(np.log(rng.dirichlet(np.ones(S), size=S)))
     obs = np.arange(1, T + 1, dtype=np.float64)
     path = np.zeros(T, np.float64)
     assert shim.drv_viterbi(em.ctypes.data, T, S, tr.ctypes.data, obs.ctypes.data, T, path.ctypes.data, err) == 0, err.value
-    assert np.array_equal(path, np.asarray(hmm.viterbi(em, tr, np.arange(1, T + 1)), dtype=np.float64))
+    assert np.array_equal(path, oracle.viterbi(em, tr, np.arange(1, T + 1), math=oracle.MATH_DET))
+    # post-decode columns and between-pass sums
+    P = oracle.params(model="hscn", S=12, selftransitionprob=0.95)
+    pth = oracle.decode_batch(n, x, cn32, seg, P, oracle.MATH_DET)
+    ref = oracle.postprocess(cn32, pth)
+    N = n.size
+    ints = np.zeros(6 * N, np.int32); baf = np.zeros(N)
+    pd_ = pth.astype(np.float64)
+    assert shim.drv_postprocess(cn32.ctypes.data, pd_.ctypes.data, N, ints.ctypes.data, baf.ctypes.data, err) == 0, err.value
+    for k, key in enumerate(("A", "B", "state_min", "LOH", "phase", "state_phase")):
+        assert np.array_equal(ints[k * N:(k + 1) * N], ref[key].astype(np.int32)), key
+    assert np.array_equal(baf.view(np.uint64), ref["state_BAF"].view(np.uint64))
+    sums = np.zeros(3); hist = np.zeros(144)
+    assert shim.drv_pass_stats(n.ctypes.data, x.ctypes.data, cn32.ctypes.data, pd_.ctypes.data, N, 11, sums.ctypes.data,
+                               hist.ctypes.data, err) == 0, err.value
+    ahom = (ref["B"] == 0) & (ref["A"] > 0)
+    assert sums.tolist() == [float(x[ahom].sum()), float(n[ahom].sum()), float(ahom.sum())]
+    h = np.zeros((12, 12)); sel = ref["B"] > 0
+    np.add.at(h, (ref["A"][sel], ref["B"][sel]), 1)
+    assert np.array_equal(hist.reshape(12, 12).T, h)          # R matrix [A+1, B+1], column-major
+    k = ctypes.c_int(0)
+    assert shim.drv_device_count(ctypes.byref(k), err) == 0 and k.value >= 1
