@@ -339,6 +339,7 @@ __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmi
             const unsigned needm = L >= 32 ? 0xffffffffu : (1u << L) - 1u;
             const bool lean = !act || (cprime < SGB_CN_TABLE && ins && sp.fast_ok && ((unsigned)sKM[cprime < SGB_CN_TABLE ? cprime : 0] & needm) == needm);
             const bool warp_lean = __all_sync(SGB_FULL, lean);
+            const bool uniformL = __all_sync(SGB_FULL, L == Lw || !act);
             const int trow = (act && cprime < SGB_CN_TABLE ? cprime : 1) * S;      // idle lanes: any valid row
             const int Lc = L > 0 ? L - 1 : 0;                                       // states beyond L are computed on row Lc and dropped
             for (int p = 0; p < npl; p++) {
@@ -372,8 +373,10 @@ __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmi
 #undef SGB_LEAN1
 #undef SGB_LEAN2
 #undef SGB_TI
-                        e0 = 4 * p + 0 < L ? e0 : NEG_INF; e1 = 4 * p + 1 < L ? e1 : NEG_INF;
-                        e2 = 4 * p + 2 < L ? e2 : NEG_INF; e3 = 4 * p + 3 < L ? e3 : NEG_INF;
+                        if (!uniformL) {        // lanes with fewer live states than the warp's maximum drop the surplus
+                            e0 = 4 * p + 0 < L ? e0 : NEG_INF; e1 = 4 * p + 1 < L ? e1 : NEG_INF;
+                            e2 = 4 * p + 2 < L ? e2 : NEG_INF; e3 = 4 * p + 3 < L ? e3 : NEG_INF;
+                        }
                     } else {
                         if (4 * p + 0 < L) e0 = sgb_emit_item_slow<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, 4 * p + 0, TB, sp);
                         if (4 * p + 1 < L) e1 = sgb_emit_item_slow<MODEL, LIKBB>(cprime, ins, kd, nkd, lcx, lcy, lgs, 4 * p + 1, TB, sp);
@@ -434,7 +437,25 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
     SgbSeqState<DD ? 1 : NL> st;
     const int Seff = A.S < NL ? A.S : NL;
     const double tr_self = sp.tr_self, tr_off = sp.tr_off, init = sp.init;
-    uint8_t* outp = A.state_out + ostart;
+    // Decoded states leave as aligned 32-bit words where the sequence covers a whole word of state_out (4 bins per
+    // store instead of 4 one-byte stores, each of which costs a sector operation in L1), single bytes at its two ends.
+    uint8_t* const out = A.state_out;
+    const long long kb = (long long)((unsigned long long)out & 3ull);      // state_out itself need not be word-aligned
+    const long long kfull = (ostart + kb + 3) & ~3ll;      // first word-aligned position (in address units) of this sequence
+    unsigned acc = 0;
+    auto put = [&](long long k, int v) {                   // state of row k (called for consecutive k)
+        const long long kk = k + kb;
+        if (kk < kfull) { out[k] = (uint8_t)v; return; }
+        acc |= (unsigned)v << (8 * (int)(kk & 3));
+        if ((kk & 3) == 3) { *(unsigned*)(out + k - 3) = acc; acc = 0; }
+    };
+    auto put_flush = [&](long long klast) {                // after the last row: bytes of an unfinished word
+        const long long kk = klast + kb;
+        if (kk < kfull) return;
+        const int pend = (int)((kk + 1) & 3);
+        for (int j = 0; j < pend; j++) out[klast - (pend - 1) + j] = (uint8_t)(acc >> (8 * j));
+    };
+    int lp_prev = NPL;                  // live planes of the previous bin (warp-uniform)
     int s = 0;
     for (int c = 0; c < nchunks; c++) {
         sgb_mbar_wait(&bar[s], (phases >> s) & 1u);
@@ -444,29 +465,44 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
 #pragma unroll
         for (int b = 0; b < 4; b++) {
             const int t = 4 * c + b;
-            if (t < len) {
-                double e[NL];
+            if (t >= Tmax) break;                                      // warp-uniform
+            const bool act = t < len;
+            double e[NL];
+            int lp = 1;
 #pragma unroll
-                for (int p = 0; p < NPL; p++) {
-                    int pos = b * NPL + p + lrm;        // < 2 RUN
-                    pos = pos >= RUN ? pos - RUN : pos;
-                    const double2* q = (const double2*)(mine + pos * 32);
-                    const double2 v0 = q[0], v1 = q[1];
-                    e[4 * p] = v0.x; e[4 * p + 1] = v0.y; e[4 * p + 2] = v1.x; e[4 * p + 3] = v1.y;
+            for (int p = 0; p < NPL; p++) {
+                int pos = b * NPL + p + lrm;        // < 2 RUN
+                pos = pos >= RUN ? pos - RUN : pos;
+                const double2* q = (const double2*)(mine + pos * 32);
+                const double2 v0 = q[0], v1 = q[1];
+                e[4 * p] = v0.x; e[4 * p + 1] = v0.y; e[4 * p + 2] = v1.x; e[4 * p + 3] = v1.y;
+                if (DD && p > 0) {
+                    // a plane whose four emissions are -Inf in every lane is dead for this bin: with the previous bin's
+                    // count it bounds the states the step has to touch (their forward values are -Inf and stay so)
+                    const unsigned h = (unsigned)__double2hiint(v0.x) & (unsigned)__double2hiint(v0.y) &
+                                       (unsigned)__double2hiint(v1.x) & (unsigned)__double2hiint(v1.y);
+                    if (!__all_sync(SGB_FULL, !act || h == 0xfff00000u)) lp = p + 1;
                 }
+            }
+            const int nl = DD ? (lp > lp_prev ? lp : lp_prev) : NPL;
+            lp_prev = lp;
+            if (act) {
                 int back = 0;
                 if (DD) {
                     if (t == 0) sgb_seq_init_r<NL>(*(double(*)[NL])T1, e, init, m1);
+                    else if (NPL >= 2 && nl == 1) back = sgb_seq_step_r<4>(*(double(*)[4])T1, *(const double(*)[4])e, m1, tr_self, tr_off);
+                    else if (NPL >= 3 && nl == 2) back = sgb_seq_step_r<8>(*(double(*)[8])T1, *(const double(*)[8])e, m1, tr_self, tr_off);
+                    else if (NPL >= 4 && nl == 3) back = sgb_seq_step_r<12>(*(double(*)[12])T1, *(const double(*)[12])e, m1, tr_self, tr_off);
                     else back = sgb_seq_step_r<NL>(*(double(*)[NL])T1, e, m1, tr_self, tr_off);
                 } else {
                     if (t == 0) sgb_seq_init<NL>(*(SgbSeqState<NL>*)&st, e, Seff, init);
                     else back = sgb_seq_step_general<NL>(*(SgbSeqState<NL>*)&st, e, Seff, tr_self, tr_off);
                 }
                 if (t == 0) {
-                    if (len == 1) outp[0] = 0;
+                    if (len == 1) out[ostart] = 0;
                 } else {
-                    outp[t - 1] = (uint8_t)back;
-                    if (t == len - 1) outp[t] = (uint8_t)back;
+                    put(ostart + t - 1, back);
+                    if (t == len - 1) { put(ostart + t, back); put_flush(ostart + t); }
                 }
             }
         }
