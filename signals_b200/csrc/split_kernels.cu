@@ -453,7 +453,10 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
         const long long kk = klast + kb;
         if (kk < kfull) return;
         const int pend = (int)((kk + 1) & 3);
-        for (int j = 0; j < pend; j++) out[klast - (pend - 1) + j] = (uint8_t)(acc >> (8 * j));
+        uint8_t* w = out + (klast - (pend - 1));
+        if (pend >= 1) w[0] = (uint8_t)acc;
+        if (pend >= 2) w[1] = (uint8_t)(acc >> 8);
+        if (pend >= 3) w[2] = (uint8_t)(acc >> 16);
     };
     int lp_prev = NPL;                  // live planes of the previous bin (warp-uniform)
     int s = 0;
