@@ -191,6 +191,50 @@ SGB_API int sgb_postprocess(int64_t N, const void* cn, int32_t cn_itemsize, cons
 SGB_API int sgb_pass_stats(int64_t N, const int32_t* n, const int32_t* x, const void* cn, int32_t cn_itemsize,
                            const uint8_t* path, int32_t n_states, int64_t* sums_out, int64_t* ab_hist_out);
 
+/* ---- the table passes either side of the hot path ------------------------------------ */
+/* order(cell_id, chr, start) of the long table (R/callHSCN.R:241-242) and the (cell, chromosome) sequence boundaries
+ * that replace the per-cell dplyr::filter scans (R/callHSCN.R:247,266) and the per-chromosome loops (:150-154).
+ * cell / chr are integer codes in 0..n_cells-1 / 0..n_chr-1 whose numeric order is the order R gives the strings
+ * (match(x, sort(unique(x))) - 1 in the C locale: chr "1","10",...,"2",...,"X"); start >= 0.
+ * perm_out[N]: row i of the sorted table is input row perm_out[i] (stable).  seg_off_out[nseg+1] (capacity N+1). */
+SGB_API int sgb_table_order(int64_t N, const int32_t* cell, const int32_t* chr, const int32_t* start, int32_t n_cells,
+                            int32_t n_chr, int32_t* perm_out, int64_t* nseg_out, int64_t* seg_off_out);
+/* The aggregation and filters of combineBAFCN (R/combinedata.R:309-325) on the joined CNbins x haplotypes rows:
+ * [totalcounts > filtern], sums of alleleA / alleleB / totalcounts by (chr, start, end, cell_id, state, copy), cells with
+ * <= minbins bins dropped, then cells whose smallest chromosome (chrX counted as 100) has <= minbinschr bins.  The key is
+ * (cell, chr, start): end, state and copy are functions of it after the join (rows of one key that disagree on `state`
+ * are an error).  Outputs (capacity N; seg_off N+1) are sorted by (cell, chr, start) -- the order
+ * .callHaplotypeSpecificCN_ sorts into anyway -- with first_row_out[i] = the first input row of output row i, so the
+ * caller can carry any other column (end, copy) over itself; BAF = alleleB_out / totalcounts_out. */
+SGB_API int sgb_combine_bafcn(int64_t N, const int32_t* cell, const int32_t* chr, const int32_t* start, const int32_t* state,
+                              const int32_t* alleleA, const int32_t* alleleB, const int32_t* totalcounts, int32_t n_cells,
+                              int32_t n_chr, double filtern, int32_t minbins, int32_t minbinschr, int32_t chrX_code,
+                              int64_t* nrow_out, int32_t* first_row_out, int32_t* cell_out, int32_t* chr_out,
+                              int32_t* start_out, int32_t* state_out, int32_t* alleleA_out, int32_t* alleleB_out,
+                              int32_t* totalcounts_out, int64_t* nseg_out, int64_t* seg_off_out);
+/* All the whole-table sums the drivers need between the two HMM passes, over the rows with row_keep[i] != 0 (NULL = all
+ * rows; the cells that pass the first-pass filter, R/callHSCN.R:883-893), exact (integer accumulation, 128-bit for the
+ * squares, converted once): out9 = { sum alleleB, sum totalcounts, rows } over the A-Hom rows (infloherror, :895-899), then
+ * { rows, sum m, sum n, sum m^2, sum m n, sum n^2 } over the rows in state selA|selB with m = alleleB, n = totalcounts
+ * (tarones_Z, :609-616: p = sum m / sum n, S = (sum m^2 - 2 p sum mn + p^2 sum n^2) / (p (1 - p)),
+ * Z = (S - sum n) / sqrt(2 (sum n^2 - sum n))); ab_hist_out[A*n_states + B] as in sgb_pass_stats. */
+SGB_API int sgb_pass_stats2(int64_t N, const int32_t* n, const int32_t* x, const void* cn, int32_t cn_itemsize,
+                            const uint8_t* path, const uint8_t* row_keep, int32_t n_states, int32_t selA, int32_t selB,
+                            double* out9, int64_t* ab_hist_out);
+/* qc_per_cell's average_distance (R/util.R:667-691): per cell, over its allele-specific states with more than 10 bins,
+ * |B/(A+B) - median(BAF)| weighted by n / (rows outside state 0|0).  cell_of_row: cell code of every row.
+ * avg_out[n_cells]: NaN for a cell without a qualifying state (the reference has no row for it). */
+SGB_API int sgb_qc_per_cell(int64_t N, const int32_t* n, const int32_t* x, const void* cn, int32_t cn_itemsize,
+                            const uint8_t* path, const int32_t* cell_of_row, int32_t n_cells, double* avg_out);
+/* fix_assignments (R/callHSCN.R:1072-1286), as written: singleton bins take their successor's B (the reference's
+ * LLprev := fifelse(is.na(LLprev), 0, LLafter) makes the likelihood comparison always true), then per run of equal A|B
+ * (inside a sequence for binomial, across the table for beta-binomial, as the reference's rleid calls differ) the
+ * densities of the run's allele totals under B/state and A/state decide whether A and B swap.  Densities are dbinom /
+ * dbetabinom values (not logs), so both underflow to 0 -- and nothing changes -- for long runs, as in R. */
+SGB_API int sgb_fix_assignments(int64_t N, const int32_t* state, const int32_t* A, const int32_t* B, const int32_t* alleleA,
+                                const int32_t* alleleB, int64_t nseg, const int64_t* seg_off, double loherror,
+                                int32_t likelihood, double rho, int32_t* A_out, int32_t* B_out);
+
 /* ---- diagnostics -------------------------------------------------------------------------- */
 /* Evaluate one deterministic math primitive on the device (tests pin device bits == host bits).
  * fn: 0 exp, 1 log, 2 log1p on [0,1], 3 log1p, 4 lgamma, 5 logspace_add(in, in2), 6 log(in!) */

@@ -183,3 +183,17 @@ def postprocess(cn, path):
     lib().orc_postprocess(ctypes.c_int64(N), _p(cn), _p(path), _p(A), _p(B), _p(smin), _p(loh), _p(phase), _p(sp),
                           _p(baf))
     return dict(A=A, B=B, state_min=smin, LOH=loh, phase=phase, state_phase=sp, state_BAF=baf)
+
+
+def fix_assignments(state, A, B, alleleA, alleleB, seg_off, loherror, likelihood="binomial", rho=0.0, math=MATH_DET):
+    """fix_assignments as written (R/callHSCN.R:1072-1286); returns (A, B) after both blocks"""
+    state, A, B, alleleA, alleleB = (_i32(v) for v in (state, A, B, alleleA, alleleB))
+    seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+    N = state.size
+    Ao = np.zeros(N, np.int32); Bo = np.zeros(N, np.int32)
+    rc = lib().orc_fix_assignments(ctypes.c_int64(N), _p(state), _p(A), _p(B), _p(alleleA), _p(alleleB),
+                                   ctypes.c_int64(seg_off.size - 1), _p(seg_off), ctypes.c_double(loherror),
+                                   int(likelihood == "betabinomial" and rho > 0), ctypes.c_double(rho), int(math), _p(Ao), _p(Bo))
+    if rc:
+        raise MemoryError("orc_fix_assignments")
+    return Ao, Bo

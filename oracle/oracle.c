@@ -443,3 +443,102 @@ void orc_postprocess(int64_t N, const int32_t* cn, const uint8_t* path, int32_t*
         state_baf[i] = baf;
     }
 }
+
+/* ------------------------------------------------------------------ fix_assignments (R/callHSCN.R:1072-1286), as written */
+/* dbinom(k, k + nk, p) / VGAM::dbetabinom(k, k + nk, p, rho) as DENSITIES (the reference does not pass log = TRUE).
+ * The det flavour exponentiates with sgb_exp, which flushes below exp(-708) to 0 (R keeps subnormals down to exp(-745)). */
+static double orc_fix_density(int64_t k, int64_t nk, double p, int lik_bb, double rho, int math)
+{
+    orc_params P;
+    memset(&P, 0, sizeof P);
+    P.likelihood = lik_bb ? ORC_LIK_BETABINOMIAL : ORC_LIK_BINOMIAL;
+    P.rho = rho;
+    double l = orc_density(k, k + nk, p, &P, math);
+    if (l != l) return l;
+    return math == ORC_MATH_DET ? sgb_exp(l, ORC_ET) : exp(l);
+}
+static double orc_fix_p(int num, int state, double loh)
+{
+    double p = (double)num / (double)state;
+    if (p != p) p = 0.0;                    /* ifelse(is.nan(B / state), 0.0, B / state)   :1083 */
+    if (p == 0.0) p = p + loh;              /* :1087-1091 */
+    if (p == 1.0) p = p - loh;              /* :1092-1096 */
+    return p;
+}
+static void orc_fix_clamp(int state, int smin, int32_t* A, int32_t* B)
+{
+    int a = state - smin, b = smin;         /* :1129-1134 */
+    if (b < 0) b = 0;
+    if (a < 0) a = 0;
+    if (b > state) b = state;
+    if (a > state) a = state;
+    *A = a; *B = b;
+}
+/* rows in table order; seg_off delimits the (cell_id, chr) groups of the rleid(..., by = .(cell_id, chr)) calls */
+int orc_fix_assignments(int64_t N, const int32_t* state, const int32_t* A, const int32_t* B, const int32_t* alleleA,
+                        const int32_t* alleleB, int64_t nseg, const int64_t* seg_off, double loherror, int lik_bb, double rho,
+                        int math, int32_t* A_out, int32_t* B_out)
+{
+    if (N <= 0) return 0;
+    uint8_t* head = (uint8_t*)calloc((size_t)N + 1, 1);
+    int32_t* A1 = (int32_t*)malloc(sizeof(int32_t) * N);
+    int32_t* B1 = (int32_t*)malloc(sizeof(int32_t) * N);
+    if (!head || !A1 || !B1) { free(head); free(A1); free(B1); return -1; }
+    for (int64_t s = 0; s < nseg; s++) if (seg_off[s + 1] > seg_off[s]) head[seg_off[s]] = 1;
+    head[N] = 1;
+    /* ---- first block (:1074-1145 binomial, :1196-1262 beta-binomial): singletons */
+    for (int64_t i = 0; i < N; i++) {
+        /* nbins := .N by (rlid, chr, cell_id), rlid := rleid(state_AS_phased) by (cell_id, chr) */
+        int same_prev = !head[i] && A[i - 1] == A[i] && B[i - 1] == B[i];
+        int same_next = !head[i + 1] && A[i + 1] == A[i] && B[i + 1] == B[i];
+        int nbins1 = !same_prev && !same_next;
+        int Bprev = i > 0 ? B[i - 1] : 0;                  /* shift(B, fill = 0): over the whole table */
+        int Bafter = i + 1 < N ? B[i + 1] : 0;             /* shift(B, fill = 0, type = "lead") */
+        double pBafter = orc_fix_p(Bafter, state[i], loherror), pBprev = orc_fix_p(Bprev, state[i], loherror);
+        double LLafter = orc_fix_density(alleleA[i], alleleB[i], pBafter, lik_bb, rho, math);
+        if (LLafter != LLafter) LLafter = 0.0;             /* fifelse(is.na(LLafter), 0, LLafter) */
+        double LLprev = orc_fix_density(alleleA[i], alleleB[i], pBprev, lik_bb, rho, math);
+        LLprev = (LLprev != LLprev) ? 0.0 : LLafter;       /* fifelse(is.na(LLprev), 0, LLafter)   [sic, :1114] */
+        int smin = (nbins1 && LLafter < LLprev) ? Bprev : B[i];      /* :1115-1119 */
+        smin = (nbins1 && LLafter >= LLprev) ? Bafter : B[i];        /* :1120-1124 overwrites it */
+        orc_fix_clamp(state[i], smin, &A1[i], &B1[i]);
+    }
+    /* ---- second block (:1147-1194 binomial: rleid by (cell_id, chr); :1264-1280 beta-binomial: rleid over the table) */
+    for (int64_t i = 0; i < N;) {
+        int64_t j = i;
+        int64_t ta = 0, tb = 0;
+        while (j < N && A1[j] == A1[i] && B1[j] == B1[i] && (j == i || lik_bb || !head[j])) { ta += alleleA[j]; tb += alleleB[j]; j++; }
+        for (int64_t r = i; r < j; r++) {
+            double pB = orc_fix_p(B1[r], state[r], loherror), pA = orc_fix_p(A1[r], state[r], loherror);
+            double LLassigned = orc_fix_density(ta, tb, pB, lik_bb, rho, math);
+            double LLother = orc_fix_density(ta, tb, pA, lik_bb, rho, math);
+            int smin = (LLother < LLassigned) ? A1[r] : B1[r];       /* fifelse(LLother < LLassigned, A, B) */
+            orc_fix_clamp(state[r], smin, &A_out[r], &B_out[r]);
+        }
+        i = j;
+    }
+    free(head); free(A1); free(B1);
+    return 0;
+}
+/* margin report for the second block: |LLother - LLassigned| relative to their maximum, per row (0 when both are 0) */
+int orc_fix_margins(int64_t N, const int32_t* state, const int32_t* A1, const int32_t* B1, const int32_t* alleleA,
+                    const int32_t* alleleB, int64_t nseg, const int64_t* seg_off, double loherror, int lik_bb, double rho,
+                    int math, double* margin_out)
+{
+    uint8_t* head = (uint8_t*)calloc((size_t)N + 1, 1);
+    if (!head) return -1;
+    for (int64_t s = 0; s < nseg; s++) if (seg_off[s + 1] > seg_off[s]) head[seg_off[s]] = 1;
+    for (int64_t i = 0; i < N;) {
+        int64_t j = i, ta = 0, tb = 0;
+        while (j < N && A1[j] == A1[i] && B1[j] == B1[i] && (j == i || lik_bb || !head[j])) { ta += alleleA[j]; tb += alleleB[j]; j++; }
+        for (int64_t r = i; r < j; r++) {
+            double la = orc_fix_density(ta, tb, orc_fix_p(B1[r], state[r], loherror), lik_bb, rho, math);
+            double lo = orc_fix_density(ta, tb, orc_fix_p(A1[r], state[r], loherror), lik_bb, rho, math);
+            double mx = fmax(la, lo);
+            margin_out[r] = mx > 0.0 ? fabs(la - lo) / mx : 0.0;
+        }
+        i = j;
+    }
+    free(head);
+    return 0;
+}

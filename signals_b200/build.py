@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libsignals_b200.so")
-SOURCES = ["hmm_kernels.cu", "split_kernels.cu", "capi.cu", "noalloc.cu"]
+SOURCES = ["hmm_kernels.cu", "split_kernels.cu", "table_kernels.cu", "capi.cu", "noalloc.cu"]
 HEADERS = ["sgb_math.h", "sgb_tables.h", "hmm_core.cuh", "kernels.h", "sgb_async.cuh", os.path.join("..", "..", "include", "signals_b200.h")]
 
 NVCC_FLAGS = [

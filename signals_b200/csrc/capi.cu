@@ -341,6 +341,8 @@ const char* err_bits_text(int bits)
     if (bits & SGB_ERR_BAD_CN) return "copy-number state outside 0..255";
     if (bits & SGB_ERR_NOT_INTEGER) return "a numeric (double) column holds NA / NaN or a value that is not an integer";
     if (bits & SGB_ERR_INTERNAL) return "internal error: emission tile bound exceeded";
+    if (bits & SGB_ERR_BAD_KEY) return "cell / chromosome code outside its declared range, negative start, or state outside 0..255";
+    if (bits & SGB_ERR_KEY_CONFLICT) return "rows with the same (cell, chr, start) disagree on `state`";
     return "unknown input error";
 }
 
@@ -1204,6 +1206,184 @@ int sgb_pass_stats(int64_t N, const int32_t* n, const int32_t* x, const void* cn
     SGB_CUDA(cudaMemcpy(h.data(), d_out, nout * 8, cudaMemcpyDeviceToHost));
     for (int i = 0; i < 3; i++) sums_out[i] = (int64_t)h[(size_t)i];
     for (size_t i = 0; i < (size_t)S * S; i++) ab_hist_out[i] = (int64_t)h[3 + i];
+    return 0;
+}
+
+// ---------------------------------------------------------------- table passes
+static int table_run(int do_combine, int64_t N, const int32_t* cell, const int32_t* chr, const int32_t* start, const int32_t* state,
+                     const int32_t* a, const int32_t* b, const int32_t* tot, int32_t n_cells, int32_t n_chr, double filtern,
+                     int32_t minbins, int32_t minbinschr, int32_t chrX, int64_t* nrow_out, int32_t* o_first, int32_t* o_cell, int32_t* o_chr,
+                     int32_t* o_start, int32_t* o_state, int32_t* o_a, int32_t* o_b, int32_t* o_n, int64_t* nseg_out, int64_t* seg_off_out)
+{
+    if (N < 0) return fail("negative size");
+    if (N >= (1ll << 31)) return fail("tables of 2^31 rows or more are not supported");
+    if (n_cells < 1 || n_chr < 1 || n_chr > 256) return fail("n_cells must be >= 1 and n_chr in 1..256");
+    if (!nrow_out || !nseg_out || !seg_off_out) return fail("NULL pointer");
+    *nrow_out = 0; *nseg_out = 0; seg_off_out[0] = 0;
+    if (N == 0) return 0;
+    if (!cell || !chr || !start || !o_first) return fail("NULL pointer");
+    if (do_combine && (!state || !a || !b || !tot || !o_cell || !o_chr || !o_start || !o_state || !o_a || !o_b || !o_n)) return fail("NULL pointer");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    cudaStream_t st = C->main;
+    const size_t n4 = ((size_t)N * 4 + 255) & ~(size_t)255;
+    const int ncol_in = do_combine ? 7 : 3, ncol_out = do_combine ? 8 : 1;
+    const size_t seg_bytes = ((size_t)N + 1) * 8;
+    if (C->scratch_a.reserve(n4 * (ncol_in + ncol_out) + seg_bytes + 512)) return 1;
+    if (C->scratch_b.reserve(sgbk_table_scratch_bytes(N, n_cells, n_chr))) return 1;
+    char* base = (char*)C->scratch_a.p;
+    const int32_t* hin[7] = {cell, chr, start, state, a, b, tot};
+    int32_t* din[7] = {nullptr};
+    for (int k = 0; k < ncol_in; k++) {
+        din[k] = (int32_t*)(base + n4 * k);
+        SGB_CUDA(cudaMemcpyAsync(din[k], hin[k], (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    }
+    int32_t* dout[8];
+    for (int k = 0; k < ncol_out; k++) dout[k] = (int32_t*)(base + n4 * (ncol_in + k));
+    long long* dseg = (long long*)(base + n4 * (ncol_in + ncol_out));
+    SGB_CUDA(cudaMemsetAsync(C->d_err, 0, sizeof(int), st));
+    long long counts[2] = {0, 0};
+    SGB_CUDA(sgbk_table(N, din[0], din[1], din[2], din[3], din[4], din[5], din[6], n_cells, n_chr, do_combine, filtern, minbins,
+                        minbinschr, chrX, C->scratch_b.p, dout[0], do_combine ? dout[1] : nullptr, do_combine ? dout[2] : nullptr,
+                        do_combine ? dout[3] : nullptr, do_combine ? dout[4] : nullptr, do_combine ? dout[5] : nullptr,
+                        do_combine ? dout[6] : nullptr, do_combine ? dout[7] : nullptr, dseg, counts, C->d_err, st));
+    int bits = 0;
+    SGB_CUDA(cudaMemcpy(&bits, C->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (bits) return fail(err_bits_text(bits));
+    int32_t* hout[8] = {o_first, o_cell, o_chr, o_start, o_state, o_a, o_b, o_n};
+    for (int k = 0; k < ncol_out; k++)
+        if (counts[0] > 0) SGB_CUDA(cudaMemcpyAsync(hout[k], dout[k], (size_t)counts[0] * 4, cudaMemcpyDeviceToHost, st));
+    SGB_CUDA(cudaMemcpyAsync(seg_off_out, dseg, ((size_t)counts[1] + 1) * 8, cudaMemcpyDeviceToHost, st));
+    SGB_CUDA(cudaStreamSynchronize(st));
+    if (counts[1] == 0) seg_off_out[0] = 0;
+    *nrow_out = counts[0]; *nseg_out = counts[1];
+    return 0;
+}
+
+int sgb_table_order(int64_t N, const int32_t* cell, const int32_t* chr, const int32_t* start, int32_t n_cells, int32_t n_chr,
+                    int32_t* perm_out, int64_t* nseg_out, int64_t* seg_off_out)
+{
+    int64_t nrow = 0;
+    return table_run(0, N, cell, chr, start, nullptr, nullptr, nullptr, nullptr, n_cells, n_chr, 0.0, 0, 0, -1, &nrow, perm_out, nullptr,
+                     nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nseg_out, seg_off_out);
+}
+
+int sgb_combine_bafcn(int64_t N, const int32_t* cell, const int32_t* chr, const int32_t* start, const int32_t* state,
+                      const int32_t* alleleA, const int32_t* alleleB, const int32_t* totalcounts, int32_t n_cells, int32_t n_chr,
+                      double filtern, int32_t minbins, int32_t minbinschr, int32_t chrX_code, int64_t* nrow_out, int32_t* first_row_out,
+                      int32_t* cell_out, int32_t* chr_out, int32_t* start_out, int32_t* state_out, int32_t* alleleA_out,
+                      int32_t* alleleB_out, int32_t* totalcounts_out, int64_t* nseg_out, int64_t* seg_off_out)
+{
+    if (filtern != filtern) return fail("NaN parameter");
+    return table_run(1, N, cell, chr, start, state, alleleA, alleleB, totalcounts, n_cells, n_chr, filtern, minbins, minbinschr, chrX_code,
+                     nrow_out, first_row_out, cell_out, chr_out, start_out, state_out, alleleA_out, alleleB_out, totalcounts_out, nseg_out,
+                     seg_off_out);
+}
+
+int sgb_pass_stats2(int64_t N, const int32_t* n, const int32_t* x, const void* cn, int32_t cn_itemsize, const uint8_t* path,
+                    const uint8_t* row_keep, int32_t n_states, int32_t selA, int32_t selB, double* out9, int64_t* ab_hist_out)
+{
+    if (N < 0) return fail("negative size");
+    if (cn_itemsize != 1 && cn_itemsize != 4) return fail("cn_itemsize must be 1 (uint8) or 4 (int32)");
+    if (n_states < 1 || n_states > SGB_MAX_STATES) return fail("n_states (maxCN+1) must be in 1..32");
+    if (!out9 || !ab_hist_out) return fail("NULL pointer");
+    const int S = n_states;
+    for (int i = 0; i < 9; i++) out9[i] = 0.0;
+    for (int i = 0; i < S * S; i++) ab_hist_out[i] = 0;
+    if (N == 0) return 0;
+    if (!n || !x || !cn || !path) return fail("NULL pointer");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    cudaStream_t st = C->main;
+    const size_t n4 = ((size_t)N * 4 + 255) & ~(size_t)255, n1 = ((size_t)N + 255) & ~(size_t)255;
+    const int nb = sgbk_pass_stats2_blocks(N);
+    if (C->scratch_a.reserve(3 * n4 + 2 * n1 + 512) || C->scratch_c.reserve(((size_t)nb * 9 + 16) * 8 + (size_t)S * S * 8 + 512)) return 1;
+    char* base = (char*)C->scratch_a.p;
+    int32_t* d_n = (int32_t*)base; int32_t* d_x = (int32_t*)(base + n4); char* d_cn = base + 2 * n4;
+    uint8_t* d_path = (uint8_t*)(base + 3 * n4); uint8_t* d_keep = d_path + n1;
+    double* d_part = (double*)C->scratch_c.p; double* d_out = d_part + (size_t)nb * 9;
+    unsigned long long* d_hist = (unsigned long long*)(d_out + 16);
+    SGB_CUDA(cudaMemcpyAsync(d_n, n, (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(cudaMemcpyAsync(d_x, x, (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(cudaMemcpyAsync(d_cn, cn, (size_t)N * cn_itemsize, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(cudaMemcpyAsync(d_path, path, (size_t)N, cudaMemcpyHostToDevice, st));
+    if (row_keep) SGB_CUDA(cudaMemcpyAsync(d_keep, row_keep, (size_t)N, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(sgbk_pass_stats2(d_n, d_x, d_cn, cn_itemsize, d_path, row_keep ? d_keep : nullptr, N, S, selA, selB, d_part, d_out, d_hist, st));
+    std::vector<unsigned long long> h((size_t)S * S);
+    SGB_CUDA(cudaMemcpyAsync(out9, d_out, 9 * 8, cudaMemcpyDeviceToHost, st));
+    SGB_CUDA(cudaMemcpyAsync(h.data(), d_hist, (size_t)S * S * 8, cudaMemcpyDeviceToHost, st));
+    SGB_CUDA(cudaStreamSynchronize(st));
+    for (int i = 0; i < S * S; i++) ab_hist_out[i] = (int64_t)h[(size_t)i];
+    return 0;
+}
+
+int sgb_qc_per_cell(int64_t N, const int32_t* n, const int32_t* x, const void* cn, int32_t cn_itemsize, const uint8_t* path,
+                    const int32_t* cell_of_row, int32_t n_cells, double* avg_out)
+{
+    if (N < 0 || n_cells < 0) return fail("negative size");
+    if (N >= (1ll << 31)) return fail("tables of 2^31 rows or more are not supported");
+    if (cn_itemsize != 1 && cn_itemsize != 4) return fail("cn_itemsize must be 1 (uint8) or 4 (int32)");
+    if (n_cells == 0) return 0;
+    if (!avg_out) return fail("NULL pointer");
+    if (N > 0 && (!n || !x || !cn || !path || !cell_of_row)) return fail("NULL pointer");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    cudaStream_t st = C->main;
+    const size_t n4 = ((size_t)N * 4 + 255) & ~(size_t)255, n1 = ((size_t)N + 255) & ~(size_t)255;
+    if (C->scratch_a.reserve(4 * n4 + n1 + (size_t)n_cells * 8 + 1024) || C->scratch_b.reserve(sgbk_qc_scratch_bytes(N))) return 1;
+    char* base = (char*)C->scratch_a.p;
+    int32_t* d_n = (int32_t*)base; int32_t* d_x = (int32_t*)(base + n4); char* d_cn = base + 2 * n4;
+    int32_t* d_cell = (int32_t*)(base + 3 * n4); uint8_t* d_path = (uint8_t*)(base + 4 * n4);
+    double* d_avg = (double*)(base + 4 * n4 + n1);
+    if (N > 0) {
+        SGB_CUDA(cudaMemcpyAsync(d_n, n, (size_t)N * 4, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(d_x, x, (size_t)N * 4, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(d_cn, cn, (size_t)N * cn_itemsize, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(d_cell, cell_of_row, (size_t)N * 4, cudaMemcpyHostToDevice, st));
+        SGB_CUDA(cudaMemcpyAsync(d_path, path, (size_t)N, cudaMemcpyHostToDevice, st));
+    }
+    SGB_CUDA(cudaMemsetAsync(C->d_err, 0, sizeof(int), st));
+    SGB_CUDA(sgbk_qc_per_cell(d_n, d_x, d_cn, cn_itemsize, d_path, d_cell, N, n_cells, C->scratch_b.p, d_avg, C->d_err, st));
+    SGB_CUDA(cudaMemcpyAsync(avg_out, d_avg, (size_t)n_cells * 8, cudaMemcpyDeviceToHost, st));
+    int bits = 0;
+    SGB_CUDA(cudaMemcpy(&bits, C->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    SGB_CUDA(cudaStreamSynchronize(st));
+    if (bits) return fail(err_bits_text(bits));
+    return 0;
+}
+
+int sgb_fix_assignments(int64_t N, const int32_t* state, const int32_t* A, const int32_t* B, const int32_t* alleleA,
+                        const int32_t* alleleB, int64_t nseg, const int64_t* seg_off, double loherror, int32_t likelihood, double rho,
+                        int32_t* A_out, int32_t* B_out)
+{
+    if (N < 0 || nseg < 0) return fail("negative size");
+    if (likelihood != SGB_LIK_BINOMIAL && likelihood != SGB_LIK_BETABINOMIAL) return fail("Likelihood model must be one of binomial or betabinomial");
+    if (loherror != loherror || rho != rho) return fail("NaN parameter");
+    if (N == 0) return 0;
+    if (!state || !A || !B || !alleleA || !alleleB || !seg_off || !A_out || !B_out) return fail("NULL pointer");
+    if (nseg < 1 || seg_off[0] != 0 || seg_off[nseg] != N) return fail("seg_off must cover rows 0..N");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    cudaStream_t st = C->main;
+    const size_t n4 = ((size_t)N * 4 + 255) & ~(size_t)255, n1 = ((size_t)N + 255) & ~(size_t)255;
+    if (C->scratch_a.reserve(9 * n4 + n1 + 512)) return 1;
+    std::vector<uint8_t> head((size_t)N, 0);
+    for (int64_t s = 0; s < nseg; s++) {
+        if (seg_off[s + 1] < seg_off[s]) return fail("seg_off must be non-decreasing");
+        if (seg_off[s] < N && seg_off[s + 1] > seg_off[s]) head[(size_t)seg_off[s]] = 1;
+    }
+    char* base = (char*)C->scratch_a.p;
+    int32_t* d[9];
+    for (int k = 0; k < 9; k++) d[k] = (int32_t*)(base + n4 * k);
+    uint8_t* d_head = (uint8_t*)(base + 9 * n4);
+    const int32_t* hin[5] = {state, A, B, alleleA, alleleB};
+    for (int k = 0; k < 5; k++) SGB_CUDA(cudaMemcpyAsync(d[k], hin[k], (size_t)N * 4, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(cudaMemcpyAsync(d_head, head.data(), (size_t)N, cudaMemcpyHostToDevice, st));
+    SGB_CUDA(sgbk_fix_assignments(d[0], d[1], d[2], d[3], d[4], d_head, N, loherror, likelihood == SGB_LIK_BETABINOMIAL && rho > 0.0, rho,
+                                  d[5], d[6], d[7], d[8], st));
+    SGB_CUDA(cudaMemcpyAsync(A_out, d[7], (size_t)N * 4, cudaMemcpyDeviceToHost, st));
+    SGB_CUDA(cudaMemcpyAsync(B_out, d[8], (size_t)N * 4, cudaMemcpyDeviceToHost, st));
+    SGB_CUDA(cudaStreamSynchronize(st));
     return 0;
 }
 

@@ -46,6 +46,8 @@ struct SgbModelArgs {
 #define SGB_ERR_BAD_CN 4
 #define SGB_ERR_NOT_INTEGER 8          // a double-typed column holds NaN or a non-integer value
 #define SGB_ERR_INTERNAL 16            // a scratch-size bound was violated (a bug, never an input problem)
+#define SGB_ERR_BAD_KEY 32             // a cell / chromosome code outside its declared range, or a negative start
+#define SGB_ERR_KEY_CONFLICT 64        // rows with the same (cell, chr, start) disagree on `state`
 
 cudaError_t sgbk_setup(SgbDevTables* d_tabs, const SgbModelArgs& m, double eps, double Abias, double stp,
                        cudaStream_t st);
@@ -125,3 +127,21 @@ cudaError_t sgbk_split_decode(const SgbPlanDev& plan, long long nseq, const SgbC
                               cudaStream_t st, cudaEvent_t ev_prep, cudaEvent_t ev_mid);
 void sgb_internal_set_error(const char* msg);      // sets the calling thread's sgb_last_error() text (capi.cu)
 cudaError_t sgbk_fp64_peak(int iters, int sm_count, cudaStream_t st, double* tflops);
+
+// ---- table passes (table_kernels.cu): sort / segment, combineBAFCN reduce, between-pass sums, qc_per_cell, fix_assignments
+size_t sgbk_table_scratch_bytes(long long n, int ncell, int nchr);
+cudaError_t sgbk_table(long long n, const int32_t* d_cell, const int32_t* d_chr, const int32_t* d_start, const int32_t* d_state,
+                       const int32_t* d_a, const int32_t* d_b, const int32_t* d_n, int ncell, int nchr, int do_combine, double filtern,
+                       int minbins, int minbinschr, int chrX, void* d_scratch, int32_t* o_first, int32_t* o_cell, int32_t* o_chr,
+                       int32_t* o_start, int32_t* o_state, int32_t* o_a, int32_t* o_b, int32_t* o_n, long long* o_seg_off,
+                       long long* h_counts, int* d_err, cudaStream_t st);
+int sgbk_pass_stats2_blocks(long long N);
+cudaError_t sgbk_pass_stats2(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize, const uint8_t* d_path,
+                             const uint8_t* d_rowkeep, long long N, int S, int selA, int selB, double* d_part, double* d_out9,
+                             unsigned long long* d_hist, cudaStream_t st);
+size_t sgbk_qc_scratch_bytes(long long n);
+cudaError_t sgbk_qc_per_cell(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize, const uint8_t* d_path,
+                             const int32_t* d_cell_of_row, long long N, int ncell, void* d_scratch, double* d_avg, int* d_err, cudaStream_t st);
+cudaError_t sgbk_fix_assignments(const int32_t* d_state, const int32_t* d_A, const int32_t* d_B, const int32_t* d_alleleA,
+                                 const int32_t* d_alleleB, const uint8_t* d_seqhead, long long N, double loherror, int lik_bb, double rho,
+                                 int32_t* d_A1, int32_t* d_B1, int32_t* d_A2, int32_t* d_B2, cudaStream_t st);

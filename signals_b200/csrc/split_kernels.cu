@@ -408,6 +408,9 @@ struct SgbRecurArgs {
 
 #define SGB_RECUR_WARPS 4               // per CTA when at most 3 planes (maxCN <= 11); 2 for the 8-plane kernel
 #define SGB_RECUR_NWARPS(maxnpl) ((maxnpl) <= 3 ? SGB_RECUR_WARPS : 2)
+#ifndef SGB_RECUR_NARROW
+#define SGB_RECUR_NARROW 1            // per bin, run the step over the planes that are live in this or the previous bin only
+#endif
 #define SGB_RECUR_MAXDEPTH 16            // ring slots per warp: one mbarrier each, phases kept in a bit mask
 
 // One group of 32 sequences with NPL planes.  Chunk c of its tile (4 bins, 4 NPL KB, contiguous) is one 1-D TMA bulk copy
@@ -437,27 +440,7 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
     SgbSeqState<DD ? 1 : NL> st;
     const int Seff = A.S < NL ? A.S : NL;
     const double tr_self = sp.tr_self, tr_off = sp.tr_off, init = sp.init;
-    // Decoded states leave as aligned 32-bit words where the sequence covers a whole word of state_out (4 bins per
-    // store instead of 4 one-byte stores, each of which costs a sector operation in L1), single bytes at its two ends.
-    uint8_t* const out = A.state_out;
-    const long long kb = (long long)((unsigned long long)out & 3ull);      // state_out itself need not be word-aligned
-    const long long kfull = (ostart + kb + 3) & ~3ll;      // first word-aligned position (in address units) of this sequence
-    unsigned acc = 0;
-    auto put = [&](long long k, int v) {                   // state of row k (called for consecutive k)
-        const long long kk = k + kb;
-        if (kk < kfull) { out[k] = (uint8_t)v; return; }
-        acc |= (unsigned)v << (8 * (int)(kk & 3));
-        if ((kk & 3) == 3) { *(unsigned*)(out + k - 3) = acc; acc = 0; }
-    };
-    auto put_flush = [&](long long klast) {                // after the last row: bytes of an unfinished word
-        const long long kk = klast + kb;
-        if (kk < kfull) return;
-        const int pend = (int)((kk + 1) & 3);
-        uint8_t* w = out + (klast - (pend - 1));
-        if (pend >= 1) w[0] = (uint8_t)acc;
-        if (pend >= 2) w[1] = (uint8_t)(acc >> 8);
-        if (pend >= 3) w[2] = (uint8_t)(acc >> 16);
-    };
+    uint8_t* outp = A.state_out + ostart;
     int lp_prev = NPL;                  // live planes of the previous bin (warp-uniform)
     int s = 0;
     for (int c = 0; c < nchunks; c++) {
@@ -479,7 +462,7 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
                 const double2* q = (const double2*)(mine + pos * 32);
                 const double2 v0 = q[0], v1 = q[1];
                 e[4 * p] = v0.x; e[4 * p + 1] = v0.y; e[4 * p + 2] = v1.x; e[4 * p + 3] = v1.y;
-                if (DD && p > 0) {
+                if (SGB_RECUR_NARROW && DD && p > 0) {
                     // a plane whose four emissions are -Inf in every lane is dead for this bin: with the previous bin's
                     // count it bounds the states the step has to touch (their forward values are -Inf and stay so)
                     const unsigned h = (unsigned)__double2hiint(v0.x) & (unsigned)__double2hiint(v0.y) &
@@ -487,7 +470,7 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
                     if (!__all_sync(SGB_FULL, !act || h == 0xfff00000u)) lp = p + 1;
                 }
             }
-            const int nl = DD ? (lp > lp_prev ? lp : lp_prev) : NPL;
+            const int nl = (SGB_RECUR_NARROW && DD) ? (lp > lp_prev ? lp : lp_prev) : NPL;
             lp_prev = lp;
             if (act) {
                 int back = 0;
@@ -502,10 +485,10 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
                     else back = sgb_seq_step_general<NL>(*(SgbSeqState<NL>*)&st, e, Seff, tr_self, tr_off);
                 }
                 if (t == 0) {
-                    if (len == 1) out[ostart] = 0;
+                    if (len == 1) outp[0] = 0;
                 } else {
-                    put(ostart + t - 1, back);
-                    if (t == len - 1) { put(ostart + t, back); put_flush(ostart + t); }
+                    outp[t - 1] = (uint8_t)back;
+                    if (t == len - 1) outp[t] = (uint8_t)back;
                 }
             }
         }
