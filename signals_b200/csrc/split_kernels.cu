@@ -408,9 +408,6 @@ struct SgbRecurArgs {
 
 #define SGB_RECUR_WARPS 4               // per CTA when at most 3 planes (maxCN <= 11); 2 for the 8-plane kernel
 #define SGB_RECUR_NWARPS(maxnpl) ((maxnpl) <= 3 ? SGB_RECUR_WARPS : 2)
-#ifndef SGB_RECUR_NARROW
-#define SGB_RECUR_NARROW 1            // per bin, run the step over the planes that are live in this or the previous bin only
-#endif
 #define SGB_RECUR_MAXDEPTH 16            // ring slots per warp: one mbarrier each, phases kept in a bit mask
 
 // One group of 32 sequences with NPL planes.  Chunk c of its tile (4 bins, 4 NPL KB, contiguous) is one 1-D TMA bulk copy
@@ -441,7 +438,6 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
     const int Seff = A.S < NL ? A.S : NL;
     const double tr_self = sp.tr_self, tr_off = sp.tr_off, init = sp.init;
     uint8_t* outp = A.state_out + ostart;
-    int lp_prev = NPL;                  // live planes of the previous bin (warp-uniform)
     int s = 0;
     for (int c = 0; c < nchunks; c++) {
         sgb_mbar_wait(&bar[s], (phases >> s) & 1u);
@@ -451,34 +447,19 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
 #pragma unroll
         for (int b = 0; b < 4; b++) {
             const int t = 4 * c + b;
-            if (t >= Tmax) break;                                      // warp-uniform
-            const bool act = t < len;
-            double e[NL];
-            int lp = 1;
+            if (t < len) {
+                double e[NL];
 #pragma unroll
-            for (int p = 0; p < NPL; p++) {
-                int pos = b * NPL + p + lrm;        // < 2 RUN
-                pos = pos >= RUN ? pos - RUN : pos;
-                const double2* q = (const double2*)(mine + pos * 32);
-                const double2 v0 = q[0], v1 = q[1];
-                e[4 * p] = v0.x; e[4 * p + 1] = v0.y; e[4 * p + 2] = v1.x; e[4 * p + 3] = v1.y;
-                if (SGB_RECUR_NARROW && DD && p > 0) {
-                    // a plane whose four emissions are -Inf in every lane is dead for this bin: with the previous bin's
-                    // count it bounds the states the step has to touch (their forward values are -Inf and stay so)
-                    const unsigned h = (unsigned)__double2hiint(v0.x) & (unsigned)__double2hiint(v0.y) &
-                                       (unsigned)__double2hiint(v1.x) & (unsigned)__double2hiint(v1.y);
-                    if (!__all_sync(SGB_FULL, !act || h == 0xfff00000u)) lp = p + 1;
+                for (int p = 0; p < NPL; p++) {
+                    int pos = b * NPL + p + lrm;        // < 2 RUN
+                    pos = pos >= RUN ? pos - RUN : pos;
+                    const double2* q = (const double2*)(mine + pos * 32);
+                    const double2 v0 = q[0], v1 = q[1];
+                    e[4 * p] = v0.x; e[4 * p + 1] = v0.y; e[4 * p + 2] = v1.x; e[4 * p + 3] = v1.y;
                 }
-            }
-            const int nl = (SGB_RECUR_NARROW && DD) ? (lp > lp_prev ? lp : lp_prev) : NPL;
-            lp_prev = lp;
-            if (act) {
                 int back = 0;
                 if (DD) {
                     if (t == 0) sgb_seq_init_r<NL>(*(double(*)[NL])T1, e, init, m1);
-                    else if (NPL >= 2 && nl == 1) back = sgb_seq_step_r<4>(*(double(*)[4])T1, *(const double(*)[4])e, m1, tr_self, tr_off);
-                    else if (NPL >= 3 && nl == 2) back = sgb_seq_step_r<8>(*(double(*)[8])T1, *(const double(*)[8])e, m1, tr_self, tr_off);
-                    else if (NPL >= 4 && nl == 3) back = sgb_seq_step_r<12>(*(double(*)[12])T1, *(const double(*)[12])e, m1, tr_self, tr_off);
                     else back = sgb_seq_step_r<NL>(*(double(*)[NL])T1, e, m1, tr_self, tr_off);
                 } else {
                     if (t == 0) sgb_seq_init<NL>(*(SgbSeqState<NL>*)&st, e, Seff, init);
