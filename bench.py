@@ -249,9 +249,12 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         plan.enable_timing(True)
         plans = [plan]
         hdl = None
-        want = os.environ.get("BENCH_GATHER", "p2p")
+        # BENCH_GATHER: "root" (default: what north_star asks for -- every rank pushes its paths to rank 0 only),
+        # "p2p" (all-gather by pushes to every peer), "p2p_serial" (the same without overlap), "nccl" (NCCL all-gather)
+        want = os.environ.get("BENCH_GATHER", "root")
+        to_root = want == "root"
         nbuf = 1 if want == "p2p_serial" else 2
-        if want in ("p2p", "p2p_serial"):
+        if want in ("root", "p2p", "p2p_serial"):
             try:
                 import torch.distributed._symmetric_memory as symm_mem
                 if hasattr(symm_mem, "enable_symm_mem_for_group"):
@@ -262,7 +265,7 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                 gathered_all = symm_mem.empty(nbuf * N * world, dtype=torch.uint8, device=dev)
                 hdl = symm_mem.rendezvous(gathered_all, dist.group.WORLD)
                 peers = [hdl.get_buffer(r, (nbuf * N * world,), torch.uint8) for r in range(world)]
-                gather_mode = "p2p_dma_push" if nbuf == 1 else "p2p_dma_push_pipelined"
+                gather_mode = "p2p_dma_push_to_root_pipelined" if to_root else ("p2p_dma_push" if nbuf == 1 else "p2p_dma_push_pipelined")
             except Exception as ex:          # symmetric memory unavailable: NCCL path below
                 hdl = None
                 sys.stderr.write("symmetric memory unavailable (%s); using NCCL all_gather\n" % ex)
@@ -290,6 +293,8 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                 start.record(here)
             for k in range(1, world):
                 r = (rank + k) % world
+                if to_root and r != 0:
+                    continue
                 st = ([here] + cp_streams)[(k - 1) % n_cp]
                 if st is not here:
                     st.wait_event(start)
@@ -390,12 +395,13 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                cn_dtype=str(cn_host.dtype),
                scratch_bytes=sum(pl.scratch_bytes() for pl in plans), checksum=int(out.to(torch.int64).sum().item()))
     if world > 1:
-        # every rank must hold every rank's paths: compare checksums of the gathered slices with their owners'
+        # the gathering rank(s) must hold every rank's paths: compare checksums of the gathered slices with their owners'
         sums = torch.stack([gathered[r * N: (r + 1) * N].to(torch.int64).sum() for r in range(world)])
         ref = torch.zeros(world, dtype=torch.int64, device=dev)
         ref[rank] = res["checksum"]
         dist.all_reduce(ref)
-        assert torch.equal(sums, ref), "gathered paths differ from the owners' results"
+        if gather_mode != "p2p_dma_push_to_root_pipelined" or rank == 0:
+            assert torch.equal(sums, ref), "gathered paths differ from the owners' results"
 
     if want_e2e:
         lib = _lib.load()
