@@ -253,7 +253,9 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         # "p2p" (all-gather by pushes to every peer), "p2p_serial" (the same without overlap), "nccl" (NCCL all-gather)
         want = os.environ.get("BENCH_GATHER", "root")
         to_root = want == "root"
-        nbuf = 1 if want == "p2p_serial" else 2
+        # gather buffers in rotation: a rank may run up to nbuf steps ahead of the slowest one; the ranks meet at one
+        # symmetric-memory barrier per rotation (before a buffer is reused), not per step, plus one at the very end
+        nbuf = 1 if want == "p2p_serial" else max(2, int(os.environ.get("BENCH_GATHER_BUFS", "4")))
         if want in ("root", "p2p", "p2p_serial"):
             try:
                 import torch.distributed._symmetric_memory as symm_mem
@@ -276,7 +278,7 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         W = N * world
         outs = [gathered_all[b * W + rank * N: b * W + (rank + 1) * N] for b in range(nbuf)] if hdl is not None \
             else [torch.zeros(N, dtype=torch.uint8, device=dev)]
-        side = torch.cuda.Stream(device=dev) if nbuf == 2 else None
+        side = torch.cuda.Stream(device=dev) if nbuf >= 2 else None
         trace = [] if os.environ.get("BENCH_TRACE") == "1" else None       # per-step (decode start, decode end, push end) events
         ev_dec = [torch.cuda.Event() for _ in range(nbuf)]
         ev_push = [None] * nbuf
@@ -286,7 +288,7 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
         n_cp = max(1, min(int(os.environ.get("BENCH_PUSH_STREAMS", "3")), world - 1))
         cp_streams = [torch.cuda.Stream(device=dev) for _ in range(n_cp - 1)]
 
-        def push(b):
+        def push(b, barrier=True):
             here = torch.cuda.current_stream()
             if cp_streams:
                 start = torch.cuda.Event()
@@ -302,7 +304,8 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                     peers[r][b * W + rank * N: b * W + (rank + 1) * N].copy_(outs[b], non_blocking=True)
             for st in cp_streams:
                 here.wait_stream(st)
-            hdl.barrier()
+            if barrier:
+                hdl.barrier()
 
         def step():
             b = step_no[0] % nbuf
@@ -323,15 +326,17 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                 ev_dec[b].record()
                 with torch.cuda.stream(side):
                     side.wait_event(ev_dec[b])
-                    push(b)
+                    push(b, barrier=(b == nbuf - 1))
                     ev_push[b] = torch.cuda.Event(enable_timing=trace is not None)
                     ev_push[b].record()
                 if trace is not None:
                     trace.append((t0, ev_dec[b], ev_push[b]))
 
         def drain():
-            # joins the side stream: every gather issued so far has landed on every rank
+            # joins the side stream: every gather issued so far has landed (one closing barrier over all ranks)
             if side is not None:
+                with torch.cuda.stream(side):
+                    hdl.barrier()
                 torch.cuda.current_stream().wait_stream(side)
 
     for _ in range(max(warmup, 3)):
