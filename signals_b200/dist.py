@@ -42,3 +42,21 @@ def gather_paths(local_paths, sizes, group=None, dst=0):
     dist.all_gather_into_tensor(out, buf, group=group)
     parts = [out[r * maxlen: r * maxlen + int(sizes[r])] for r in range(world)]
     return torch.cat(parts)
+
+
+def allreduce_pass_stats(out9, hist, group=None):
+    """Between-pass sums of a cohort sharded over ranks: every rank holds the sums of its own cells
+    (`table.pass_stats2_arrays`: nine doubles that are exact integers below 2^53, and the A x B histogram); one
+    all-reduce makes them the cohort's -- infloherror (R/callHSCN.R:895-899), tarones_Z (:609-616) and fitBB's modal
+    state (:619) then follow on every rank without gathering a single row.  float64 / int64 sums of exact integers:
+    the result does not depend on the reduction order.  Tensors may live on the GPU (NCCL) or the CPU (gloo)."""
+    import torch
+    import torch.distributed as dist
+    if dist.get_world_size(group) == 1:
+        return out9, hist
+    o = out9 if torch.is_tensor(out9) else torch.as_tensor(out9, dtype=torch.float64)
+    h = hist if torch.is_tensor(hist) else torch.as_tensor(hist, dtype=torch.int64)
+    o = o.clone(); h = h.clone()
+    dist.all_reduce(o, group=group)
+    dist.all_reduce(h, group=group)
+    return o, h

@@ -32,9 +32,30 @@ def _worker(rank, world, port, q):
     local = co.decode_batch(d["n"][r0:r1], d["x"][r0:r1], cn[r0:r1], so[a:b + 1] - r0, P, co.MATH_DET)
     sizes = [int(so[e] - so[s]) for s, e in cuts]
     full = sd.gather_paths(torch.from_numpy(local), sizes)
+    # between-pass sums of the sharded cohort: every rank reduces its own rows (the oracle's table restatement stands in for
+    # sgb_pass_stats2), one all-reduce gives every rank the cohort's sums
+    tab = co.postprocess(cn[r0:r1], local)
+    A, B = tab["A"], tab["B"]
+    ah = (B == 0) & (A > 0); ms = (A == 1) & (B == 1)
+    x_, n_ = d["x"][r0:r1].astype(np.int64), d["n"][r0:r1].astype(np.int64)
+    out9 = np.array([x_[ah].sum(), n_[ah].sum(), ah.sum(), ms.sum(), x_[ms].sum(), n_[ms].sum(), (x_[ms] ** 2).sum(),
+                     (x_[ms] * n_[ms]).sum(), (n_[ms] ** 2).sum()], np.float64)
+    hist = np.zeros((12, 12), np.int64)
+    np.add.at(hist, (A[B > 0], B[B > 0]), 1)
+    o_all, h_all = sd.allreduce_pass_stats(out9, hist)
     if rank == 0:
         ref = co.decode_batch(d["n"], d["x"], cn, so, P, co.MATH_DET)
-        q.put(bool(np.array_equal(full.numpy(), ref)))
+        ok = bool(np.array_equal(full.numpy(), ref))
+        tabr = co.postprocess(cn, ref)
+        Ar, Br = tabr["A"], tabr["B"]
+        ahr = (Br == 0) & (Ar > 0); msr = (Ar == 1) & (Br == 1)
+        xr, nr = d["x"].astype(np.int64), d["n"].astype(np.int64)
+        ref9 = [xr[ahr].sum(), nr[ahr].sum(), ahr.sum(), msr.sum(), xr[msr].sum(), nr[msr].sum(), (xr[msr] ** 2).sum(),
+                (xr[msr] * nr[msr]).sum(), (nr[msr] ** 2).sum()]
+        hr = np.zeros((12, 12), np.int64)
+        np.add.at(hr, (Ar[Br > 0], Br[Br > 0]), 1)
+        ok = ok and o_all.tolist() == [float(v) for v in ref9] and bool(np.array_equal(h_all.numpy(), hr))
+        q.put(ok)
     dist.barrier()
     dist.destroy_process_group()
 
