@@ -381,7 +381,11 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
     if world > 1:
         dist.barrier()
     ms = torch.tensor([elapsed], dtype=torch.float64, device=dev)
+    by_rank = None
     if world > 1:
+        allms = [torch.zeros_like(ms) for _ in range(world)]
+        dist.all_gather(allms, ms)
+        by_rank = [float(v.item()) / steps for v in allms]
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     total_ms = float(ms.item())
     for pl in plans:
@@ -397,7 +401,7 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
     res = dict(ms_per_step=total_ms / steps, value=N * world * steps / (total_ms * 1e-3),
                decode_ms=decode_ms, emit_ms=emit_ms, pack_ms=prep_ms, N=N, gather=gather_mode, staging=stg,
                kernels=KERNELS[stg], launches_per_step=len(KERNELS[stg]), e_bytes=e_bytes, ngroups=ngroups,
-               cn_dtype=str(cn_host.dtype),
+               cn_dtype=str(cn_host.dtype), ms_per_step_by_rank=by_rank,
                scratch_bytes=sum(pl.scratch_bytes() for pl in plans), checksum=int(out.to(torch.int64).sum().item()))
     if world > 1:
         # the gathering rank(s) must hold every rank's paths: compare checksums of the gathered slices with their owners'
@@ -628,7 +632,7 @@ def main():
             "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": main_res["ms_per_step"], "higher_is_better": True,
             "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": config, "clocks": clocks, "e2e": main_res.get("e2e"), "gpu_launches": main_res["launches_per_step"] * a.steps,
-            "gather": main_res["gather"], "gpu_kernels_per_step": main_res["kernels"],
+            "gather": main_res["gather"], "gpu_kernels_per_step": main_res["kernels"], "ms_per_step_by_rank": main_res["ms_per_step_by_rank"],
             "schedule": "split" if split else "fused", "roofline": roofline,
             "scratch_bytes": main_res["scratch_bytes"], "torch_peak_device_bytes": int(torch.cuda.max_memory_allocated())}
 
