@@ -468,7 +468,9 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
     }
     if (loglik_out && !direct_types) return fail("loglik_out needs int32 count columns and uint8 output");
     // the `l` matrix kernel and the chained decode read int32 counts: no narrowing for them
-    const bool narrow_ok = staged && !loglik_out && m.decode == SGB_DECODE_REFERENCE;
+    // (uint16 counts are read by k_emit only: a caller who forces the fused schedule gets int32 staging)
+    const char* sched_env = getenv("SGB_SCHED");
+    const bool narrow_ok = staged && !loglik_out && m.decode == SGB_DECODE_REFERENCE && !(sched_env && !strcmp(sched_env, "fused"));
     if (staged && !C->pool) C->pool.reset(new SgbPool(host_threads_default(share)));
     const int cn_itemsize = H.cn_type == SGB_T_I32 ? 4 : 1;
 
