@@ -63,7 +63,8 @@ __global__ void __launch_bounds__(256) k_split_class(SgbPlanDev plan, long long 
         const int len = plan.len[i];
         const long long o = plan.ostart[i];
         int mx = 0;
-        for (int t = lane; t < len; t += 32) {
+#pragma unroll 4
+        for (int t = lane; t < len; t += 32) {          // (unrolled: the loads of four strides are in flight together)
             const int c = sgb_load_cn(cn, kind, o + t);
             mx = c > mx ? c : mx;
         }
