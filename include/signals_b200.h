@@ -212,6 +212,8 @@ SGB_API int sgb_combine_bafcn(int64_t N, const int32_t* cell, const int32_t* chr
                               int64_t* nrow_out, int32_t* first_row_out, int32_t* cell_out, int32_t* chr_out,
                               int32_t* start_out, int32_t* state_out, int32_t* alleleA_out, int32_t* alleleB_out,
                               int32_t* totalcounts_out, int64_t* nseg_out, int64_t* seg_off_out);
+/* diagnostic: device time (CUDA events, ms) of the kernels of the last sgb_table_order / sgb_combine_bafcn call, copies excluded */
+SGB_API int sgb_table_last_ms(double* ms_out);
 /* All the whole-table sums the drivers need between the two HMM passes, over the rows with row_keep[i] != 0 (NULL = all
  * rows; the cells that pass the first-pass filter, R/callHSCN.R:883-893), exact (integer accumulation, 128-bit for the
  * squares, converted once): out9 = { sum alleleB, sum totalcounts, rows } over the A-Hom rows (infloherror, :895-899), then

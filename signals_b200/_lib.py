@@ -59,6 +59,7 @@ SIGNATURES = {
     "sgb_table_order": (ctypes.c_int, [_i64, _vp, _vp, _vp, _i32, _i32, _vp, ctypes.POINTER(_i64), _vp]),
     "sgb_combine_bafcn": (ctypes.c_int, [_i64] + [_vp] * 7 + [_i32, _i32, _dbl, _i32, _i32, _i32, ctypes.POINTER(_i64)] + [_vp] * 8 +
                           [ctypes.POINTER(_i64), _vp]),
+    "sgb_table_last_ms": (ctypes.c_int, [ctypes.POINTER(_dbl)]),
     "sgb_pass_stats2": (ctypes.c_int, [_i64, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
     "sgb_qc_per_cell": (ctypes.c_int, [_i64, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _vp]),
     "sgb_fix_assignments": (ctypes.c_int, [_i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _dbl, _i32, _dbl, _vp, _vp]),

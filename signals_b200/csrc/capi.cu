@@ -1212,6 +1212,15 @@ int sgb_pass_stats(int64_t N, const int32_t* n, const int32_t* x, const void* cn
 }
 
 // ---------------------------------------------------------------- table passes
+static double g_table_last_ms = 0.0;      // device time of the kernels of the last sgb_table_order / sgb_combine_bafcn call
+
+int sgb_table_last_ms(double* ms_out)
+{
+    if (!ms_out) return fail("NULL pointer");
+    *ms_out = g_table_last_ms;
+    return 0;
+}
+
 static int table_run(int do_combine, int64_t N, const int32_t* cell, const int32_t* chr, const int32_t* start, const int32_t* state,
                      const int32_t* a, const int32_t* b, const int32_t* tot, int32_t n_cells, int32_t n_chr, double filtern,
                      int32_t minbins, int32_t minbinschr, int32_t chrX, int64_t* nrow_out, int32_t* o_first, int32_t* o_cell, int32_t* o_chr,
@@ -1245,10 +1254,21 @@ static int table_run(int do_combine, int64_t N, const int32_t* cell, const int32
     long long* dseg = (long long*)(base + n4 * (ncol_in + ncol_out));
     SGB_CUDA(cudaMemsetAsync(C->d_err, 0, sizeof(int), st));
     long long counts[2] = {0, 0};
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
+    SGB_CUDA(cudaEventCreate(&t0));
+    SGB_CUDA(cudaEventCreate(&t1));
+    SGB_CUDA(cudaEventRecord(t0, st));
     SGB_CUDA(sgbk_table(N, din[0], din[1], din[2], din[3], din[4], din[5], din[6], n_cells, n_chr, do_combine, filtern, minbins,
                         minbinschr, chrX, C->scratch_b.p, dout[0], do_combine ? dout[1] : nullptr, do_combine ? dout[2] : nullptr,
                         do_combine ? dout[3] : nullptr, do_combine ? dout[4] : nullptr, do_combine ? dout[5] : nullptr,
                         do_combine ? dout[6] : nullptr, do_combine ? dout[7] : nullptr, dseg, counts, C->d_err, st));
+    SGB_CUDA(cudaEventRecord(t1, st));
+    SGB_CUDA(cudaEventSynchronize(t1));
+    {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, t0, t1) == cudaSuccess) g_table_last_ms = (double)ms;
+        cudaEventDestroy(t0); cudaEventDestroy(t1);
+    }
     int bits = 0;
     SGB_CUDA(cudaMemcpy(&bits, C->d_err, sizeof(int), cudaMemcpyDeviceToHost));
     if (bits) return fail(err_bits_text(bits));
