@@ -216,14 +216,17 @@ static inline size_t emit_smem_bytes(int S, int lik_bb)
     return d * sizeof(double) + ((size_t)SGB_CN_TABLE * S + SGB_CN_TABLE) * sizeof(int);
 }
 
-// one row of the caller's columns, whatever their element type; returns validation bits
+// one row of the caller's columns, whatever their element type; returns validation bits.  KIND >= 0: the element types
+// are known at compile time (no branches); KIND < 0: taken from in.kind
+template <int KIND>
 __device__ __forceinline__ int sgb_load_row(const SgbColsIn& in, long long row, int& n, int& x, int& cnv)
 {
     int bad = 0;
-    if (in.kind == SGB_IN_U16_U8) {
+    const int kind = KIND >= 0 ? KIND : in.kind;
+    if (kind == SGB_IN_U16_U8) {
         n = (int)__ldg((const uint16_t*)in.n + row); x = (int)__ldg((const uint16_t*)in.x + row);
         cnv = (int)__ldg((const uint8_t*)in.cn + row);
-    } else if (in.kind == SGB_IN_F64) {
+    } else if (kind == SGB_IN_F64) {
         const double dn = __ldg((const double*)in.n + row), dx = __ldg((const double*)in.x + row);
         const double dc = __ldg((const double*)in.cn + row);
         const double lim = (double)(1 << SGB_COUNT_BITS);
@@ -235,7 +238,7 @@ __device__ __forceinline__ int sgb_load_row(const SgbColsIn& in, long long row, 
         n = bad ? 0 : (int)dn; x = bad ? 0 : (int)dx; cnv = bad ? 0 : (int)dc;
     } else {
         n = __ldg((const int32_t*)in.n + row); x = __ldg((const int32_t*)in.x + row);
-        cnv = in.kind == SGB_IN_I32_I32 ? __ldg((const int32_t*)in.cn + row) : (int)__ldg((const uint8_t*)in.cn + row);
+        cnv = kind == SGB_IN_I32_I32 ? __ldg((const int32_t*)in.cn + row) : (int)__ldg((const uint8_t*)in.cn + row);
     }
     // the checks of the fused path: a bad bin is neutralised, the call fails afterwards
     if ((unsigned)(n | x) >> SGB_COUNT_BITS) {
@@ -246,7 +249,7 @@ __device__ __forceinline__ int sgb_load_row(const SgbColsIn& in, long long row, 
     return bad;
 }
 
-template <int MODEL, int LIKBB>
+template <int MODEL, int LIKBB, int KIND>
 __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmitArgs A)
 {
     extern __shared__ __align__(16) double smem[];
@@ -262,10 +265,13 @@ __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmi
     int* sKind = (int*)(sL0 + (LIKBB ? CTS : 0));
     int* sKM = sKind + CTS;                 // per total-CN bit mask of the states on the lean path
     if (threadIdx.x < SGB_CN_TABLE) {
-        unsigned mask = 0;
-        for (int st = 0; st < S; st++)
-            if (A.tabs->kind[threadIdx.x * SGB_MAX_STATES + st] == SGB_KIND_NORMAL) mask |= 1u << st;
-        sKM[threadIdx.x] = (int)mask;
+        // 1 when every live state of total copy number c is an ordinary one (0 < p < 1) and the call's eps / Abias allow the
+        // lean emission: then a bin with this copy number and a count inside the support takes the lean path
+        const int Lc_ = sgb_live_states(MODEL, (int)threadIdx.x, S);
+        int ok = A.tabs->sp.fast_ok;
+        for (int st = 0; st < Lc_; st++)
+            if (A.tabs->kind[threadIdx.x * SGB_MAX_STATES + st] != SGB_KIND_NORMAL) ok = 0;
+        sKM[threadIdx.x] = ok;
     }
     for (int i = threadIdx.x; i < SGB_LTP_LEN; i += blockDim.x) {
         const int pair = i >> 4, w = i & 1;                // (pair, column, word): column = (i >> 1) & 7
@@ -309,14 +315,14 @@ __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmi
         const int lrm = lr % run;
         double* tile = A.W.E + (A.W.g_eoff[g] + (long long)lr * run) * 4;  // + chunk * 128 npl sectors + rotated position
         int n = 0, x = 0, cnv = 0;
-        if (lane < len) bad |= sgb_load_row(A.in, o + lane, n, x, cnv);
+        if (lane < len) bad |= sgb_load_row<KIND>(A.in, o + lane, n, x, cnv);
         for (int t0 = 0; t0 < len; t0 += 32) {
             const int t = t0 + lane;
             const bool act = t < len;
             const int nc = n, xc = x, cc = cnv;
             // next tile's row: in flight while this one is evaluated
             n = 0; x = 0; cnv = 0;
-            if (t + 32 < len) bad |= sgb_load_row(A.in, o + t + 32, n, x, cnv);
+            if (t + 32 < len) bad |= sgb_load_row<KIND>(A.in, o + t + 32, n, x, cnv);
             const int cprime = sgb_cprime(MODEL, cc);
             const int ins = xc <= nc;
             const int L = act ? sgb_live_states(MODEL, cprime, S) : 0;
@@ -337,8 +343,7 @@ __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmi
             // lean path for the whole warp: every live state of every lane's bin is an ordinary one (tabulated total CN,
             // 0 < p < 1, count inside the support, default eps / no Abias) -- the usual case.  Idle lanes ride along on
             // harmless operands.  Otherwise the general per-item function (same bits where both apply).
-            const unsigned needm = L >= 32 ? 0xffffffffu : (1u << L) - 1u;
-            const bool lean = !act || (cprime < SGB_CN_TABLE && ins && sp.fast_ok && ((unsigned)sKM[cprime < SGB_CN_TABLE ? cprime : 0] & needm) == needm);
+            const bool lean = !act || (ins && cprime < SGB_CN_TABLE && sKM[cprime < SGB_CN_TABLE ? cprime : 0]);
             const bool warp_lean = __all_sync(SGB_FULL, lean);
             const bool uniformL = __all_sync(SGB_FULL, L == Lw || !act);
             const int trow = (act && cprime < SGB_CN_TABLE ? cprime : 1) * S;      // idle lanes: any valid row
@@ -579,8 +584,8 @@ static int split_occupancy(K kern, int threads, size_t smem, size_t smem_max, in
     return occ;
 }
 
-template <int MODEL, int LIKBB>
-static cudaError_t launch_emit(const SgbEmitArgs& A, long long nseq, int sm_count, cudaStream_t st)
+template <int MODEL, int LIKBB, int KIND>
+static cudaError_t launch_emit_k(const SgbEmitArgs& A, long long nseq, int sm_count, cudaStream_t st)
 {
     static int cache[64][SGB_MAX_STATES + 1];            // per device and S (the table size depends on S)
     static int flat[64];
@@ -588,14 +593,24 @@ static cudaError_t launch_emit(const SgbEmitArgs& A, long long nseq, int sm_coun
     cudaGetDevice(&dev);
     const size_t smem = emit_smem_bytes(A.S, LIKBB);
     flat[dev & 63] = cache[dev & 63][A.S];
-    const int occ = split_occupancy(k_emit<MODEL, LIKBB>, SGB_EMIT_THREADS, smem, emit_smem_bytes(SGB_MAX_STATES, LIKBB), flat);
+    const int occ = split_occupancy(k_emit<MODEL, LIKBB, KIND>, SGB_EMIT_THREADS, smem, emit_smem_bytes(SGB_MAX_STATES, LIKBB), flat);
     cache[dev & 63][A.S] = occ;
     if (occ < 1) return cudaErrorInvalidConfiguration;
     long long blocks = (nseq + 7) / 8;
     if (blocks > (long long)sm_count * occ) blocks = (long long)sm_count * occ;
     if (blocks < 1) blocks = 1;
-    k_emit<MODEL, LIKBB><<<(unsigned)blocks, SGB_EMIT_THREADS, smem, st>>>(A);
+    k_emit<MODEL, LIKBB, KIND><<<(unsigned)blocks, SGB_EMIT_THREADS, smem, st>>>(A);
     return cudaGetLastError();
+}
+template <int MODEL, int LIKBB>
+static cudaError_t launch_emit(const SgbEmitArgs& A, long long nseq, int sm_count, cudaStream_t st)
+{
+    switch (A.in.kind) {
+    case SGB_IN_I32_U8: return launch_emit_k<MODEL, LIKBB, SGB_IN_I32_U8>(A, nseq, sm_count, st);
+    case SGB_IN_I32_I32: return launch_emit_k<MODEL, LIKBB, SGB_IN_I32_I32>(A, nseq, sm_count, st);
+    case SGB_IN_U16_U8: return launch_emit_k<MODEL, LIKBB, SGB_IN_U16_U8>(A, nseq, sm_count, st);
+    default: return launch_emit_k<MODEL, LIKBB, -1>(A, nseq, sm_count, st);
+    }
 }
 
 template <int MAXNPL>
