@@ -643,6 +643,41 @@ SGB_HD int sgb_seq_step_r(double (&T1)[NL], const double (&e)[NL], double& m1io,
     return back;
 }
 
+// The same step without the tie analysis: the forward column advances exactly as in sgb_seq_step_r and the column-best state
+// i1 is returned; `tie` tells whether the backpointer of i1 may differ from i1 (the best off-diagonal candidate reaches
+// the maximum), in which case the caller has to redo the step with sgb_seq_step_r from the column it started with.
+// Branch-free, so that consecutive steps of an unrolled loop form one basic block and overlap.
+template <int NL>
+SGB_HD int sgb_seq_step_fast(double (&T1)[NL], const double (&e)[NL], double& m1io, double tr_self, double tr_off, bool& tie)
+{
+    const double u1 = sgb_add(m1io, tr_off);
+    double tv[NL];
+    int ti[NL];
+#pragma unroll
+    for (int i = 0; i < NL; i++) {
+        const double td = sgb_add(T1[i], tr_self);
+        T1[i] = sgb_add((td > u1) ? td : u1, e[i]);
+        tv[i] = T1[i]; ti[i] = i;
+    }
+#pragma unroll
+    for (int stride = 1; stride < NL; stride *= 2) {
+#pragma unroll
+        for (int i = 0; i + stride < NL; i += 2 * stride) {
+            const bool gt = tv[i + stride] > tv[i];
+            tv[i] = gt ? tv[i + stride] : tv[i];
+            ti[i] = gt ? ti[i + stride] : ti[i];
+        }
+    }
+    const double m1 = tv[0];
+    const int i1 = ti[0];
+    double ej = e[0];
+#pragma unroll
+    for (int i = 1; i < NL; i++) ej = (i == i1) ? e[i] : ej;
+    tie = (m1 == sgb_add(u1, ej));
+    m1io = m1;
+    return i1;
+}
+
 // number of 4-state planes a sequence whose largest live-state count is L needs; the recursion kernels are compiled
 // for 1, 2, 3, 4, 6 and 8 planes
 SGB_HD int sgb_planes_for(int L)

@@ -29,6 +29,7 @@
 // (sgb_emission_fast*, sgb_emit_item_slow, the max-plus step), hence the same bits.
 #define SGB_ETI(j) ((j) * 16)             // exp table: 16 lane-private columns of doubles
 #define SGB_LTI(i) ((i) * 16)             // log table: 8 lane-private columns of {1/c, log c} pairs
+#include <cstdlib>
 #include "kernels.h"
 #include "sgb_async.cuh"
 
@@ -415,20 +416,32 @@ struct SgbRecurArgs {
 #define SGB_RECUR_WARPS 4               // per CTA when at most 3 planes (maxCN <= 11); 2 for the 8-plane kernel
 #define SGB_RECUR_NWARPS(maxnpl) ((maxnpl) <= 3 ? SGB_RECUR_WARPS : 2)
 #define SGB_RECUR_MAXDEPTH 16            // ring slots per warp: one mbarrier each, phases kept in a bit mask
+// Decoded states are staged per warp as [bin mod 32][sequence] (row stride 33 bytes: both the per-step column write and the
+// per-sequence row read of the flush are spread over the banks) and written out 32 bins of ONE sequence per store
+// instruction -- one or two 32-byte sectors instead of 32 scattered ones (a lane-per-sequence byte store costs the L1 ~64
+// cycles per warp, which with 8 warps per SM was 2/3 of the step).
+#ifndef SGB_FAST_MAXNPL
+#define SGB_FAST_MAXNPL 2
+#endif
+#define SGB_STAGE_STRIDE 33
+#define SGB_STAGE_BYTES (32 * SGB_STAGE_STRIDE + 16)
 
 // One group of 32 sequences with NPL planes.  Chunk c of its tile (4 bins, 4 NPL KB, contiguous) is one 1-D TMA bulk copy
 // into the next slot of the warp's ring, `depth` chunks ahead of the recursion.
 // DD = 1: diagonal-dominant transition (every realistic selftransitionprob), forward column in registers, O(S) step.
 // DD = 0: selftransitionprob below 1/S -- the two-maxima variant, kept out of line so that it does not set the hot
 // path's register count.
-template <int NPL, int DD>
+template <int NPL, int DD, bool STAGED>
 __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbScalars& sp, unsigned char* ring, unsigned long long* bar,
                                               unsigned& phases, int depth, int lane, int Tmax, long long eoff, int len,
-                                              long long ostart)
+                                              long long ostart, unsigned char* stage)
 {
     constexpr int NL = 4 * NPL;
     constexpr int RUN = 4 * NPL;                       // sectors of one sequence inside a chunk
     constexpr unsigned SLOT = NPL * 4096;
+    // the four-step block pays in the throughput regime (measured 0.49 -> 0.44 ms at 10,000 cells); on a latency-bound batch and for
+    // wider groups the one-step-at-a-time body is the faster one (0.164 vs 0.179 ms at 1,000 cells)
+    constexpr bool FAST = DD != 0 && STAGED && NPL <= SGB_FAST_MAXNPL;
     const unsigned char* src = (const unsigned char*)A.W.E + eoff * 32;
     const int nchunks = (Tmax + 3) >> 2;
     auto issue = [&](int c, int s) {
@@ -444,71 +457,152 @@ __device__ __forceinline__ void recur_group_t(const SgbRecurArgs& A, const SgbSc
     const int Seff = A.S < NL ? A.S : NL;
     const double tr_self = sp.tr_self, tr_off = sp.tr_off, init = sp.init;
     uint8_t* outp = A.state_out + ostart;
+    const int lrm = lane % RUN;
+    const unsigned char* mine0 = ring + lane * (RUN * 32);         // this lane's run inside slot 0
+    int lastback = 0;                                              // backpointer found at the sequence's last bin
     int s = 0;
     for (int c = 0; c < nchunks; c++) {
         sgb_mbar_wait(&bar[s], (phases >> s) & 1u);
         phases ^= 1u << s;
-        const unsigned char* mine = ring + s * SLOT + lane * (RUN * 32);
-        const int lrm = lane % RUN;
+        const unsigned char* mine = mine0 + s * SLOT;
+        auto load_e = [&](int b, double (&e)[NL]) {
 #pragma unroll
-        for (int b = 0; b < 4; b++) {
-            const int t = 4 * c + b;
-            if (t < len) {
+            for (int p = 0; p < NPL; p++) {
+                int pos = b * NPL + p + lrm;        // < 2 RUN
+                pos = pos >= RUN ? pos - RUN : pos;
+                const double2 lo = *(const double2*)(mine + pos * 32), hi = *(const double2*)(mine + pos * 32 + 16);
+                e[4 * p] = lo.x; e[4 * p + 1] = lo.y; e[4 * p + 2] = hi.x; e[4 * p + 3] = hi.y;
+            }
+        };
+        if (FAST && c >= 1) {
+            if constexpr (FAST) {
+            // Four ordinary steps as ONE basic block: the branch-free step, lanes past their sequence's end riding along
+            // (stores predicated off).  Steps whose backpointer needs the tie analysis are flagged; the (rare) chunk that has
+            // one is redone from the column it started with by the full step.
+            double T1s[NL];
+#pragma unroll
+            for (int i = 0; i < NL; i++) T1s[i] = T1[i];
+            const double m1s = m1;
+            int back[4];
+            unsigned ties = 0;
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
                 double e[NL];
+                load_e(b, e);
+                bool tie;
+                back[b] = sgb_seq_step_fast<NL>(*(double(*)[NL])T1, e, m1, tr_self, tr_off, tie);
+                ties |= (tie && 4 * c + b < len) ? 1u << b : 0u;
+            }
+            if (__any_sync(SGB_FULL, ties != 0)) {
+                if (ties) {
+                    // this lane redoes its steps up to the last flagged one: the full step where flagged, else the lean one
+                    double m1r = m1s;
+#pragma unroll 1
+                    for (int b = 0; (ties >> b) != 0; b++) {
+                        double e[NL];
+                        load_e(b, e);
+                        if ((ties >> b) & 1u) {
+                            const int bk = sgb_seq_step_r<NL>(T1s, e, m1r, tr_self, tr_off);
+                            back[0] = (b == 0) ? bk : back[0]; back[1] = (b == 1) ? bk : back[1];
+                            back[2] = (b == 2) ? bk : back[2]; back[3] = (b == 3) ? bk : back[3];
+                        } else {
+                            bool tie_;
+                            sgb_seq_step_fast<NL>(T1s, e, m1r, tr_self, tr_off, tie_);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
 #pragma unroll
-                for (int p = 0; p < NPL; p++) {
-                    int pos = b * NPL + p + lrm;        // < 2 RUN
-                    pos = pos >= RUN ? pos - RUN : pos;
-                    const double2* q = (const double2*)(mine + pos * 32);
-                    const double2 v0 = q[0], v1 = q[1];
-                    e[4 * p] = v0.x; e[4 * p + 1] = v0.y; e[4 * p + 2] = v1.x; e[4 * p + 3] = v1.y;
-                }
-                int back = 0;
-                if (DD) {
-                    if (t == 0) sgb_seq_init_r<NL>(*(double(*)[NL])T1, e, init, m1);
-                    else back = sgb_seq_step_r<NL>(*(double(*)[NL])T1, e, m1, tr_self, tr_off);
-                } else {
-                    if (t == 0) sgb_seq_init<NL>(*(SgbSeqState<NL>*)&st, e, Seff, init);
-                    else back = sgb_seq_step_general<NL>(*(SgbSeqState<NL>*)&st, e, Seff, tr_self, tr_off);
-                }
-                if (t == 0) {
-                    if (len == 1) outp[0] = 0;
-                } else {
-                    outp[t - 1] = (uint8_t)back;
-                    if (t == len - 1) outp[t] = (uint8_t)back;
+            for (int b = 0; b < 4; b++) {
+                const int t = 4 * c + b;
+                if (STAGED) stage[(t & 31) * SGB_STAGE_STRIDE + lane] = (unsigned char)back[b];
+                else if (t < len) outp[t - 1] = (uint8_t)back[b];
+                lastback = (t == len - 1) ? back[b] : lastback;
+            }
+            }
+        } else {
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const int t = 4 * c + b;
+                if (t < len) {
+                    double e[NL];
+                    load_e(b, e);
+                    int back = 0;
+                    if (DD) {
+                        if (t == 0) sgb_seq_init_r<NL>(*(double(*)[NL])T1, e, init, m1);
+                        else back = sgb_seq_step_r<NL>(*(double(*)[NL])T1, e, m1, tr_self, tr_off);
+                    } else {
+                        if (t == 0) sgb_seq_init<NL>(*(SgbSeqState<NL>*)&st, e, Seff, init);
+                        else back = sgb_seq_step_general<NL>(*(SgbSeqState<NL>*)&st, e, Seff, tr_self, tr_off);
+                    }
+                    if (STAGED) stage[(t & 31) * SGB_STAGE_STRIDE + lane] = (unsigned char)back;
+                    else if (t > 0) outp[t - 1] = (uint8_t)back;
+                    lastback = (t == len - 1) ? back : lastback;
                 }
             }
         }
         __syncwarp();                       // every lane has read slot s: it can be refilled
         if (c + depth < nchunks) issue(c + depth, s);
+        if (STAGED && ((c & 7) == 7 || c == nchunks - 1)) {
+            // flush: bins t = 32 k + lane of sequence j hold path[t - 1] (the decode rule writes one bin behind)
+            const int t = (c >> 3) * 32 + lane;
+            uint8_t* const outt = A.state_out + (t - 1);
+#pragma unroll
+            for (int j0 = 0; j0 < 32; j0 += 8) {
+                int len_j[8];
+                long long o_j[8];
+                unsigned char v[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) {             // (eight sequences' shuffles and reads in flight together)
+                    len_j[j] = __shfl_sync(SGB_FULL, len, j0 + j);
+                    o_j[j] = __shfl_sync(SGB_FULL, ostart, j0 + j);
+                    v[j] = stage[lane * SGB_STAGE_STRIDE + j0 + j];
+                }
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    if (t >= 1 && t < len_j[j]) outt[o_j[j]] = v[j];
+            }
+            __syncwarp();
+        }
         s = (s + 1 == depth) ? 0 : s + 1;
     }
+    if (len > 0) outp[len - 1] = (uint8_t)lastback;     // path[T-1] = path[T-2]; T == 1: 0 (src/code.cpp:37)
 }
 
-template <int NPL>
+template <int NPL, bool STAGED>
 __device__ __noinline__ void recur_group_general(const SgbRecurArgs& A, const SgbScalars& sp, unsigned char* ring, unsigned long long* bar,
                                                  unsigned& phases, int depth, int lane, int Tmax, long long eoff, int len,
-                                                 long long ostart)
+                                                 long long ostart, unsigned char* stage)
 {
-    recur_group_t<NPL, 0>(A, sp, ring, bar, phases, depth, lane, Tmax, eoff, len, ostart);
+    recur_group_t<NPL, 0, STAGED>(A, sp, ring, bar, phases, depth, lane, Tmax, eoff, len, ostart, stage);
 }
 
-template <int NPL>
+template <int NPL, bool STAGED>
 __device__ __forceinline__ void recur_group(const SgbRecurArgs& A, const SgbScalars& sp, unsigned char* ring, unsigned long long* bar,
                                             unsigned& phases, int ring_bytes, int lane, int Tmax, long long eoff, int len,
-                                            long long ostart)
+                                            long long ostart, unsigned char* stage)
 {
     int depth = ring_bytes / (NPL * 4096);
     depth = depth > SGB_RECUR_MAXDEPTH ? SGB_RECUR_MAXDEPTH : depth;
-    if (sp.diag_dominant) recur_group_t<NPL, 1>(A, sp, ring, bar, phases, depth, lane, Tmax, eoff, len, ostart);
-    else recur_group_general<NPL>(A, sp, ring, bar, phases, depth, lane, Tmax, eoff, len, ostart);
+    if (sp.diag_dominant) recur_group_t<NPL, 1, STAGED>(A, sp, ring, bar, phases, depth, lane, Tmax, eoff, len, ostart, stage);
+    else recur_group_general<NPL, STAGED>(A, sp, ring, bar, phases, depth, lane, Tmax, eoff, len, ostart, stage);
 }
 
-template <int MAXNPL>
+#ifdef SGB_RECUR_TIMING
+static __device__ unsigned long long gs_dbg[4 * 8192];
+extern "C" __attribute__((visibility("default"))) int sgb_debug_recur_read(unsigned long long* dst, int n)
+{
+    return (int)cudaMemcpyFromSymbol(dst, gs_dbg, (size_t)n * 8);
+}
+__device__ __forceinline__ unsigned long long sgb_gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#endif
+template <int MAXNPL, bool STAGED>
 __global__ void __launch_bounds__(SGB_RECUR_NWARPS(MAXNPL) * 32, MAXNPL <= 3 ? 2 : 1) k_recur(SgbRecurArgs A, int ring_bytes)
 {
     extern __shared__ __align__(128) unsigned char rsm[];
     __shared__ __align__(8) unsigned long long bars[SGB_RECUR_WARPS][SGB_RECUR_MAXDEPTH];
+    __shared__ __align__(16) unsigned char stages[SGB_RECUR_WARPS][STAGED ? SGB_STAGE_BYTES : 16];
     __shared__ SgbScalars s_sp;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     unsigned char* ring = rsm + (size_t)wid * ring_bytes;
@@ -521,10 +615,19 @@ __global__ void __launch_bounds__(SGB_RECUR_NWARPS(MAXNPL) * 32, MAXNPL <= 3 ? 2
     const SgbScalars& sp = s_sp;
     unsigned phases = 0;              // bit s: parity of the next completed phase of slot s's barrier
     const int ng = *A.W.ngroups;
+    // Groups are ordered heaviest first (plane count, then length).  The first one of every warp is assigned by position, strided
+    // over the CTAs and rotated over the warp slots, so that the heavy groups land on different SMs and different
+    // schedulers (handed out by arrival order they ended up eight to an SM); further groups come from a counter.
+    const int nw = (int)(blockDim.x >> 5);
+    bool first = true;
     for (;;) {
         int g = 0;
-        if (lane == 0) g = (int)atomicAdd(&A.W.counters[1], 1u);
-        g = __shfl_sync(SGB_FULL, g, 0);
+        if (first) g = ((wid + (int)blockIdx.x) % nw) * (int)gridDim.x + (int)blockIdx.x;
+        else {
+            if (lane == 0) g = (int)atomicAdd(&A.W.counters[1], 1u) + nw * (int)gridDim.x;
+            g = __shfl_sync(SGB_FULL, g, 0);
+        }
+        first = false;
         if (g >= ng) break;
         const int npl = A.W.g_npl[g];
         const int Tmax = A.W.g_tmax[g];
@@ -534,7 +637,11 @@ __global__ void __launch_bounds__(SGB_RECUR_NWARPS(MAXNPL) * 32, MAXNPL <= 3 ? 2
         long long ostart = 0;
         if (idx >= 0) { len = A.plan.len[idx]; ostart = A.plan.ostart[idx]; }
         if (Tmax <= 0 || npl <= 0) continue;
-#define SGB_RG(N) recur_group<N>(A, sp, ring, bar, phases, ring_bytes, lane, Tmax, eoff, len, ostart)
+#ifdef SGB_RECUR_TIMING
+        const unsigned long long dbg_t0 = sgb_gtime();
+        const long long dbg_c0 = clock64();
+#endif
+#define SGB_RG(N) recur_group<N, STAGED>(A, sp, ring, bar, phases, ring_bytes, lane, Tmax, eoff, len, ostart, stages[wid])
         if (npl == 1) SGB_RG(1);
         else if (npl == 2) SGB_RG(2);
         else if (npl == 3) SGB_RG(3);
@@ -545,6 +652,16 @@ __global__ void __launch_bounds__(SGB_RECUR_NWARPS(MAXNPL) * 32, MAXNPL <= 3 ? 2
         }
 #undef SGB_RG
         __syncwarp();
+#ifdef SGB_RECUR_TIMING
+        if (lane == 0 && g < 8192) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            gs_dbg[4 * g] = (unsigned long long)npl | ((unsigned long long)(Tmax & 0xffff) << 8) | ((unsigned long long)(smid & 0xff) << 24);
+            gs_dbg[4 * g + 1] = dbg_t0;
+            gs_dbg[4 * g + 2] = sgb_gtime();
+            gs_dbg[4 * g + 3] = (unsigned long long)(clock64() - dbg_c0);
+        }
+#endif
     }
 }
 
@@ -613,8 +730,8 @@ static cudaError_t launch_emit(const SgbEmitArgs& A, long long nseq, int sm_coun
     }
 }
 
-template <int MAXNPL>
-static cudaError_t launch_recur(const SgbRecurArgs& A, int gcap, int sm_count, cudaStream_t st)
+template <int MAXNPL, bool STAGED>
+static cudaError_t launch_recur_k(const SgbRecurArgs& A, int gcap, int sm_count, cudaStream_t st)
 {
     // Ring size per warp: the TMA copies must run far enough ahead of the recursion to cover the memory latency (~1 us)
     // at ~100-250 cycles per bin, i.e. >= 8 bins whatever the plane count (a chunk is 4 bins x planes KB).  Small
@@ -626,13 +743,24 @@ static cudaError_t launch_recur(const SgbRecurArgs& A, int gcap, int sm_count, c
     const int ci = gcap <= sm_count * NW ? 0 : 1;
     const int ring_kb = ci == 0 ? big : small;
     const size_t smem = (size_t)NW * ring_kb * 1024;
-    const int occ = split_occupancy(k_recur<MAXNPL>, NW * 32, smem, (size_t)NW * big * 1024, cache[ci]);
+    const int occ = split_occupancy(k_recur<MAXNPL, STAGED>, NW * 32, smem, (size_t)NW * big * 1024, cache[ci]);
     if (occ < 1) return cudaErrorInvalidConfiguration;
     long long blocks = ((long long)gcap + NW - 1) / NW;
     if (blocks > (long long)sm_count * occ) blocks = (long long)sm_count * occ;
     if (blocks < 1) blocks = 1;
-    k_recur<MAXNPL><<<(unsigned)blocks, NW * 32, smem, st>>>(A, ring_kb * 1024);
+    k_recur<MAXNPL, STAGED><<<(unsigned)blocks, NW * 32, smem, st>>>(A, ring_kb * 1024);
     return cudaGetLastError();
+}
+
+// Batches that fill the device several times over are bound by the L1's store path unless the decoded states are staged
+// (one byte per lane per bin = 32 sectors per store instruction); a batch of at most one wave of groups is bound by the
+// latency of its longest chain, where the flush of the staging buffer would only add to it.
+template <int MAXNPL>
+static cudaError_t launch_recur(const SgbRecurArgs& A, int gcap, int sm_count, cudaStream_t st)
+{
+    const char* e = getenv("SGB_RECUR_STAGED");          // 0 / 1 forces a variant (tests)
+    const bool staged = (e && *e) ? atoi(e) != 0 : gcap > 2 * sm_count * SGB_RECUR_NWARPS(MAXNPL);
+    return staged ? launch_recur_k<MAXNPL, true>(A, gcap, sm_count, st) : launch_recur_k<MAXNPL, false>(A, gcap, sm_count, st);
 }
 
 cudaError_t sgbk_split_decode(const SgbPlanDev& plan, long long nseq, const SgbColsIn& in, const SgbDevTables* d_tabs,

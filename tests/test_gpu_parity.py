@@ -29,10 +29,13 @@ def _bits(a):
     return np.ascontiguousarray(a, dtype=np.float64).view(np.uint64)
 
 
-@pytest.fixture(params=["split", "fused"])
+@pytest.fixture(params=["split", "split_staged", "fused"])
 def sched(request, monkeypatch):
-    """both schedules of the reference decode: "split" (k_emit + k_recur, the default) and "fused" (k_decode)"""
-    monkeypatch.setenv("SGB_SCHED", request.param)
+    """the schedules of the reference decode: "split" (k_emit + k_recur, the default; small batches store the decoded states
+    directly), "split_staged" (k_recur's variant for large batches: four-bin blocks, states staged in shared memory) and
+    "fused" (k_decode)"""
+    monkeypatch.setenv("SGB_SCHED", request.param.split("_")[0])
+    monkeypatch.setenv("SGB_RECUR_STAGED", "1" if request.param == "split_staged" else "0")
     return request.param
 
 
