@@ -166,7 +166,9 @@ int want_split(const SgbModelArgs& m, long long nseq)
     long long lim = 60000;
     const char* t = getenv("SGB_SPLIT_MAX_SEQ");
     if (t && atoll(t) > 0) lim = atoll(t);
-    return nseq < lim;
+    // beta-binomial: the emission dominates and the split kernels evaluate it faster at every batch size
+    // (10,000 cells ASCN: 3.78 ms against the fused kernel's 3.86 ms); binomial: the fused kernel wins once the device is full
+    return m.lik_bb || nseq < lim;
 }
 
 // host-side description of a batch of sequences, sorted by length (longest first)

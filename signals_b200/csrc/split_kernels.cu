@@ -217,19 +217,38 @@ static inline size_t emit_smem_bytes(int S, int lik_bb)
     return d * sizeof(double) + ((size_t)SGB_CN_TABLE * S + SGB_CN_TABLE) * sizeof(int);
 }
 
-// one row of the caller's columns, whatever their element type; returns validation bits.  KIND >= 0: the element types
-// are known at compile time (no branches); KIND < 0: taken from in.kind
+// One row of the caller's columns, whatever their element type, in two halves: sgb_row_fetch only issues the loads (the
+// row of the NEXT 32-bin tile is fetched while the current one is evaluated), sgb_row_check converts and validates the
+// values when they are consumed -- a check right behind the loads would wait for them and undo the prefetch (it did: a
+// quarter of k_emit's stall samples sat on the first instruction after the loads).  KIND >= 0: the element types are
+// known at compile time (no branches); KIND < 0: taken from in.kind.
+struct SgbRawRow {
+    int n, x, cn;            // integer kinds
+    double dn, dx, dc;       // SGB_IN_F64
+};
 template <int KIND>
-__device__ __forceinline__ int sgb_load_row(const SgbColsIn& in, long long row, int& n, int& x, int& cnv)
+__device__ __forceinline__ void sgb_row_fetch(const SgbColsIn& in, long long row, SgbRawRow& r)
+{
+    const int kind = KIND >= 0 ? KIND : in.kind;
+    if (kind == SGB_IN_U16_U8) {
+        r.n = (int)__ldg((const uint16_t*)in.n + row); r.x = (int)__ldg((const uint16_t*)in.x + row);
+        r.cn = (int)__ldg((const uint8_t*)in.cn + row);
+    } else if (kind == SGB_IN_F64) {
+        r.dn = __ldg((const double*)in.n + row); r.dx = __ldg((const double*)in.x + row);
+        r.dc = __ldg((const double*)in.cn + row);
+    } else {
+        r.n = __ldg((const int32_t*)in.n + row); r.x = __ldg((const int32_t*)in.x + row);
+        r.cn = kind == SGB_IN_I32_I32 ? __ldg((const int32_t*)in.cn + row) : (int)__ldg((const uint8_t*)in.cn + row);
+    }
+}
+// returns validation bits; a bad bin is neutralised (n = x = cn = 0), the call fails afterwards -- the checks of the fused path
+template <int KIND>
+__device__ __forceinline__ int sgb_row_check(const SgbColsIn& in, const SgbRawRow& r, int& n, int& x, int& cnv)
 {
     int bad = 0;
     const int kind = KIND >= 0 ? KIND : in.kind;
-    if (kind == SGB_IN_U16_U8) {
-        n = (int)__ldg((const uint16_t*)in.n + row); x = (int)__ldg((const uint16_t*)in.x + row);
-        cnv = (int)__ldg((const uint8_t*)in.cn + row);
-    } else if (kind == SGB_IN_F64) {
-        const double dn = __ldg((const double*)in.n + row), dx = __ldg((const double*)in.x + row);
-        const double dc = __ldg((const double*)in.cn + row);
+    if (kind == SGB_IN_F64) {
+        const double dn = r.dn, dx = r.dx, dc = r.dc;
         const double lim = (double)(1 << SGB_COUNT_BITS);
         if (dn != dn || dx != dx || dc != dc) bad |= SGB_ERR_NOT_INTEGER;
         else if (dn < 0.0 || dx < 0.0) bad |= SGB_ERR_NEGATIVE_COUNT;
@@ -238,10 +257,8 @@ __device__ __forceinline__ int sgb_load_row(const SgbColsIn& in, long long row, 
         else if (dn != rint(dn) || dx != rint(dx) || dc != rint(dc)) bad |= SGB_ERR_NOT_INTEGER;
         n = bad ? 0 : (int)dn; x = bad ? 0 : (int)dx; cnv = bad ? 0 : (int)dc;
     } else {
-        n = __ldg((const int32_t*)in.n + row); x = __ldg((const int32_t*)in.x + row);
-        cnv = kind == SGB_IN_I32_I32 ? __ldg((const int32_t*)in.cn + row) : (int)__ldg((const uint8_t*)in.cn + row);
+        n = r.n; x = r.x; cnv = r.cn;
     }
-    // the checks of the fused path: a bad bin is neutralised, the call fails afterwards
     if ((unsigned)(n | x) >> SGB_COUNT_BITS) {
         bad |= (n | x) < 0 ? SGB_ERR_NEGATIVE_COUNT : SGB_ERR_COUNT_TOO_LARGE;
         n = 0; x = 0; cnv = 0;
@@ -315,15 +332,16 @@ __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmi
         const int run = 4 * npl;                                          // sectors of one sequence inside a chunk
         const int lrm = lr % run;
         double* tile = A.W.E + (A.W.g_eoff[g] + (long long)lr * run) * 4;  // + chunk * 128 npl sectors + rotated position
-        int n = 0, x = 0, cnv = 0;
-        if (lane < len) bad |= sgb_load_row<KIND>(A.in, o + lane, n, x, cnv);
+        SgbRawRow raw;
+        raw.n = raw.x = raw.cn = 0; raw.dn = raw.dx = raw.dc = 0.0;
+        if (lane < len) sgb_row_fetch<KIND>(A.in, o + lane, raw);
         for (int t0 = 0; t0 < len; t0 += 32) {
             const int t = t0 + lane;
             const bool act = t < len;
-            const int nc = n, xc = x, cc = cnv;
+            int nc = 0, xc = 0, cc = 0;
+            if (act) bad |= sgb_row_check<KIND>(A.in, raw, nc, xc, cc);
             // next tile's row: in flight while this one is evaluated
-            n = 0; x = 0; cnv = 0;
-            if (t + 32 < len) bad |= sgb_load_row<KIND>(A.in, o + t + 32, n, x, cnv);
+            if (t + 32 < len) sgb_row_fetch<KIND>(A.in, o + t + 32, raw);
             const int cprime = sgb_cprime(MODEL, cc);
             const int ins = xc <= nc;
             const int L = act ? sgb_live_states(MODEL, cprime, S) : 0;
