@@ -429,9 +429,6 @@ struct SgbRecurArgs {
     const SgbDevTables* tabs;
     uint8_t* state_out;
     int S;
-#ifdef SGB_RECUR_TIMING
-    int dbg_ng_limit;
-#endif
 };
 
 #define SGB_RECUR_WARPS 4               // per CTA when at most 3 planes (maxCN <= 11); 2 for the 8-plane kernel
@@ -635,11 +632,7 @@ __global__ void __launch_bounds__(SGB_RECUR_NWARPS(MAXNPL) * 32, MAXNPL <= 3 ? 2
     __syncthreads();
     const SgbScalars& sp = s_sp;
     unsigned phases = 0;              // bit s: parity of the next completed phase of slot s's barrier
-#ifdef SGB_RECUR_TIMING
-    const int ng = *A.W.ngroups < A.dbg_ng_limit ? *A.W.ngroups : A.dbg_ng_limit;      // (study: only the first groups)
-#else
     const int ng = *A.W.ngroups;
-#endif
     // Groups are ordered heaviest first (plane count, then length).  The first one of every warp is assigned by position, strided
     // over the CTAs and rotated over the warp slots, so that the heavy groups land on different SMs and different
     // schedulers (handed out by arrival order they ended up eight to an SM); further groups come from a counter.
@@ -765,8 +758,7 @@ static cudaError_t launch_recur_k(const SgbRecurArgs& A, int gcap, int sm_count,
     static int cache[2][64];
     constexpr int NW = SGB_RECUR_NWARPS(MAXNPL);
     const int big = MAXNPL <= 3 ? 48 : 96, small = MAXNPL <= 3 ? 24 : 64;
-    int ci = gcap <= sm_count * NW ? 0 : 1;
-    { const char* e = getenv("SGB_DBG_RING"); if (e && *e) ci = atoi(e) ? 0 : 1; }
+    const int ci = gcap <= sm_count * NW ? 0 : 1;
     const int ring_kb = ci == 0 ? big : small;
     const size_t smem = (size_t)NW * ring_kb * 1024;
     const int occ = split_occupancy(k_recur<MAXNPL, STAGED>, NW * 32, smem, (size_t)NW * big * 1024, cache[ci]);
@@ -817,8 +809,5 @@ cudaError_t sgbk_split_decode(const SgbPlanDev& plan, long long nseq, const SgbC
     if (ev_mid && (e = cudaEventRecord(ev_mid, st)) != cudaSuccess) return e;
     SgbRecurArgs RA;
     RA.plan = plan; RA.W = W; RA.tabs = d_tabs; RA.state_out = d_state_out; RA.S = m.S;
-#ifdef SGB_RECUR_TIMING
-    { const char* e = getenv("SGB_DBG_NG"); RA.dbg_ng_limit = e ? atoi(e) : 0x7fffffff; }
-#endif
     return m.S <= 12 ? launch_recur<3>(RA, W.gcap, sm_count, st) : launch_recur<8>(RA, W.gcap, sm_count, st);
 }
