@@ -205,11 +205,22 @@ struct SgbEmitArgs {
 };
 
 #define SGB_EMIT_THREADS 256
+#ifndef SGB_EMIT_BIN_MINBLOCKS
+#define SGB_EMIT_BIN_MINBLOCKS 3
+#endif
+// resident CTAs per SM the register allocation is bounded for (measured, 57 M cell-bins: binomial 3 -> 1.154 ms, 4 -> 1.163, 2 -> 1.379;
+// beta-binomial 3 -> 2.91 ms, 2 -> 3.12, 4 -> 2.97; evaluating two beta-binomial items at a time: 2.96 at 2 CTAs, 3.25 at 3)
+#ifndef SGB_EMIT_BB_MINBLOCKS
+#define SGB_EMIT_BB_MINBLOCKS 3
+#endif
 #define SGB_EMIT_LF 1024
 #define SGB_LTP_LEN (((SGB_LOGTAB_LEN + 1) / 2) * 16)      // lane-private log table: pairs x 8 columns x 2 doubles
 #define SGB_ETP_LEN (SGB_EXPTAB_LEN * 16)                   // lane-private exp table: entries x 16 columns
+#ifndef SGB_EMIT_BB_PAIR
+#define SGB_EMIT_BB_PAIR 0
+#endif
 #ifndef SGB_PAIR_OK
-#define SGB_PAIR_OK(likbb) (!(likbb))      // beta-binomial: one item at a time (instruction-cache footprint, see hmm_kernels.cu)
+#define SGB_PAIR_OK(likbb) (!(likbb) || SGB_EMIT_BB_PAIR)      // beta-binomial: one item at a time (instruction-cache footprint, see hmm_kernels.cu)
 #endif
 static inline size_t emit_smem_bytes(int S, int lik_bb)
 {
@@ -268,7 +279,7 @@ __device__ __forceinline__ int sgb_row_check(const SgbColsIn& in, const SgbRawRo
 }
 
 template <int MODEL, int LIKBB, int KIND>
-__global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? 2 : 3) k_emit(SgbEmitArgs A)
+__global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? SGB_EMIT_BB_MINBLOCKS : SGB_EMIT_BIN_MINBLOCKS) k_emit(SgbEmitArgs A)
 {
     extern __shared__ __align__(16) double smem[];
     const int S = A.S;
