@@ -537,6 +537,31 @@ def gpu_measure(name, d, steps, warmup, rank, world, dist, sampler, want_e2e=Tru
                 del dn_, dx_, dc_, o1_, o2_, h1_, h2_
             except Exception as ex:
                 variants["two_passes_one_upload_pinned"] = dict(error=str(ex))
+            # the same pair of passes for an R-style caller: PAGEABLE int32 columns through sgb_cols_upload (one conversion +
+            # upload), two sgb_cols_decode calls with numeric (double) results -- against 2 x pageable_int32_in_double_out
+            try:
+                pn, px, pc = d["n"].astype(np.int32), d["x"].astype(np.int32), d["cn"].astype(np.int32)
+                po1, po2 = np.zeros(N, dtype=np.float64), np.zeros(N, dtype=np.float64)
+                P2 = hmm.make_params(model=model, likelihood=lik, rho=rho, **dict(PARAMS, loherror=0.031))
+                def two_pass_cols():
+                    h = ctypes.c_void_p()
+                    hmm.check(lib.sgb_cols_upload(N, pn.ctypes.data, _lib.T_I32, px.ctypes.data, _lib.T_I32, pc.ctypes.data, _lib.T_I32,
+                                                  so_.size - 1, so_.ctypes.data, ctypes.byref(h)))
+                    hmm.check(lib.sgb_cols_decode(h, ctypes.byref(P), po1.ctypes.data, _lib.T_F64))
+                    hmm.check(lib.sgb_cols_decode(h, ctypes.byref(P2), po2.ctypes.data, _lib.T_F64))
+                    lib.sgb_cols_free(h)
+                two_pass_cols()
+                t0 = time.perf_counter()
+                for _ in range(3):
+                    two_pass_cols()
+                ms = (time.perf_counter() - t0) / 3 * 1e3
+                assert int(po1.sum()) == res["checksum"], "sgb_cols two-pass variant: pass 1 differs"
+                variants["two_passes_one_upload_pageable_int32_double_out"] = dict(
+                    value=2 * N / (ms * 1e-3), ms_per_step=ms, ms_per_pass=ms / 2, h2d_bytes_per_step=int(N * 9),
+                    d2h_bytes_per_step=int(2 * N), note="sgb_cols_upload + 2 x sgb_cols_decode + sgb_cols_free; value counts both passes")
+                del pn, px, pc, po1, po2
+            except Exception as ex:
+                variants["two_passes_one_upload_pageable_int32_double_out"] = dict(error=str(ex))
             res["e2e"]["variants"] = variants
     for pl in plans:
         pl.close()

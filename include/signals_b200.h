@@ -102,6 +102,19 @@ SGB_API int sgb_hmm_decode_typed(const sgb_params* params, int64_t N, const void
                                  int32_t x_type, const void* cn, int32_t cn_type, int64_t nseg, const int64_t* seg_off,
                                  void* state_out, int32_t out_type, int32_t n_devices);
 
+/* One upload, several passes.  callHaplotypeSpecificCN decodes the same sorted table twice -- pass 1 at the default
+ * loherror, pass 2 at the inferred one and possibly beta-binomial (R/callHSCN.R:883-935, both through
+ * .callHaplotypeSpecificCN_, R/callHSCN.R:217-295) -- and callAlleleSpecificCN a third time (R/callASCN.R:372-414); the
+ * reference hands the three columns to every pass anew.  sgb_cols_upload converts (any element type, validated like
+ * sgb_hmm_decode_typed) and copies them to the current device ONCE; sgb_cols_decode runs one pass on the resident columns
+ * with any parameters (model, likelihood, loherror, rho, n_states, decode rule) and writes the states into a host vector
+ * of any element type; sgb_cols_free releases the device memory.  9 bytes per cell-bin stay on the device between passes. */
+typedef struct sgb_cols sgb_cols;
+SGB_API int sgb_cols_upload(int64_t N, const void* n, int32_t n_type, const void* x, int32_t x_type, const void* cn,
+                            int32_t cn_type, int64_t nseg, const int64_t* seg_off, sgb_cols** cols_out);
+SGB_API int sgb_cols_decode(sgb_cols* cols, const sgb_params* params, void* state_out, int32_t out_type);
+SGB_API int sgb_cols_free(sgb_cols* cols);
+
 /* Device-resident variant: inputs and outputs are device pointers on the current device.
  * sgb_plan_create sorts the sequences by length on the host, uploads the index and reserves the
  * packed-record scratch; the plan can be reused for any inputs with the same seg_off.

@@ -91,10 +91,16 @@ assignalleleHMM <- function(CNBAF, minor_cn, eps = 1e-12, loherror = 0.02, selft
                                       progressbar = TRUE, ncores = 1, likelihood = "binomial", rho = 0.0,
                                       Abias = 0.0, viterbiver = "cpp") {
   # progressbar / viterbiver are accepted and ignored: one call decodes every cell; ncores picks the number of GPUs
-  CNBAF <- data.table::as.data.table(CNBAF) %>% .[order(cell_id, chr, start)]      # R/callHSCN.R:241-242
-  seg <- .sgb_seg_off(CNBAF$cell_id, as.character(CNBAF$chr))
-  CNBAF$state_min <- .sgb_decode(0L, CNBAF$totalcounts, CNBAF$alleleB, CNBAF$state, seg, maxCN, loherror,
-                                 selftransitionprob, eps, likelihood, rho, Abias, ngpus = .sgb_ngpus(ncores))[[1]]
+  if (inherits(CNBAF, "sgb_table")) {                                               # columns already on the device
+    tab <- CNBAF
+    CNBAF <- data.table::copy(tab$CNBAF)
+    CNBAF$state_min <- .sgb_table_decode(tab, 0L, maxCN, loherror, selftransitionprob, eps, likelihood, rho, Abias)
+  } else {
+    CNBAF <- data.table::as.data.table(CNBAF) %>% .[order(cell_id, chr, start)]    # R/callHSCN.R:241-242
+    seg <- .sgb_seg_off(CNBAF$cell_id, as.character(CNBAF$chr))
+    CNBAF$state_min <- .sgb_decode(0L, CNBAF$totalcounts, CNBAF$alleleB, CNBAF$state, seg, maxCN, loherror,
+                                   selftransitionprob, eps, likelihood, rho, Abias, ngpus = .sgb_ngpus(ncores))[[1]]
+  }
   alleleCN <- CNBAF %>%                                                             # R/callHSCN.R:282-292 unchanged
     .[, state_min := fifelse(state_min < 0, 0, state_min)] %>%
     .[, A := state - state_min] %>% .[, B := state_min] %>%
@@ -102,6 +108,28 @@ assignalleleHMM <- function(CNBAF, minor_cn, eps = 1e-12, loherror = 0.02, selft
     .[, B := fifelse(B > state, state, B)] %>% .[, A := fifelse(A > state, state, A)]
   as.data.frame(add_states(alleleCN))
 }
+
+# Several passes on ONE upload of the table.  callHaplotypeSpecificCN calls .callHaplotypeSpecificCN_ twice on the same CNBAF
+# (R/callHSCN.R:883-893 with the default loherror, :925-935 with the inferred one and the fitted rho); the three columns and
+# their order do not change in between.  With
+#   tab <- .sgb_table(CNBAF)                      # sort (R/callHSCN.R:241-242), offsets, one conversion + upload
+#   hscn_data <- .callHaplotypeSpecificCN_(tab, loherror = loherror, ...)            # pass 1
+#   hscn_data <- .callHaplotypeSpecificCN_(tab, loherror = infloherror, likelihood = likelihood, rho = bbfit$rho, ...)   # pass 2
+#   .sgb_table_free(tab)                          # (or leave it to the garbage collector)
+# the second pass costs the kernels and the copy of state_min.  A `tab` is list(handle, nrows, CNBAF sorted); a plain data
+# frame still works everywhere (it is uploaded for that one call).
+.sgb_table <- function(CNBAF) {
+  CNBAF <- data.table::as.data.table(CNBAF) %>% .[order(cell_id, chr, start)]
+  seg <- .sgb_seg_off(CNBAF$cell_id, as.character(CNBAF$chr))
+  h <- .Call("_signals_cols_upload", CNBAF$totalcounts, CNBAF$alleleB, CNBAF$state, as.numeric(seg), PACKAGE = "signals")
+  structure(list(handle = h[[1]], nrows = h[[2]], CNBAF = CNBAF), class = "sgb_table")
+}
+.sgb_table_decode <- function(tab, model, maxCN, loherror, selftransitionprob, eps, likelihood, rho, Abias) {
+  .Call("_signals_cols_decode", tab$handle, tab$nrows, as.integer(model), as.character(likelihood), as.integer(maxCN),
+        as.numeric(loherror), as.numeric(eps), as.numeric(rho), as.numeric(Abias), as.numeric(selftransitionprob),
+        PACKAGE = "signals")
+}
+.sgb_table_free <- function(tab) invisible(.Call("_signals_cols_free", tab$handle, PACKAGE = "signals"))
 
 # The per-cell loops of callAlleleSpecificCN (R/callASCN.R:382-414) and callAlleleSpecificCNfromHSCN (:556-588):
 #   alleleCN <- rbindlist(lapply / mclapply(unique(CNBAF$cell_id), function(cell) assignalleleHMM(filter(CNBAF, cell_id == cell), ...)))
@@ -111,6 +139,11 @@ assignalleleHMM <- function(CNBAF, minor_cn, eps = 1e-12, loherror = 0.02, selft
 # (callAlleleSpecificCN: likelihood = likelihood, rho = bbfit$rho; ...fromHSCN: hscn$likelihood$likelihood / $rho).
 # Everything after the loop (:416-447, :590-621) is unchanged.
 .sgb_ascn_batch <- function(CNBAF, maxCN, eps, loherror, selftransitionprob, likelihood, rho, ncores = 1) {
+  if (inherits(CNBAF, "sgb_table")) {
+    alleleCN <- data.table::copy(CNBAF$CNBAF)
+    alleleCN$state_min <- .sgb_table_decode(CNBAF, 1L, maxCN, loherror, selftransitionprob, eps, likelihood, rho, 0.0)
+    return(alleleCN)
+  }
   alleleCN <- data.table::as.data.table(CNBAF) %>% .[order(cell_id, chr, start)]
   seg <- .sgb_seg_off(alleleCN$cell_id, as.character(alleleCN$chr))
   alleleCN$state_min <- .sgb_decode(1L, alleleCN$totalcounts, alleleCN$alleleB, alleleCN$state, seg, maxCN, loherror,

@@ -159,6 +159,63 @@ SEXP _signals_hmm_decode_batch(SEXP model, SEXP totalcounts, SEXP alleleB, SEXP 
     return out;
 }
 
+/* The table kept on the device between passes (sgb_cols_*): callHaplotypeSpecificCN runs .callHaplotypeSpecificCN_ twice on
+ * the same CNBAF (R/callHSCN.R:883-935), callAlleleSpecificCN once more (R/callASCN.R:372-414); with a handle the second and
+ * third pass cost the kernels and the copy of the states, not another conversion + upload of the three columns.
+ * _signals_cols_upload returns an external pointer (finalizer: sgb_cols_free); _signals_cols_decode runs one pass and
+ * returns state_min as numeric; _signals_cols_free releases the device memory at once. */
+static void cols_finalizer(SEXP h)
+{
+    sgb_cols* c = (sgb_cols*)R_ExternalPtrAddr(h);
+    if (c) {
+        sgb_cols_free(c);
+        R_ClearExternalPtr(h);
+    }
+}
+
+SEXP _signals_cols_upload(SEXP totalcounts, SEXP alleleB, SEXP state, SEXP seg_off)
+{
+    const int tn = col_type(totalcounts, "totalcounts"), tx = col_type(alleleB, "alleleB"), tc = col_type(state, "state");
+    R_xlen_t N = XLENGTH(totalcounts);
+    if (XLENGTH(alleleB) != N || XLENGTH(state) != N) Rf_error("totalcounts, alleleB and state must have the same length");
+    R_xlen_t nseg = 0;
+    int64_t* off = seg_offsets(seg_off, &nseg);
+    sgb_cols* c = NULL;
+    check_rc(sgb_cols_upload((int64_t)N, col_ptr(totalcounts), tn, col_ptr(alleleB), tx, col_ptr(state), tc, (int64_t)nseg, off, &c));
+    SEXP h = PROTECT(R_MakeExternalPtr(c, R_NilValue, R_NilValue));
+    R_RegisterCFinalizerEx(h, cols_finalizer, TRUE);
+    SEXP len = PROTECT(Rf_allocVector(REALSXP, 1));
+    REAL(len)[0] = (double)N;
+    SEXP out = PROTECT(Rf_allocVector(VECSXP, 2));       /* list(handle, number of rows) */
+    SET_VECTOR_ELT(out, 0, h);
+    SET_VECTOR_ELT(out, 1, len);
+    UNPROTECT(3);
+    return out;
+}
+
+SEXP _signals_cols_decode(SEXP handle, SEXP nrows, SEXP model, SEXP likelihood, SEXP maxCN, SEXP loherror, SEXP eps, SEXP rho,
+                          SEXP Abias, SEXP stp)
+{
+    if (TYPEOF(handle) != EXTPTRSXP) Rf_error("handle must come from the table upload");
+    sgb_cols* c = (sgb_cols*)R_ExternalPtrAddr(handle);
+    if (!c) Rf_error("signals_b200: the table has been released");
+    sgb_params P;
+    fill_params(&P, model, likelihood, maxCN, loherror, eps, rho, Abias, stp);
+    const double nr = Rf_asReal(nrows);
+    if (ISNAN(nr) || nr < 0) Rf_error("bad row count");
+    SEXP res = PROTECT(Rf_allocVector(REALSXP, (R_xlen_t)nr));
+    check_rc(sgb_cols_decode(c, &P, REAL(res), SGB_T_F64));
+    UNPROTECT(1);
+    return res;
+}
+
+SEXP _signals_cols_free(SEXP handle)
+{
+    if (TYPEOF(handle) != EXTPTRSXP) Rf_error("handle must come from the table upload");
+    cols_finalizer(handle);
+    return R_NilValue;
+}
+
 /* Post-decode columns on the device: the clamp block R/callHSCN.R:282-290 and the numeric part of add_states
  * (R/util.R:1078-1097).  state: integer vector; state_min: numeric / integer vector of decoded states (0..255).
  * Returns list(A, B, state_min, LOH (1/0), phase (0/1/2), state_phase (0..4), state_BAF). */
@@ -236,6 +293,9 @@ static const R_CallMethodDef CallEntries[] = {
     {"_signals_postprocess", (DL_FUNC)&_signals_postprocess, 2},
     {"_signals_pass_stats", (DL_FUNC)&_signals_pass_stats, 5},
     {"_signals_device_count", (DL_FUNC)&_signals_device_count, 0},
+    {"_signals_cols_upload", (DL_FUNC)&_signals_cols_upload, 4},
+    {"_signals_cols_decode", (DL_FUNC)&_signals_cols_decode, 10},
+    {"_signals_cols_free", (DL_FUNC)&_signals_cols_free, 1},
     {NULL, NULL, 0}};
 
 void R_init_signals(DllInfo* dll)

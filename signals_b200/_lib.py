@@ -38,6 +38,9 @@ SIGNATURES = {
     "sgb_hmm_decode": (ctypes.c_int, [_PP, _i64, _vp, _vp, _vp, _i32, _i64, _vp, _vp, _vp]),
     "sgb_hmm_decode_multi": (ctypes.c_int, [_PP, _i32, _i64, _vp, _vp, _vp, _i32, _i64, _vp, _vp]),
     "sgb_hmm_decode_typed": (ctypes.c_int, [_PP, _i64, _vp, _i32, _vp, _i32, _vp, _i32, _i64, _vp, _vp, _i32, _i32]),
+    "sgb_cols_upload": (ctypes.c_int, [_i64, _vp, _i32, _vp, _i32, _vp, _i32, _i64, _vp, ctypes.POINTER(_vp)]),
+    "sgb_cols_decode": (ctypes.c_int, [_vp, _PP, _vp, _i32]),
+    "sgb_cols_free": (ctypes.c_int, [_vp]),
     "sgb_plan_create": (ctypes.c_int, [_i64, _i64, _vp, _i32, _i32, ctypes.POINTER(_vp)]),
     "sgb_plan_destroy": (ctypes.c_int, [_vp]),
     "sgb_plan_reserve_packed": (ctypes.c_int, [_vp]),

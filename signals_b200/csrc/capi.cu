@@ -1053,6 +1053,152 @@ int sgb_plan_check(sgb_plan* pl, void* stream)
     return 0;
 }
 
+// ---------------------------------------------------------------- resident columns (one upload, several passes)
+// callHaplotypeSpecificCN decodes the same table twice (R/callHSCN.R:883-935: pass 1 at the default loherror, pass 2 at the
+// inferred one, possibly beta-binomial), callAlleleSpecificCN once more on top: the columns are the same every time.
+// sgb_cols keeps them on the device -- int32 counts, uint8 copy number, converted and validated on the way up by the staging
+// workers -- so that every pass after the first costs the kernels and the copy of the states back.
+struct sgb_cols {
+    int device = 0;
+    int64_t N = 0, nseg = 0;
+    std::vector<int64_t> seg_off;
+    DevBuf n, x, cn, out;
+    sgb_plan* plan = nullptr;   // made by the first decode (its scratch depends on n_states and the decode rule)
+};
+
+int sgb_cols_free(sgb_cols* c)
+{
+    if (!c) return 0;
+    if (c->plan) sgb_plan_destroy(c->plan);
+    c->n.release(); c->x.release(); c->cn.release(); c->out.release();
+    delete c;
+    return 0;
+}
+
+int sgb_cols_upload(int64_t N, const void* n, int32_t n_type, const void* x, int32_t x_type, const void* cn, int32_t cn_type,
+                    int64_t nseg, const int64_t* seg_off, sgb_cols** cols_out)
+{
+    if (!cols_out) return fail("cols_out is NULL");
+    *cols_out = nullptr;
+    if (N < 0 || nseg < 0 || (nseg > 0 && !seg_off)) return fail("bad arguments");
+    if (N > 0 && (!n || !x || !cn)) return fail("NULL column");
+    if (!sgb_type_size(n_type) || !sgb_type_size(x_type) || !sgb_type_size(cn_type)) return fail("unknown element type code");
+    for (int64_t s = 0; s < nseg; s++)
+        if (seg_off[s] > seg_off[s + 1]) return fail("seg_off must be non-decreasing");
+    if (nseg > 0 && (seg_off[0] < 0 || seg_off[nseg] > N)) return fail("seg_off out of range");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    sgb_cols* c = new sgb_cols();
+    c->device = C->device; c->N = N; c->nseg = nseg;
+    c->seg_off.assign(seg_off, seg_off + (nseg > 0 ? nseg + 1 : 0));
+    if (c->n.reserve((size_t)N * 4 + 16) || c->x.reserve((size_t)N * 4 + 16) || c->cn.reserve((size_t)N + 16) ||
+        c->out.reserve((size_t)N + 16)) { sgb_cols_free(c); return 1; }
+    // chunks of rows: workers convert into a page-locked slot, the slot is copied up while they fill the other one
+    // (the page-locked slots are the context's chunk-staging buffers: allocated once per device -- page-locking 72 MB costs
+    // ~40 ms, more than the upload itself -- and idle between calls, the library not being re-entrant)
+    const int64_t CH = 4 << 20;
+    PinBuf* slot[2] = {&C->slot[0].stage_in, &C->slot[1].stage_in};
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    cudaStream_t st = nullptr;
+    int rc = 0, host_bits = 0;
+    if (N > 0) {
+        if (!C->pool) C->pool.reset(new SgbPool(host_threads_default(1)));
+        if (slot[0]->reserve((size_t)CH * 9) || slot[1]->reserve((size_t)CH * 9)) rc = 1;
+        if (!rc && (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess ||
+                    cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming) != cudaSuccess ||
+                    cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming) != cudaSuccess))
+            rc = fail("could not create the upload stream");
+    }
+    int k = 0;
+    for (int64_t r0 = 0; !rc && r0 < N; r0 += CH, k++) {
+        const int64_t rows = std::min<int64_t>(CH, N - r0);
+        char* base = (char*)slot[k & 1]->p;
+        if (k >= 2 && cudaEventSynchronize(ev[k & 1]) != cudaSuccess) { rc = fail("upload failed"); break; }
+        std::atomic<int> bits(0);
+        C->pool->run([&](int w, int nw) {
+            const int64_t per = (rows + nw - 1) / nw;
+            const int64_t a = r0 + std::min<int64_t>(rows, per * w), b = r0 + std::min<int64_t>(rows, per * (w + 1));
+            if (a >= b) return;
+            int bb = sgb_stage_count_i32(n, n_type, a, b, (int32_t*)base + (a - r0));
+            bb |= sgb_stage_count_i32(x, x_type, a, b, (int32_t*)(base + (size_t)CH * 4) + (a - r0));
+            bb |= sgb_stage_cn_u8(cn, cn_type, a, b, (uint8_t*)(base + (size_t)CH * 8) + (a - r0));
+            bits |= bb;
+        });
+        host_bits |= bits.load();
+        cudaError_t e = cudaMemcpyAsync((int32_t*)c->n.p + r0, base, (size_t)rows * 4, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync((int32_t*)c->x.p + r0, base + (size_t)CH * 4, (size_t)rows * 4, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync((uint8_t*)c->cn.p + r0, base + (size_t)CH * 8, (size_t)rows, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaEventRecord(ev[k & 1], st);
+        if (e != cudaSuccess) rc = fail(std::string("upload failed: ") + cudaGetErrorString(e));
+    }
+    if (st) {
+        if (cudaStreamSynchronize(st) != cudaSuccess && !rc) rc = fail("upload failed");
+        cudaStreamDestroy(st);
+    }
+    for (int j = 0; j < 2; j++) if (ev[j]) cudaEventDestroy(ev[j]);
+    if (!rc && (host_bits & (SGB_STG_NOT_INT | SGB_STG_BAD_CN))) {
+        int eb = 0;
+        if (host_bits & SGB_STG_NOT_INT) eb |= SGB_ERR_NOT_INTEGER;
+        if (host_bits & SGB_STG_BAD_CN) eb |= SGB_ERR_BAD_CN;
+        rc = fail(err_bits_text(eb));
+    }
+    if (rc) { sgb_cols_free(c); return 1; }
+    *cols_out = c;
+    return 0;
+}
+
+int sgb_cols_decode(sgb_cols* c, const sgb_params* params, void* state_out, int32_t out_type)
+{
+    if (!c) return fail("cols is NULL");
+    SgbModelArgs m;
+    if (check_params(params, m)) return 1;
+    if (!sgb_type_size(out_type)) return fail("unknown element type code");
+    if (c->N == 0) return 0;
+    if (!state_out) return fail("state_out is NULL");
+    Ctx* C;
+    if (get_ctx(&C)) return 1;
+    if (C->device != c->device) return fail("columns live on another device");
+    if (c->plan && (c->plan->n_states != m.S || (m.decode == SGB_DECODE_CHAINED && c->plan->decode != SGB_DECODE_CHAINED))) {
+        sgb_plan_destroy(c->plan);
+        c->plan = nullptr;
+    }
+    if (!c->plan && sgb_plan_create(c->N, c->nseg, c->seg_off.data(), m.S, m.decode, &c->plan)) return 1;
+    cudaStream_t st = C->main;
+    // bins that belong to no sequence keep state 0, as in sgb_hmm_decode
+    SGB_CUDA(cudaMemsetAsync(c->out.p, 0, (size_t)c->N, st));
+    if (sgb_hmm_decode_device(params, c->plan, (const int32_t*)c->n.p, (const int32_t*)c->x.p, c->cn.p, 1, (uint8_t*)c->out.p,
+                              nullptr, (void*)st))
+        return 1;
+    if (sgb_plan_check(c->plan, (void*)st)) return 1;
+    if (out_type == SGB_T_U8) {
+        SGB_CUDA(cudaMemcpy(state_out, c->out.p, (size_t)c->N, cudaMemcpyDeviceToHost));
+        return 0;
+    }
+    // other element types: states come down in page-locked chunks, the workers widen one chunk while the next one arrives
+    const int64_t CH = 8 << 20;
+    PinBuf& pin_out = C->slot[0].stage_out;       // (the context's page-locked output staging, idle between calls)
+    if (pin_out.reserve((size_t)std::min<int64_t>(c->N, 2 * CH))) return 1;
+    if (!C->pool) C->pool.reset(new SgbPool(host_threads_default(1)));
+    const int64_t nch = (c->N + CH - 1) / CH;
+    auto fetch = [&](int64_t k) {
+        const int64_t r0 = k * CH, rows = std::min<int64_t>(CH, c->N - r0);
+        return cudaMemcpyAsync((uint8_t*)pin_out.p + (k & 1) * CH, (const uint8_t*)c->out.p + r0, (size_t)rows, cudaMemcpyDeviceToHost, st);
+    };
+    SGB_CUDA(fetch(0));
+    for (int64_t k = 0; k < nch; k++) {
+        SGB_CUDA(cudaStreamSynchronize(st));
+        if (k + 1 < nch) SGB_CUDA(fetch(k + 1));
+        const int64_t r0 = k * CH, rows = std::min<int64_t>(CH, c->N - r0);
+        const uint8_t* src = (const uint8_t*)pin_out.p + (k & 1) * CH;
+        C->pool->run([&](int w, int nw) {
+            const int64_t per = (rows + nw - 1) / nw;
+            const int64_t a = std::min<int64_t>(rows, per * w), b = std::min<int64_t>(rows, per * (w + 1));
+            if (a < b) sgb_unstage_states(src + a, b - a, state_out, out_type, r0 + a);
+        });
+    }
+    return 0;
+}
+
 // ---------------------------------------------------------------- viterbi / logspace_add / utilities
 int sgb_viterbi(const double* emission, int64_t nrow_e, const double* transition, const int32_t* observations,
                 int64_t T, int32_t S, int32_t init_mode, int32_t decode, int32_t* path_out)

@@ -144,6 +144,54 @@ def decode_arrays(n, x, cn, seg_off, model="hscn", likelihood="binomial", n_stat
     return out
 
 
+class ResidentColumns:
+    """The three columns of a sorted long table kept on the device for several decode passes (sgb_cols_*): what the two HMM
+    passes of callHaplotypeSpecificCN (R/callHSCN.R:883-935) and callAlleleSpecificCN's third one share.
+
+        cols = ResidentColumns(n, x, cn, seg_off)          # one conversion + upload
+        p1 = cols.decode(loherror=0.02)                     # pass 1
+        p2 = cols.decode(loherror=0.031, likelihood="betabinomial", rho=0.02)
+        cols.close()
+    """
+
+    def __init__(self, n, x, cn, seg_off):
+        self._lib = _lib.load()
+        n = _as_column(n, "totalcounts"); x = _as_column(x, "alleleB"); cn = _as_column(cn, "state")
+        if not (n.size == x.size == cn.size):
+            raise ValueError("n, x and cn must have the same length")
+        seg_off = np.ascontiguousarray(seg_off, dtype=np.int64)
+        self.N = int(n.size)
+        self._h = ctypes.c_void_p()
+        check(self._lib.sgb_cols_upload(self.N, _ptr(n), _TYPE_CODE[n.dtype], _ptr(x), _TYPE_CODE[x.dtype], _ptr(cn),
+                                        _TYPE_CODE[cn.dtype], seg_off.size - 1, _ptr(seg_off), ctypes.byref(self._h)))
+
+    def decode(self, model="hscn", likelihood="binomial", n_states=12, loherror=0.02, eps=1e-12, rho=0.0, Abias=0.0,
+               selftransitionprob=0.999, decode="reference", out_dtype=np.uint8):
+        if not self._h:
+            raise SignalsB200Error("the columns have been released")
+        P = make_params(model, likelihood, n_states, loherror, eps, rho, Abias, selftransitionprob, decode)
+        out = np.zeros(self.N, dtype=np.dtype(out_dtype))
+        check(self._lib.sgb_cols_decode(self._h, ctypes.byref(P), _ptr(out), _TYPE_CODE[out.dtype]))
+        return out
+
+    def close(self):
+        if self._h:
+            self._lib.sgb_cols_free(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def postprocess_arrays(cn, path):
     """device version of the clamp block + numeric add_states columns (integer codes)"""
     cn = np.asarray(cn)

@@ -22,7 +22,7 @@ struct mock_sexp {
     SEXP dim;          /* the "dim" attribute or R_NilValue */
 };
 
-enum { NILSXP = 0, CHARSXP = 9, LGLSXP = 10, INTSXP = 13, REALSXP = 14, STRSXP = 16, VECSXP = 19 };
+enum { NILSXP = 0, CHARSXP = 9, LGLSXP = 10, INTSXP = 13, REALSXP = 14, STRSXP = 16, VECSXP = 19, EXTPTRSXP = 22 };
 
 extern SEXP R_NilValue;
 extern SEXP R_DimSymbol;
@@ -54,6 +54,12 @@ SEXP VECTOR_ELT(SEXP x, R_xlen_t i);
 SEXP SET_VECTOR_ELT(SEXP x, R_xlen_t i, SEXP v);
 void Rf_error(const char* fmt, ...) __attribute__((noreturn, format(printf, 1, 2)));
 char* R_alloc(size_t n, int size);
+/* external pointers: objects that outlive one .Call (not released by mock_reset); finalizers run in mock_gc() */
+typedef void (*R_CFinalizer_t)(SEXP);
+SEXP R_MakeExternalPtr(void* p, SEXP tag, SEXP prot);
+void* R_ExternalPtrAddr(SEXP s);
+void R_ClearExternalPtr(SEXP s);
+void R_RegisterCFinalizerEx(SEXP s, R_CFinalizer_t fun, int onexit);
 #define PROTECT(x) (x)
 #define UNPROTECT(n) ((void)(n))
 
@@ -64,6 +70,7 @@ SEXP mock_real_matrix(const double* v, int nrow, int ncol);
 SEXP mock_string(const char* s);
 SEXP mock_logical(int v);
 void mock_reset(void);                 /* frees everything allocated since the last reset */
+int mock_gc(void);                     /* runs the finalizers of all external pointers and frees them; returns how many ran */
 
 #ifdef __cplusplus
 }

@@ -21,6 +21,9 @@ SEXP _signals_logspace_add_vec(SEXP, SEXP);
 SEXP _signals_postprocess(SEXP, SEXP);
 SEXP _signals_pass_stats(SEXP, SEXP, SEXP, SEXP, SEXP);
 SEXP _signals_device_count(void);
+SEXP _signals_cols_upload(SEXP, SEXP, SEXP, SEXP);
+SEXP _signals_cols_decode(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
+SEXP _signals_cols_free(SEXP);
 
 static int fail(char* err)
 {
@@ -165,3 +168,49 @@ int drv_decode_batch_timed(int model, const int* n, const int* x, const int* sta
     *checksum_out = cs;
     DONE();
 }
+
+/* ---- the table handle: upload once (handle returned to the caller as an opaque pointer), decode passes, free / gc */
+int drv_cols_upload(const int* n, const int* x, const int* state, long N, const double* seg_off, long nseg, int as_double,
+                    void** handle_out, double* nrows_out, char* err)
+{
+    GUARDED(err);
+    SEXP sn = mock_int_vector(n, N), sx = mock_int_vector(x, N), sc = mock_int_vector(state, N);
+    if (as_double) { sn = Rf_coerceVector(sn, REALSXP); sx = Rf_coerceVector(sx, REALSXP); sc = Rf_coerceVector(sc, REALSXP); }
+    SEXP r = _signals_cols_upload(sn, sx, sc, mock_real_vector(seg_off, nseg + 1));
+    if (TYPEOF(r) != VECSXP || XLENGTH(r) != 2 || TYPEOF(VECTOR_ELT(r, 0)) != EXTPTRSXP) Rf_error("driver: upload must return list(handle, nrows)");
+    *handle_out = (void*)VECTOR_ELT(r, 0);
+    *nrows_out = REAL(VECTOR_ELT(r, 1))[0];
+    DONE();
+}
+
+int drv_cols_decode(void* handle, double nrows, int model, const char* likelihood, int maxCN, double loherror, double eps, double rho,
+                    double Abias, double stp, double* path_out, char* err)
+{
+    GUARDED(err);
+    int mdl = model, mcn = maxCN;
+    SEXP r = _signals_cols_decode((SEXP)handle, Rf_ScalarReal(nrows), mock_int_vector(&mdl, 1), mock_string(likelihood),
+                                  mock_int_vector(&mcn, 1), Rf_ScalarReal(loherror), Rf_ScalarReal(eps), Rf_ScalarReal(rho),
+                                  Rf_ScalarReal(Abias), Rf_ScalarReal(stp));
+    if (TYPEOF(r) != REALSXP || (double)XLENGTH(r) != nrows) Rf_error("driver: decode must return a numeric vector of nrows");
+    memcpy(path_out, REAL(r), (size_t)XLENGTH(r) * sizeof(double));
+    DONE();
+}
+
+int drv_cols_free(void* handle, char* err)
+{
+    GUARDED(err);
+    _signals_cols_free((SEXP)handle);
+    DONE();
+}
+
+/* a scalar where a handle is expected (argument checking) */
+int drv_cols_decode_bad_handle(char* err)
+{
+    GUARDED(err);
+    int one = 1;
+    _signals_cols_decode(Rf_ScalarReal(1.0), Rf_ScalarReal(1.0), mock_int_vector(&one, 1), mock_string("binomial"), mock_int_vector(&one, 1),
+                         Rf_ScalarReal(0.02), Rf_ScalarReal(1e-12), Rf_ScalarReal(0.0), Rf_ScalarReal(0.0), Rf_ScalarReal(0.95));
+    DONE();
+}
+
+int drv_gc(void) { return mock_gc(); }

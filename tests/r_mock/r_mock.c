@@ -187,3 +187,40 @@ int R_useDynamicSymbols(DllInfo* info, int value)
     mock_dynamic_symbols = value;
     return 1;
 }
+
+/* ---- external pointers: persistent (a handle lives across .Call invocations), finalized by mock_gc() */
+#define MOCK_MAX_EXTPTR 64
+static SEXP g_ext[MOCK_MAX_EXTPTR];
+static R_CFinalizer_t g_fin[MOCK_MAX_EXTPTR];
+SEXP R_MakeExternalPtr(void* p, SEXP tag, SEXP prot)
+{
+    (void)tag; (void)prot;
+    for (int i = 0; i < MOCK_MAX_EXTPTR; i++)
+        if (!g_ext[i]) {
+            SEXP s = (SEXP)calloc(1, sizeof(struct mock_sexp));
+            s->type = EXTPTRSXP; s->len = 1; s->data = p; s->dim = R_NilValue;
+            g_ext[i] = s; g_fin[i] = NULL;
+            return s;
+        }
+    Rf_error("mock: too many external pointers");
+    return R_NilValue;
+}
+void* R_ExternalPtrAddr(SEXP s) { return s->type == EXTPTRSXP ? s->data : NULL; }
+void R_ClearExternalPtr(SEXP s) { if (s->type == EXTPTRSXP) s->data = NULL; }
+void R_RegisterCFinalizerEx(SEXP s, R_CFinalizer_t fun, int onexit)
+{
+    (void)onexit;
+    for (int i = 0; i < MOCK_MAX_EXTPTR; i++)
+        if (g_ext[i] == s) g_fin[i] = fun;
+}
+int mock_gc(void)
+{
+    int ran = 0;
+    for (int i = 0; i < MOCK_MAX_EXTPTR; i++)
+        if (g_ext[i]) {
+            if (g_fin[i]) { g_fin[i](g_ext[i]); ran++; }
+            free(g_ext[i]);
+            g_ext[i] = NULL; g_fin[i] = NULL;
+        }
+    return ran;
+}

@@ -570,3 +570,50 @@ def test_typed_columns_pageable_and_pinned(oracle, monkeypatch):
     with pytest.raises(hmm.SignalsB200Error, match="not an integer|2\\^28"):
         hmm.decode_arrays(bad, x, cn, so, **_kw(ps))
     assert np.array_equal(hmm.decode_arrays(n, x, cn, so, **_kw(ps)), ref)       # and the library still works
+
+
+@pytest.mark.gpu
+def test_resident_columns_several_passes_one_upload(oracle, sched):
+    """sgb_cols_*: the table goes to the device once, then every pass of the reference's workflow (R/callHSCN.R:883-935:
+    binomial at the default loherror, then the inferred loherror / beta-binomial; R/callASCN.R:372-414) decodes the resident
+    columns -- each pass must give the oracle's paths, for any element type of the columns and of the result."""
+    d = cases.small_cohort("betabinomial", n_cells=90, seed=41)
+    n, x, cn, so = d["n"], d["x"], d["cn"], d["seg_off"]
+    passes = [cases.PARAM_SETS[0], cases.PARAM_SETS[2], cases.PARAM_SETS[4], cases.PARAM_SETS[11], cases.PARAM_SETS[5]]
+    refs = [oracle.decode_batch(n, x, cn.astype(np.int32), so, oracle.params(**cases.param_dict(ps)), oracle.MATH_DET, nthreads=4)
+            for ps in passes]
+    for tn, tx, tc in ((np.int32, np.int32, np.int32), (np.float64, np.float64, np.float64), (np.int32, np.int32, np.uint8),
+                       (np.uint16, np.float64, np.int32)):
+        with hmm.ResidentColumns(n.astype(tn), x.astype(tx), cn.astype(tc), so) as cols:
+            for ps, ref in zip(passes, refs):
+                for out_dtype in (np.uint8, np.float64):
+                    got = cols.decode(out_dtype=out_dtype, **_kw(ps))
+                    assert got.dtype == np.dtype(out_dtype) and np.array_equal(got.astype(np.uint8), ref), (ps[0], tn, out_dtype)
+            # chained decode on the same columns (the plan is rebuilt with backpointer scratch), then reference again
+            ch = cols.decode(decode="chained", **_kw(passes[0]))
+            ref_ch = oracle.decode_batch(n, x, cn.astype(np.int32), so, oracle.params(decode="chained", **cases.param_dict(passes[0])),
+                                         oracle.MATH_DET, nthreads=4)
+            assert np.array_equal(ch, ref_ch)
+            assert np.array_equal(cols.decode(**_kw(passes[0])), refs[0])
+    # validation: what the conversion can see fails the upload, what only the device sees fails the pass
+    bad = n.astype(np.float64); bad[11] = np.nan
+    with pytest.raises(hmm.SignalsB200Error, match="not an integer"):
+        hmm.ResidentColumns(bad, x, cn, so)
+    bad = cn.astype(np.int32); bad[11] = 700
+    with pytest.raises(hmm.SignalsB200Error, match="copy-number"):
+        hmm.ResidentColumns(n, x, bad, so)
+    bad = n.copy(); bad[11] = -4
+    cols = hmm.ResidentColumns(bad, x, cn, so)
+    with pytest.raises(hmm.SignalsB200Error, match="negative"):
+        cols.decode(**_kw(passes[0]))
+    cols.close()
+    with pytest.raises(hmm.SignalsB200Error, match="released"):
+        cols.decode(**_kw(passes[0]))
+    # empty table and a table whose sequences do not cover every row
+    e = hmm.ResidentColumns(np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.uint8), np.zeros(1, np.int64))
+    assert e.decode(**_kw(passes[0])).size == 0
+    e.close()
+    so2 = so[: so.size // 2].copy()
+    with hmm.ResidentColumns(n, x, cn, so2) as cols:
+        got = cols.decode(**_kw(passes[0]))
+        assert np.array_equal(got[: so2[-1]], refs[0][: so2[-1]]) and not got[so2[-1]:].any()

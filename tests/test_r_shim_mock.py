@@ -40,6 +40,13 @@ def shim():
     lib.drv_postprocess.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_char_p]
     lib.drv_pass_stats.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_long, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_char_p]
     lib.drv_device_count.argtypes = [ctypes.POINTER(ctypes.c_int), ctypes.c_char_p]
+    lib.drv_cols_upload.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p, ctypes.c_long,
+                                    ctypes.c_int, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_double), ctypes.c_char_p]
+    lib.drv_cols_decode.argtypes = [ctypes.c_void_p, ctypes.c_double, ctypes.c_int, ctypes.c_char_p, ctypes.c_int] + \
+                                   [ctypes.c_double] * 5 + [ctypes.c_void_p, ctypes.c_char_p]
+    lib.drv_cols_free.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
+    lib.drv_cols_decode_bad_handle.argtypes = [ctypes.c_char_p]
+    lib.drv_gc.restype = ctypes.c_int
     return lib
 
 
@@ -67,10 +74,13 @@ def test_shim_compiles_and_registers_the_reference_routines(shim):
     assert got["_signals_hmm_decode_batch"] == 14
     assert got["_signals_logspace_add_vec"] == 2 and got["_signals_postprocess"] == 2 and got["_signals_pass_stats"] == 5
     assert got["_signals_device_count"] == 0
+    assert got["_signals_cols_upload"] == 4 and got["_signals_cols_decode"] == 10 and got["_signals_cols_free"] == 1
     assert dyn.value == 0                         # R_useDynamicSymbols(dll, FALSE), as the reference does
 
 
 def test_shim_argument_errors_unwind_like_rf_error(shim):
+    err = ctypes.create_string_buffer(1024)
+    assert shim.drv_cols_decode_bad_handle(err) == 1 and "handle must come from the table upload" in err.value.decode()
     n = np.array([10, 12], np.int32); seg = np.array([0, 2])
     rc, msg, _, _ = _decode(shim, 0, n, n // 2, [2, 2], seg, lik="poisson")
     assert rc == 1 and "binomial or betabinomial" in msg          # R/callHSCN.R:778-780
@@ -156,3 +166,41 @@ def test_shim_results_equal_the_oracle(shim, oracle):
     assert np.array_equal(hist.reshape(12, 12).T, h)          # R matrix [A+1, B+1], column-major
     k = ctypes.c_int(0)
     assert shim.drv_device_count(ctypes.byref(k), err) == 0 and k.value >= 1
+
+
+@pytest.mark.gpu
+def test_shim_table_handle_two_passes_one_upload(shim, oracle):
+    """_signals_cols_upload / _decode / _free: the workflow of callHaplotypeSpecificCN (pass 1 binomial at the default
+    loherror, pass 2 at the inferred one / beta-binomial, R/callHSCN.R:883-935) on ONE upload of the three columns, INTSXP
+    and REALSXP alike; every pass equals the oracle; a released handle is refused; an un-freed handle is collected by the
+    finalizer."""
+    d = cases.small_cohort("betabinomial", n_cells=25, seed=19)
+    n, x, cn, so = d["n"], d["x"], d["cn"].astype(np.int32), d["seg_off"]
+    segd = so.astype(np.float64)
+    passes = [cases.PARAM_SETS[0], cases.PARAM_SETS[2], cases.PARAM_SETS[4]]
+    err = ctypes.create_string_buffer(1024)
+    for as_double in (0, 1):
+        h = ctypes.c_void_p(); nr = ctypes.c_double(0.0)
+        assert shim.drv_cols_upload(n.ctypes.data, x.ctypes.data, cn.ctypes.data, n.size, segd.ctypes.data, segd.size - 1, as_double,
+                                    ctypes.byref(h), ctypes.byref(nr), err) == 0, err.value
+        assert nr.value == n.size and h.value
+        for ps in passes:
+            pd = cases.param_dict(ps)
+            ref = oracle.decode_batch(n, x, cn, so, oracle.params(**pd), oracle.MATH_DET, nthreads=4)
+            path = np.zeros(n.size, np.float64)
+            rc = shim.drv_cols_decode(h, nr.value, 1 if pd["model"] == "ascn" else 0, pd["likelihood"].encode(), pd["S"] - 1, pd["loherror"],
+                                      pd["eps"], pd["rho"], pd["Abias"], pd["selftransitionprob"], path.ctypes.data, err)
+            assert rc == 0, err.value
+            assert np.array_equal(path, ref.astype(np.float64)), ps[0]
+        if as_double == 0:
+            assert shim.drv_cols_free(h, err) == 0
+            path = np.zeros(n.size, np.float64)
+            assert shim.drv_cols_decode(h, nr.value, 0, b"binomial", 11, 0.02, 1e-12, 0.0, 0.0, 0.95, path.ctypes.data, err) == 1
+            assert "released" in err.value.decode()
+    assert shim.drv_gc() >= 1          # the second handle was never freed: its finalizer runs at collection
+    # a bad column fails the upload with the library's message
+    bad = n.copy(); bad[3] = -2147483648      # NA_integer_
+    h = ctypes.c_void_p(); nr = ctypes.c_double(0.0)
+    assert shim.drv_cols_upload(bad.ctypes.data, x.ctypes.data, cn.ctypes.data, n.size, segd.ctypes.data, segd.size - 1, 1,
+                                ctypes.byref(h), ctypes.byref(nr), err) == 1
+    assert "signals_b200" in err.value.decode()
