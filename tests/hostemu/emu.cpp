@@ -120,7 +120,7 @@ extern "C" int emu_decode_sequence(int model, int lik, int S, int decode, double
 // count of the sequence) states.
 template <int NPL, int MODEL, int LIKBB>
 static void run_split(int S, double loherror, double eps, double rho, double Abias, double stp, long T, const int* n,
-                      const int* x, const int* cn, unsigned char* out)
+                      const int* x, const int* cn, unsigned char* out, int block)
 {
     constexpr int NL = 4 * NPL;
     const int lik = LIKBB ? SGB_LIK_BETABINOMIAL : SGB_LIK_BINOMIAL;
@@ -145,13 +145,66 @@ static void run_split(int S, double loherror, double eps, double rho, double Abi
     double T1[NL], m1 = 0.0;
     SgbSeqState<NL> st;
     const int Seff = S < NL ? S : NL;
-    for (long t = 0; t < T; t++) {
+    auto emit = [&](long t, double (&e)[NL]) {
         SgbBin b = sgb_bin_prepare(MODEL, LIKBB, n[t], x[t], cn[t], sp.bb_s, LF, LT);
         const int L = sgb_live_states(MODEL, b.cprime, S);
-        double e[NL];
         for (int m = 0; m < NL; m++)
             e[m] = m < L ? sgb_emit_item<MODEL, LIKBB>(b.cprime, b.in_support, b.kd, b.nkd, b.lc_x, b.lc_y, b.lg_sn, m, TB, sp)
                          : -sgb_inf();
+    };
+    if (block && sp.diag_dominant) {
+        // k_recur's variant for large batches: chunk 0 one step at a time, every later chunk of four bins with the
+        // branch-free step; a chunk in which some step flags a possible off-diagonal predecessor is redone from the column
+        // it started with -- the full step where flagged, the lean one elsewhere, up to the last flagged step.  Bins past
+        // the end of the sequence ride along on garbage exactly as the lanes of a shorter sequence do (here: clamped reads).
+        int lastback = 0;
+        for (long c = 0; 4 * c < T; c++) {
+            if (c == 0) {
+                for (long t = 0; t < 4 && t < T; t++) {
+                    double e[NL];
+                    emit(t, e);
+                    int back = 0;
+                    if (t == 0) sgb_seq_init_r<NL>(T1, e, sp.init, m1);
+                    else back = sgb_seq_step_r<NL>(T1, e, m1, sp.tr_self, sp.tr_off);
+                    if (t > 0) out[t - 1] = (unsigned char)back;
+                    if (t == T - 1) lastback = back;
+                }
+                continue;
+            }
+            double T1s[NL];
+            for (int i = 0; i < NL; i++) T1s[i] = T1[i];
+            const double m1s = m1;
+            int back[4];
+            unsigned ties = 0;
+            for (int b = 0; b < 4; b++) {
+                const long t = 4 * c + b;
+                double e[NL];
+                emit(t < T ? t : T - 1, e);
+                bool tie;
+                back[b] = sgb_seq_step_fast<NL>(T1, e, m1, sp.tr_self, sp.tr_off, tie);
+                if (tie && t < T) ties |= 1u << b;
+            }
+            if (ties) {
+                double m1r = m1s;
+                for (int b = 0; (ties >> b) != 0; b++) {
+                    double e[NL];
+                    emit(4 * c + b, e);
+                    if ((ties >> b) & 1u) back[b] = sgb_seq_step_r<NL>(T1s, e, m1r, sp.tr_self, sp.tr_off);
+                    else { bool t_; sgb_seq_step_fast<NL>(T1s, e, m1r, sp.tr_self, sp.tr_off, t_); }
+                }
+            }
+            for (int b = 0; b < 4; b++) {
+                const long t = 4 * c + b;
+                if (t < T) out[t - 1] = (unsigned char)back[b];
+                if (t == T - 1) lastback = back[b];
+            }
+        }
+        out[T - 1] = (unsigned char)lastback;
+        return;
+    }
+    for (long t = 0; t < T; t++) {
+        double e[NL];
+        emit(t, e);
         int back = 0;
         if (sp.diag_dominant) {
             if (t == 0) sgb_seq_init_r<NL>(T1, e, sp.init, m1);
@@ -167,16 +220,16 @@ static void run_split(int S, double loherror, double eps, double rho, double Abi
 
 template <int NPL>
 static void run_split_s(int model, int lik_bb, int S, double loherror, double eps, double rho, double Abias, double stp, long T,
-                        const int* n, const int* x, const int* cn, unsigned char* out)
+                        const int* n, const int* x, const int* cn, unsigned char* out, int block)
 {
-    if (model == 0 && !lik_bb) run_split<NPL, 0, 0>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out);
-    else if (model == 0) run_split<NPL, 0, 1>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out);
-    else if (!lik_bb) run_split<NPL, 1, 0>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out);
-    else run_split<NPL, 1, 1>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out);
+    if (model == 0 && !lik_bb) run_split<NPL, 0, 0>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, block);
+    else if (model == 0) run_split<NPL, 0, 1>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, block);
+    else if (!lik_bb) run_split<NPL, 1, 0>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, block);
+    else run_split<NPL, 1, 1>(S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, block);
 }
 
-extern "C" int emu_decode_sequence_split(int model, int lik, int S, double loherror, double eps, double rho, double Abias,
-                                         double stp, long T, const int* n, const int* x, const int* cn, unsigned char* out)
+static int decode_split(int model, int lik, int S, double loherror, double eps, double rho, double Abias, double stp, long T,
+                        const int* n, const int* x, const int* cn, unsigned char* out, int block)
 {
     if (T <= 0) return 0;
     if (S < 1 || S > 32) return -1;
@@ -185,12 +238,25 @@ extern "C" int emu_decode_sequence_split(int model, int lik, int S, double loher
     for (long t = 0; t < T; t++) { int c = cn[t] < 0 ? 0 : (cn[t] > 255 ? 255 : cn[t]); if (c > mx) mx = c; }
     const int npl = sgb_planes_for(sgb_live_states(model, sgb_cprime(model, mx), S));
     switch (npl) {
-    case 1: run_split_s<1>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
-    case 2: run_split_s<2>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
-    case 3: run_split_s<3>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
-    case 4: run_split_s<4>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
-    case 6: run_split_s<6>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
-    default: run_split_s<8>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out); break;
+    case 1: run_split_s<1>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, block); break;
+    case 2: run_split_s<2>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, block); break;
+    case 3: run_split_s<3>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, block); break;
+    case 4: run_split_s<4>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, block); break;
+    case 6: run_split_s<6>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, block); break;
+    default: run_split_s<8>(model, lik_bb, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, block); break;
     }
     return 0;
+}
+
+extern "C" int emu_decode_sequence_split(int model, int lik, int S, double loherror, double eps, double rho, double Abias,
+                                         double stp, long T, const int* n, const int* x, const int* cn, unsigned char* out)
+{
+    return decode_split(model, lik, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, 0);
+}
+
+// the four-bin block variant of the recursion (k_recur for large batches; every plane count, the kernel uses it up to two planes)
+extern "C" int emu_decode_sequence_split_block(int model, int lik, int S, double loherror, double eps, double rho, double Abias,
+                                               double stp, long T, const int* n, const int* x, const int* cn, unsigned char* out)
+{
+    return decode_split(model, lik, S, loherror, eps, rho, Abias, stp, T, n, x, cn, out, 1);
 }

@@ -33,9 +33,11 @@ def _emu_decode(E, d, kw, decode):
         a, b = int(so[s]), int(so[s + 1])
         if b == a:
             continue
-        if decode == "split":
-            # the split schedule (k_emit + k_recur): plane-padded emissions + register-resident recursion
-            rc = E.emu_decode_sequence_split(1 if kw["model"] == "ascn" else 0, 1 if kw["likelihood"] == "betabinomial" else 0,
+        if decode in ("split", "split_block"):
+            # the split schedule (k_emit + k_recur): plane-padded emissions + register-resident recursion, one step at a
+            # time or in k_recur's branch-free four-bin blocks with the redo of flagged chunks
+            fn = E.emu_decode_sequence_split if decode == "split" else E.emu_decode_sequence_split_block
+            rc = fn(1 if kw["model"] == "ascn" else 0, 1 if kw["likelihood"] == "betabinomial" else 0,
                                              kw["S"], D(kw["loherror"]), D(kw["eps"]), D(kw["rho"]), D(kw["Abias"]),
                                              D(kw["selftransitionprob"]), ctypes.c_long(b - a),
                                              n[a:b].ctypes.data_as(ctypes.c_void_p), x[a:b].ctypes.data_as(ctypes.c_void_p),
@@ -59,7 +61,7 @@ def test_core_bit_exact_vs_oracle(oracle, emu, ps):
     d = cases.small_cohort("betabinomial" if kw["likelihood"] == "betabinomial" else "binomial", n_cells=4, seed=3)
     n = np.concatenate((n, d["n"])); x = np.concatenate((x, d["x"])); cn = np.concatenate((cn, d["cn"].astype(np.int32)))
     seg = np.concatenate((seg, seg[-1] + d["seg_off"][1:]))
-    for decode, dname in ((0, "reference"), (1, "chained"), ("split", "reference")):
+    for decode, dname in ((0, "reference"), (1, "chained"), ("split", "reference"), ("split_block", "reference")):
         P = oracle.params(**kw, decode=dname)
         ref = oracle.decode_batch(n, x, cn, seg, P, oracle.MATH_DET)
         got = _emu_decode(emu, (n, x, cn, seg), kw, decode)
@@ -73,7 +75,7 @@ def test_core_bit_exact_on_randomised_cases(oracle, emu, seed):
     kw = dict(model=g["model"], likelihood=g["likelihood"], S=g["n_states"], loherror=g["loherror"], eps=g["eps"],
               rho=g["rho"], Abias=g["Abias"], selftransitionprob=g["selftransitionprob"])
     cn = cn.astype(np.int32)
-    for decode, dname in ((0, "reference"), (1, "chained"), ("split", "reference")):
+    for decode, dname in ((0, "reference"), (1, "chained"), ("split", "reference"), ("split_block", "reference")):
         ref = oracle.decode_batch(n, x, cn, seg, oracle.params(**kw, decode=dname), oracle.MATH_DET)
         got = _emu_decode(emu, (n, x, cn, seg), kw, decode)
         assert np.array_equal(ref, got), (kw, decode, np.nonzero(ref != got)[0][:8])
