@@ -111,17 +111,28 @@ __global__ void __launch_bounds__(256) k_rs_hist(const unsigned long long* __res
     hist[(long long)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 // One block scatters its tile in order: warp w owns elements [w * 256, (w + 1) * 256) of the tile, processed in 8 rounds of
-// 32; the rank of an element among the tile's earlier elements with the same digit keeps the sort stable.
+// 32; the rank of an element among the tile's earlier elements with the same digit keeps the sort stable.  The tile is
+// first put in digit order in shared memory and then written out by consecutive threads, so that the ~8 elements a tile holds
+// of each digit leave as one contiguous run (a store straight from the registers touched up to 32 sectors per instruction with
+// 8 or 4 useful bytes each).
 __global__ void __launch_bounds__(256) k_rs_scatter(const unsigned long long* __restrict__ keys, const unsigned* __restrict__ vals,
-                                                    long long n, int shift, const unsigned* __restrict__ offs /* scanned hist */,
+                                                    long long n, int shift, const unsigned* __restrict__ offs /* hist scanned inside its scan tiles */,
+                                                    const unsigned* __restrict__ tile_offs /* scanned sums of those tiles */,
                                                     int nblocks, unsigned long long* __restrict__ keys_out, unsigned* __restrict__ vals_out)
 {
-    __shared__ unsigned cnt[8][RS_BINS];          // per warp, per digit: elements of this warp
+    __shared__ unsigned cnt[8][RS_BINS];          // per warp, per digit: elements of this warp, then their start inside the digit's run
+    __shared__ unsigned lstart[RS_BINS];          // start of the digit's run inside the tile
+    __shared__ unsigned gbase[RS_BINS];           // start of the digit's run in the output
+    __shared__ unsigned wsum[8];
+    __shared__ unsigned long long keyS[RS_TILE];
+    __shared__ unsigned valS[RS_TILE];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < 8 * RS_BINS; i += 256) (&cnt[0][0])[i] = 0;
     __syncthreads();
-    const long long tbase = (long long)blockIdx.x * RS_TILE + wid * 256;
+    const long long tile0 = (long long)blockIdx.x * RS_TILE;
+    const long long tbase = tile0 + wid * 256;
     unsigned long long k[8];
+    unsigned v[8];
     unsigned dg[8], rk[8];
     // pass 1: ranks inside the warp's 256 elements
 #pragma unroll
@@ -129,6 +140,7 @@ __global__ void __launch_bounds__(256) k_rs_scatter(const unsigned long long* __
         const long long j = tbase + r * 32 + lane;
         const bool ok = j < n;
         k[r] = ok ? keys[j] : 0ull;
+        v[r] = ok ? vals[j] : 0u;
         dg[r] = ok ? ((unsigned)(k[r] >> shift) & 255u) : 0xffffffffu;
         const unsigned m = __match_any_sync(SGB_FULL, dg[r]);
         const unsigned before = __popc(m & ((1u << lane) - 1u));
@@ -140,21 +152,43 @@ __global__ void __launch_bounds__(256) k_rs_scatter(const unsigned long long* __
         rk[r] = prior + before;
     }
     __syncthreads();
-    // digit d of this block starts at offs[d][block]; warp w's elements follow those of warps < w
+    // digit d: its elements of warp w follow those of warps < w; its run starts after the runs of the smaller digits
     {
         const int d = threadIdx.x;
-        unsigned run = offs[(long long)d * nblocks + blockIdx.x];
-        for (int w = 0; w < 8; w++) { const unsigned c = cnt[w][d]; cnt[w][d] = run; run += c; }
+        unsigned tot = 0;
+        for (int w = 0; w < 8; w++) { const unsigned c = cnt[w][d]; cnt[w][d] = tot; tot += c; }
+        unsigned incl = tot;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const unsigned u = __shfl_up_sync(SGB_FULL, incl, s);
+            if (lane >= s) incl += u;
+        }
+        if (lane == 31) wsum[wid] = incl;
+        __syncthreads();
+        unsigned woff = 0;
+        for (int w = 0; w < wid; w++) woff += wsum[w];
+        lstart[d] = woff + incl - tot;
+        const long long hi = (long long)d * nblocks + blockIdx.x;
+        gbase[d] = offs[hi] + tile_offs[hi / SCAN_TILE];        // (the scan's last pass, folded in: one launch less per digit)
     }
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < 8; r++) {
-        const long long j = tbase + r * 32 + lane;
-        if (j < n) {
-            const unsigned pos = cnt[wid][dg[r]] + rk[r];
-            keys_out[pos] = k[r];
-            vals_out[pos] = vals[j];
+        if (dg[r] != 0xffffffffu) {
+            const unsigned lp = lstart[dg[r]] + cnt[wid][dg[r]] + rk[r];
+            keyS[lp] = k[r];
+            valS[lp] = v[r];
         }
+    }
+    __syncthreads();
+    const long long left = n - tile0;
+    const int ntile = left < RS_TILE ? (int)left : RS_TILE;
+    for (int i = threadIdx.x; i < ntile; i += 256) {
+        const unsigned long long kk = keyS[i];
+        const unsigned d = (unsigned)(kk >> shift) & 255u;
+        const unsigned pos = gbase[d] + ((unsigned)i - lstart[d]);
+        keys_out[pos] = kk;
+        vals_out[pos] = valS[i];
     }
 }
 // sorts n (key, value) pairs by the key bits [bit_lo, bit_hi); ping-pongs between (k0, v0) and (k1, v1); returns in *which
@@ -170,9 +204,11 @@ static cudaError_t radix_sort(unsigned long long* k0, unsigned* v0, unsigned lon
         unsigned long long* ki = cur ? k1 : k0; unsigned* vi = cur ? v1 : v0;
         unsigned long long* ko = cur ? k0 : k1; unsigned* vo = cur ? v0 : v1;
         k_rs_hist<<<nblocks, 256, 0, st>>>(ki, n, shift, hist, nblocks);
-        cudaError_t e = scan_u32(hist, hist, (long long)RS_BINS * nblocks, tile_sums, nullptr, st);
-        if (e != cudaSuccess) return e;
-        k_rs_scatter<<<nblocks, 256, 0, st>>>(ki, vi, n, shift, hist, nblocks, ko, vo);
+        const long long nh = (long long)RS_BINS * nblocks;
+        const int nt = (int)((nh + SCAN_TILE - 1) / SCAN_TILE);
+        k_scan_tiles<<<nt, 256, 0, st>>>(hist, hist, nh, tile_sums);
+        k_scan_sums<<<1, 1024, 0, st>>>(tile_sums, nt, nullptr);
+        k_rs_scatter<<<nblocks, 256, 0, st>>>(ki, vi, n, shift, hist, tile_sums, nblocks, ko, vo);
         cur ^= 1;
     }
     *which = cur;
@@ -181,11 +217,22 @@ static cudaError_t radix_sort(unsigned long long* k0, unsigned* v0, unsigned lon
 static int bits_for(long long maxval) { int b = 1; while (b < 63 && (1ll << b) <= maxval) b++; return b; }
 
 // ------------------------------------------------------------------ table order + combine
-// key = cell << (cb + 32) | chr << 32 | start  (cb = bits of the chromosome code); rows failing the filter (or with a bad
+// key = cell << (cb + sb) | chr << sb | start  (cb = bits of the chromosome code, sb = bits of the largest start in the
+// table: 28 for a human genome, which saves one 8-bit radix pass against a fixed 32); rows failing the filter (or with a bad
 // key) get the DROP bit above the key bits and so sort last
+__global__ void __launch_bounds__(256) k_tab_maxstart(const int32_t* __restrict__ start, long long n, int* __restrict__ out)
+{
+    int m = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int s = start[i];
+        m = s > m ? s : m;
+    }
+    m = __reduce_max_sync(SGB_FULL, m);
+    if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
+}
 __global__ void __launch_bounds__(256) k_tab_keys(const int32_t* __restrict__ cell, const int32_t* __restrict__ chr,
                                                   const int32_t* __restrict__ start, const int32_t* __restrict__ total, double filtern,
-                                                  int use_filter, long long n, int chr_bits, int drop_bit, int ncell, int nchr,
+                                                  int use_filter, long long n, int chr_bits, int start_bits, int drop_bit, int ncell, int nchr,
                                                   unsigned long long* __restrict__ keys, unsigned* __restrict__ idx, int* err)
 {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -193,7 +240,7 @@ __global__ void __launch_bounds__(256) k_tab_keys(const int32_t* __restrict__ ce
         unsigned long long key;
         const unsigned long long DROP = 1ull << drop_bit;
         if ((unsigned)c >= (unsigned)ncell || (unsigned)h >= (unsigned)nchr || s < 0) { atomicOr(err, SGB_ERR_BAD_KEY); key = DROP; }
-        else key = ((unsigned long long)(unsigned)c << (chr_bits + 32)) | ((unsigned long long)(unsigned)h << 32) | (unsigned)s;
+        else key = ((unsigned long long)(unsigned)c << (chr_bits + start_bits)) | ((unsigned long long)(unsigned)h << start_bits) | (unsigned)s;
         if (use_filter && !((double)total[i] > filtern)) key |= DROP;             // .[totalcounts > filtern]
         keys[i] = key;
         idx[i] = (unsigned)i;
@@ -281,10 +328,11 @@ __global__ void __launch_bounds__(256) k_tab_compact(long long ng, const unsigne
     }
 }
 // table order only: perm = idx, sequence heads where (cell, chr) changes
-__global__ void __launch_bounds__(256) k_tab_seqheads(const unsigned long long* __restrict__ keys, long long n, unsigned* __restrict__ sflag)
+__global__ void __launch_bounds__(256) k_tab_seqheads(const unsigned long long* __restrict__ keys, long long n, int start_bits,
+                                                      unsigned* __restrict__ sflag)
 {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-        sflag[i] = (i == 0 || (keys[i - 1] >> 32) != (keys[i] >> 32)) ? 1u : 0u;
+        sflag[i] = (i == 0 || (keys[i - 1] >> start_bits) != (keys[i] >> start_bits)) ? 1u : 0u;
 }
 __global__ void __launch_bounds__(256) k_tab_segwrite(const unsigned* __restrict__ sflag, const unsigned* __restrict__ spos, long long n,
                                                       long long* __restrict__ seg_off)
@@ -347,17 +395,25 @@ cudaError_t sgbk_table(long long n, const int32_t* d_cell, const int32_t* d_chr,
     unsigned char* keep = cv.take<unsigned char>((size_t)ncell);
     unsigned long long* d_tot = cv.take<unsigned long long>(4);
     const int chr_bits = bits_for(nchr - 1 > 0 ? nchr - 1 : 1);
-    const int key_bits = 32 + chr_bits + bits_for(ncell - 1 > 0 ? ncell - 1 : 1);
+    cudaError_t e;
+    // the largest start decides how many key bits (and radix passes) the position needs
+    int* d_maxstart = (int*)(d_tot + 3);
+    int maxstart = 0;
+    if ((e = cudaMemsetAsync(d_maxstart, 0, sizeof(int), st)) != cudaSuccess) return e;
+    k_tab_maxstart<<<grid_for(n), 256, 0, st>>>(d_start, n, d_maxstart);
+    if ((e = cudaMemcpyAsync(&maxstart, d_maxstart, sizeof(int), cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+    if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
+    const int start_bits = bits_for(maxstart > 1 ? maxstart : 1);
+    const int key_bits = start_bits + chr_bits + bits_for(ncell - 1 > 0 ? ncell - 1 : 1);
     if (key_bits > 62) return cudaErrorInvalidValue;
     const int drop_bit = key_bits;
-    cudaError_t e;
-    k_tab_keys<<<grid_for(n), 256, 0, st>>>(d_cell, d_chr, d_start, d_n, filtern, do_combine, n, chr_bits, drop_bit, ncell, nchr, k0, v0, d_err);
+    k_tab_keys<<<grid_for(n), 256, 0, st>>>(d_cell, d_chr, d_start, d_n, filtern, do_combine, n, chr_bits, start_bits, drop_bit, ncell, nchr, k0, v0, d_err);
     int which = 0;
     if ((e = radix_sort(k0, v0, k1, v1, n, 0, key_bits + 1, hist, tsum, &which, st)) != cudaSuccess) return e;
     unsigned long long* ks = which ? k1 : k0; unsigned* vs = which ? v1 : v0;
     if (!do_combine) {
         if ((e = cudaMemcpyAsync(o_first, vs, N * 4, cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
-        k_tab_seqheads<<<grid_for(n), 256, 0, st>>>(ks, n, f0);
+        k_tab_seqheads<<<grid_for(n), 256, 0, st>>>(ks, n, start_bits, f0);
         if ((e = scan_u32(f0, f1, n, tsum, d_tot, st)) != cudaSuccess) return e;
         k_tab_segwrite<<<grid_for(n), 256, 0, st>>>(f0, f1, n, o_seg_off);
         unsigned long long nseg = 0;

@@ -24,7 +24,7 @@ def bits(v):
     b = 1
     while (1 << b) <= v: b += 1
     return b
-key_bits = 32 + bits(22) + bits(n_cells - 1) + 1
+key_bits = bits(int(pos.max())) + bits(22) + bits(n_cells - 1) + 1       # position field sized from the largest start
 passes = (key_bits + 7) // 8
 # per pass: histogram read (8 B key) + scatter read (8 + 4) + scatter write (8 + 4) = 32 B per row; + keys written once (12 B) and inputs read (12 B)
 alg = N * (passes * 32 + 24)
