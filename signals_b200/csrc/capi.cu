@@ -1536,7 +1536,7 @@ int sgb_fix_assignments(int64_t N, const int32_t* state, const int32_t* A, const
     if (get_ctx(&C)) return 1;
     cudaStream_t st = C->main;
     const size_t n4 = ((size_t)N * 4 + 255) & ~(size_t)255, n1 = ((size_t)N + 255) & ~(size_t)255;
-    if (C->scratch_a.reserve(9 * n4 + n1 + 512)) return 1;
+    if (C->scratch_a.reserve(9 * n4 + n1 + 512) || C->scratch_b.reserve(sgbk_fix_scratch_bytes(N))) return 1;
     std::vector<uint8_t> head((size_t)N, 0);
     for (int64_t s = 0; s < nseg; s++) {
         if (seg_off[s + 1] < seg_off[s]) return fail("seg_off must be non-decreasing");
@@ -1550,7 +1550,7 @@ int sgb_fix_assignments(int64_t N, const int32_t* state, const int32_t* A, const
     for (int k = 0; k < 5; k++) SGB_CUDA(cudaMemcpyAsync(d[k], hin[k], (size_t)N * 4, cudaMemcpyHostToDevice, st));
     SGB_CUDA(cudaMemcpyAsync(d_head, head.data(), (size_t)N, cudaMemcpyHostToDevice, st));
     SGB_CUDA(sgbk_fix_assignments(d[0], d[1], d[2], d[3], d[4], d_head, N, loherror, likelihood == SGB_LIK_BETABINOMIAL && rho > 0.0, rho,
-                                  d[5], d[6], d[7], d[8], st));
+                                  d[5], d[6], d[7], d[8], C->scratch_b.p, st));
     SGB_CUDA(cudaMemcpyAsync(A_out, d[7], (size_t)N * 4, cudaMemcpyDeviceToHost, st));
     SGB_CUDA(cudaMemcpyAsync(B_out, d[8], (size_t)N * 4, cudaMemcpyDeviceToHost, st));
     SGB_CUDA(cudaStreamSynchronize(st));

@@ -144,4 +144,5 @@ cudaError_t sgbk_qc_per_cell(const int32_t* d_n, const int32_t* d_x, const void*
                              const int32_t* d_cell_of_row, long long N, int ncell, void* d_scratch, double* d_avg, int* d_err, cudaStream_t st);
 cudaError_t sgbk_fix_assignments(const int32_t* d_state, const int32_t* d_A, const int32_t* d_B, const int32_t* d_alleleA,
                                  const int32_t* d_alleleB, const uint8_t* d_seqhead, long long N, double loherror, int lik_bb, double rho,
-                                 int32_t* d_A1, int32_t* d_B1, int32_t* d_A2, int32_t* d_B2, cudaStream_t st);
+                                 int32_t* d_A1, int32_t* d_B1, int32_t* d_A2, int32_t* d_B2, void* d_scratch, cudaStream_t st);
+size_t sgbk_fix_scratch_bytes(long long N);
