@@ -587,37 +587,62 @@ __global__ void __launch_bounds__(256) k_qc_gather(const unsigned long long* __r
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (long long)gridDim.x * blockDim.x) out[i] = kgrp[idx[i]];
 }
 // kg: group keys sorted (rows of a cell contiguous, groups inside it contiguous, BAF ascending inside a group);
-// rows[i]: the table row at sorted position i.  One thread per cell head walks the cell's rows once.
+// rows[i]: the table row at sorted position i.  One WARP per cell: its row range comes from two binary searches on the
+// sorted keys, the lanes scan it 32 rows at a time for group boundaries, and the (few) groups are closed in order with the
+// arithmetic of the reference -- every lane computes the same values.  (One thread per cell walking ~5,700 rows took 2.5 ms
+// for 4,000 cells.)
+__device__ __forceinline__ long long qc_lower_bound(const unsigned long long* __restrict__ kg, long long N, unsigned long long cellkey)
+{
+    long long lo = 0, hi = N;                       // first i with (kg[i] >> 16) >= cellkey; dropped rows carry a bit above the cell bits
+    while (lo < hi) {
+        const long long mid = (lo + hi) >> 1;
+        if ((kg[mid] >> 16) < cellkey) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
 __global__ void __launch_bounds__(128) k_qc_cells(const unsigned long long* __restrict__ kg, const unsigned* __restrict__ rows,
-                                                  const unsigned long long* __restrict__ kbaf, long long N, int drop_bit,
+                                                  const unsigned long long* __restrict__ kbaf, long long N, int ncell,
                                                   const unsigned long long* __restrict__ ntot, double* __restrict__ avg)
 {
     const double ntd = (double)*ntot;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (long long)gridDim.x * blockDim.x) {
-        const unsigned long long g0 = kg[i];
-        if ((g0 >> drop_bit) & 1ull) continue;
-        const unsigned long long cell = g0 >> 16;
-        if (i > 0 && (kg[i - 1] >> 16) == cell && !((kg[i - 1] >> drop_bit) & 1ull)) continue;      // not the cell's first row
-        double num = 0.0, den = 0.0;
-        long long j = i;
-        while (j < N && (kg[j] >> 16) == cell && !((kg[j] >> drop_bit) & 1ull)) {
-            const unsigned long long g = kg[j];
-            long long e = j;
-            while (e < N && kg[e] == g) e++;
-            const long long cnt = e - j;
-            if (cnt > 10) {                                             // dplyr::filter(n > 10)
-                const double lo = sgb_u2d(kbaf[rows[j + (cnt - 1) / 2]]), hi = sgb_u2d(kbaf[rows[j + cnt / 2]]);
-                const double med = sgb_mul(sgb_add(lo, hi), 0.5);       // R's median: mean of the two middle values
-                const int ab = (int)(g & 0xffffull), a = ab >> 8, b = ab & 255;
-                const double d = sgb_fabs(sgb_sub(sgb_div((double)b, (double)(a + b)), med));      // sqrt((expBAF - medianBAF)^2)
-                const double frac = sgb_div((double)cnt, ntd);
-                num = sgb_add(num, sgb_mul(d, frac));
-                den = sgb_add(den, frac);
-            }
-            j = e;
+    const int lane = threadIdx.x & 31;
+    const int cell = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (cell >= ncell) return;
+    long long s = 0;
+    if (lane < 2) s = qc_lower_bound(kg, N, (unsigned long long)cell + lane);
+    const long long e = __shfl_sync(SGB_FULL, s, 1);
+    s = __shfl_sync(SGB_FULL, s, 0);
+    if (s >= e) return;                                                  // no rows: avg[cell] stays NaN
+    double num = 0.0, den = 0.0;
+    long long gstart = s;                                                // first row of the open group
+    unsigned long long gkey = kg[s];
+    auto close_group = [&](long long gend) {
+        const long long cnt = gend - gstart;
+        if (cnt > 10) {                                                  // dplyr::filter(n > 10)
+            const double lo = sgb_u2d(kbaf[rows[gstart + (cnt - 1) / 2]]), hi = sgb_u2d(kbaf[rows[gstart + cnt / 2]]);
+            const double med = sgb_mul(sgb_add(lo, hi), 0.5);            // R's median: mean of the two middle values
+            const int ab = (int)(gkey & 0xffffull), a = ab >> 8, b = ab & 255;
+            const double d = sgb_fabs(sgb_sub(sgb_div((double)b, (double)(a + b)), med));      // sqrt((expBAF - medianBAF)^2)
+            const double frac = sgb_div((double)cnt, ntd);
+            num = sgb_add(num, sgb_mul(d, frac));
+            den = sgb_add(den, frac);
         }
-        avg[cell] = sgb_div(num, den);                                  // weighted.mean(distance, frac); NaN when no state qualifies
+    };
+    for (long long j0 = s + 1; j0 < e; j0 += 32) {
+        const long long j = j0 + lane;
+        const bool headj = j < e && kg[j] != kg[j - 1];
+        unsigned m = __ballot_sync(SGB_FULL, headj);
+        while (m) {                                                       // group heads of this stretch, in row order
+            const int l = __ffs(m) - 1;
+            m &= m - 1;
+            const long long p = j0 + l;
+            close_group(p);
+            gstart = p;
+            gkey = kg[p];
+        }
     }
+    close_group(e);
+    if (lane == 0) avg[cell] = sgb_div(num, den);                         // weighted.mean(distance, frac); NaN when no state qualifies
 }
 size_t sgbk_qc_scratch_bytes(long long n)
 {
@@ -657,7 +682,7 @@ cudaError_t sgbk_qc_per_cell(const int32_t* d_n, const int32_t* d_x, const void*
     int w2 = 0;
     if ((e = radix_sort(ka, ord1, kb, ordt, N, 0, drop_bit + 1, hist, tsum, &w2, st)) != cudaSuccess) return e;
     const unsigned long long* kg = w2 ? kb : ka; const unsigned* rows = w2 ? ordt : ord1;
-    k_qc_cells<<<grid_for(N, 128), 128, 0, st>>>(kg, rows, kbaf, N, drop_bit, ntot, d_avg);
+    k_qc_cells<<<(unsigned)((ncell + 3) / 4), 128, 0, st>>>(kg, rows, kbaf, N, ncell, ntot, d_avg);
     return cudaGetLastError();
 }
 
