@@ -534,7 +534,7 @@ int decode_host_range(Ctx* C, const sgb_params* P, const SgbModelArgs& m, const 
                 SL.cn.reserve((size_t)rows * cn_itemsize) || SL.out.reserve((size_t)rows))
                 return 1;
             if (m.decode == SGB_DECODE_CHAINED &&
-                (SL.bp.reserve((size_t)rows * S) || SL.last_state.reserve((size_t)SL.hp.nseq * 4 + 16)))
+                (SL.bp.reserve((size_t)rows * sgb_bp_stride(S) + 16) || SL.last_state.reserve((size_t)SL.hp.nseq * 4 + 16)))
                 return 1;
             if (loglik_out && SL.loglik.reserve((size_t)rows * S * 8)) return 1;
             SgbPlanDev pd;
@@ -846,7 +846,7 @@ int sgb_plan_create(int64_t N, int64_t nseg, const int64_t* seg_off, int32_t n_s
               pl->cn8.reserve((size_t)N + 16) ||
               ((C->stage != 2 || decode == SGB_DECODE_CHAINED) && pl->packed.reserve((size_t)pl->hp.packed_len * 8 + 16));
     if (!bad && decode == SGB_DECODE_CHAINED)
-        bad = pl->bp.reserve((size_t)N * n_states + 16) || pl->last_state.reserve(ns * 4 + 16);
+        bad = pl->bp.reserve((size_t)N * sgb_bp_stride(n_states) + 16) || pl->last_state.reserve(ns * 4 + 16);
     if (bad) { sgb_plan_destroy(pl); return 1; }
     cudaError_t e = cudaSuccess;
     if (ns) {

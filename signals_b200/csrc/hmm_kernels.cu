@@ -611,9 +611,20 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     } else {
                         unsigned char bpv[SMAX];
                         sgb_seq_step_chained<SMAX>(st, e, S, sp.tr_self, sp.tr_off, bpv);
-                        uint8_t* dst = A.bp + (ostart + t) * (long long)S;
+                        // the bin's backpointers as ONE 16-byte record (two for more than 16 states): a byte store per state
+                        // and lane was 12 x 32 scattered sectors per warp and bin, and the kernel ran at 7.6 ms for 57 M bins
+                        constexpr int BPW = SMAX <= 16 ? 4 : 8;
+                        unsigned w[BPW];
 #pragma unroll
-                        for (int i = 0; i < SMAX; i++) if (i < S) dst[i] = bpv[i];
+                        for (int q = 0; q < BPW; q++) {
+                            unsigned v = 0;
+#pragma unroll
+                            for (int b = 0; b < 4; b++) if (4 * q + b < SMAX) v |= (unsigned)bpv[4 * q + b] << (8 * b);
+                            w[q] = v;
+                        }
+                        uint4* dst = (uint4*)(A.bp + (ostart + t) * (long long)(4 * BPW));
+                        dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+                        if (BPW == 8) dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
                     }
 #pragma unroll
                     for (int i = 0; i < SMAX; i++) colT[i] = st.T1[i];
@@ -750,7 +761,7 @@ __global__ void k_backtrace(SgbPlanDev plan, const uint8_t* __restrict__ bp, con
     int cur = last_state[r];
     state_out[o + len - 1] = (uint8_t)cur;
     for (int t = len - 1; t > 0; t--) {
-        cur = bp[(o + t) * (long long)S + cur];
+        cur = bp[(o + t) * (long long)sgb_bp_stride(S) + cur];
         state_out[o + t - 1] = (uint8_t)cur;
     }
 }

@@ -69,6 +69,8 @@ int sgbk_resolve_stage(const SgbModelArgs& m, int stage, const SgbRawIn& raw);
 cudaError_t sgbk_decode(const SgbPlanDev& plan, const unsigned long long* d_packed, const SgbRawIn& raw,
                         const SgbDevTables* d_tabs, const SgbModelArgs& m, uint8_t* d_state_out, uint8_t* d_bp,
                         int* d_last_state, unsigned int* d_counter, int sm_count, int stage, cudaStream_t st);
+// bytes of backpointers kept per bin by decode = chained: one 16-byte record up to 16 states, two beyond
+static __host__ __device__ inline int sgb_bp_stride(int S) { return S <= 16 ? 16 : 32; }
 cudaError_t sgbk_backtrace(const SgbPlanDev& plan, const uint8_t* d_bp, const int* d_last_state, int S,
                            uint8_t* d_state_out, cudaStream_t st);
 cudaError_t sgbk_loglik(const int32_t* d_n, const int32_t* d_x, const void* d_cn, int cn_itemsize,
