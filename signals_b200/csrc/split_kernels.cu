@@ -38,6 +38,11 @@ static __device__ const double gs_exptab[SGB_EXPTAB_LEN] = SGB_EXPTAB_INIT;
 static __device__ const double gs_lftab[SGB_LFTAB_LEN] = SGB_LFTAB_INIT;
 
 #define SGB_FULL 0xffffffffu
+// Programmatic dependent launch: the kernels of one decode are launched back to back with the stream-serialization attribute;
+// each lets its successor start launching right away (its blocks become resident as this kernel's blocks retire and run
+// their prologue -- table loads, barrier set-up) and waits here for its predecessor to have completed before touching its
+// results.  Launched without the attribute both calls are no-ops.
+#define SGB_PDL_ENTER() do { cudaTriggerProgrammaticLaunchCompletion(); cudaGridDependencySynchronize(); } while (0)
 
 
 #define SGB_NCLS 9                        // plane classes 0 (empty sequence) .. 8
@@ -85,6 +90,7 @@ __global__ void __launch_bounds__(256) k_split_class(SgbPlanDev plan, long long 
 __global__ void __launch_bounds__(256) k_split_scan(SgbSplitDev W)
 {
     __shared__ unsigned int tot[SGB_NCLS], start[SGB_NCLS];
+    SGB_PDL_ENTER();
     const int c = threadIdx.x;
     if (c < SGB_NCLS) {
         unsigned int s = 0;
@@ -117,6 +123,7 @@ __global__ void __launch_bounds__(256) k_split_scan(SgbSplitDev W)
 __global__ void __launch_bounds__(SGB_PART_TILE) k_split_scatter(long long nseq, SgbSplitDev W)
 {
     __shared__ unsigned int wcnt[32][SGB_NCLS];
+    SGB_PDL_ENTER();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const long long i = (long long)blockIdx.x * SGB_PART_TILE + threadIdx.x;
     const int c = i < nseq ? (int)W.cls[i] : 0;
@@ -138,6 +145,7 @@ __global__ void __launch_bounds__(SGB_PART_TILE) k_split_scatter(long long nseq,
 // ------------------------------------------------------------------ k_split_groups (one warp per group)
 __global__ void __launch_bounds__(256) k_split_groups(SgbPlanDev plan, SgbSplitDev W)
 {
+    SGB_PDL_ENTER();
     const int lane = threadIdx.x & 31;
     const int g = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (g >= *W.ngroups) return;
@@ -158,6 +166,7 @@ __global__ void __launch_bounds__(1024) k_split_gscan(SgbSplitDev W, int* err)
 {
     __shared__ unsigned long long wsum[32];
     __shared__ unsigned long long carry;
+    SGB_PDL_ENTER();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int ng = *W.ngroups;
     if (threadIdx.x == 0) carry = 0;
@@ -319,6 +328,7 @@ __global__ void __launch_bounds__(SGB_EMIT_THREADS, LIKBB ? SGB_EMIT_BB_MINBLOCK
     __shared__ SgbScalars s_sp;
     if (threadIdx.x == 0) s_sp = A.tabs->sp;
     __syncthreads();
+    SGB_PDL_ENTER();            // (the tables above come from k_setup, which completed before the partition kernels started)
     const SgbScalars& sp = s_sp;
     const int lane = threadIdx.x & 31;
     const double* LT = sLTp + 2 * (lane & 7);              // this lane's columns of the two tables
@@ -641,6 +651,7 @@ __global__ void __launch_bounds__(SGB_RECUR_NWARPS(MAXNPL) * 32, MAXNPL <= 3 ? 2
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async;" ::: "memory");
     __syncthreads();
+    SGB_PDL_ENTER();
     const SgbScalars& sp = s_sp;
     unsigned phases = 0;              // bit s: parity of the next completed phase of slot s's barrier
     const int ng = *A.W.ngroups;
@@ -695,6 +706,23 @@ __global__ void __launch_bounds__(SGB_RECUR_NWARPS(MAXNPL) * 32, MAXNPL <= 3 ? 2
 }
 
 // ------------------------------------------------------------------ host side
+static bool pdl_enabled()
+{
+    const char* e = getenv("SGB_PDL");
+    return !(e && *e == '0');
+}
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_dep(void (*kern)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 SgbSplitSizes sgbk_split_sizes(long long nseq, long long rows, int maxlen, int S)
 {
     SgbSplitSizes z;
@@ -745,8 +773,7 @@ static cudaError_t launch_emit_k(const SgbEmitArgs& A, long long nseq, int sm_co
     long long blocks = (nseq + 7) / 8;
     if (blocks > (long long)sm_count * occ) blocks = (long long)sm_count * occ;
     if (blocks < 1) blocks = 1;
-    k_emit<MODEL, LIKBB, KIND><<<(unsigned)blocks, SGB_EMIT_THREADS, smem, st>>>(A);
-    return cudaGetLastError();
+    return launch_dep(k_emit<MODEL, LIKBB, KIND>, (unsigned)blocks, SGB_EMIT_THREADS, smem, st, A);
 }
 template <int MODEL, int LIKBB>
 static cudaError_t launch_emit(const SgbEmitArgs& A, long long nseq, int sm_count, cudaStream_t st)
@@ -777,8 +804,7 @@ static cudaError_t launch_recur_k(const SgbRecurArgs& A, int gcap, int sm_count,
     long long blocks = ((long long)gcap + NW - 1) / NW;
     if (blocks > (long long)sm_count * occ) blocks = (long long)sm_count * occ;
     if (blocks < 1) blocks = 1;
-    k_recur<MAXNPL, STAGED><<<(unsigned)blocks, NW * 32, smem, st>>>(A, ring_kb * 1024);
-    return cudaGetLastError();
+    return launch_dep(k_recur<MAXNPL, STAGED>, (unsigned)blocks, NW * 32, smem, st, A, ring_kb * 1024);
 }
 
 // Batches that fill the device several times over are bound by the L1's store path unless the decoded states are staged
@@ -803,11 +829,11 @@ cudaError_t sgbk_split_decode(const SgbPlanDev& plan, long long nseq, const SgbC
     long long cb = (nseq + 7) / 8;
     if (cb > (long long)sm_count * 8) cb = (long long)sm_count * 8;
     k_split_class<<<(unsigned)cb, 256, 0, st>>>(plan, nseq, in.cn, in.kind, m.model, m.S, W);
-    k_split_scan<<<1, 256, 0, st>>>(W);
-    k_split_scatter<<<(unsigned)W.ntile, SGB_PART_TILE, 0, st>>>(nseq, W);
-    k_split_groups<<<(unsigned)((W.gcap + 7) / 8), 256, 0, st>>>(plan, W);
-    k_split_gscan<<<1, 1024, 0, st>>>(W, in.err);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if ((e = launch_dep(k_split_scan, 1u, 256u, 0, st, W)) != cudaSuccess) return e;
+    if ((e = launch_dep(k_split_scatter, (unsigned)W.ntile, (unsigned)SGB_PART_TILE, 0, st, nseq, W)) != cudaSuccess) return e;
+    if ((e = launch_dep(k_split_groups, (unsigned)((W.gcap + 7) / 8), 256u, 0, st, plan, W)) != cudaSuccess) return e;
+    if ((e = launch_dep(k_split_gscan, 1u, 1024u, 0, st, W, in.err)) != cudaSuccess) return e;
     if (ev_prep && (e = cudaEventRecord(ev_prep, st)) != cudaSuccess) return e;
     SgbEmitArgs EA;
     EA.plan = plan; EA.W = W; EA.in = in; EA.tabs = d_tabs; EA.S = m.S;
