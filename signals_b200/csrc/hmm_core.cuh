@@ -548,20 +548,25 @@ SGB_HD int sgb_seq_step_mem(double* T1, int ts, const double* E, int es, double&
 }
 
 // Chained (textbook) mode: backpointers of ALL states for bin j, bp[i] = first argmax_k.
+// nl: states >= nl are dead in this bin AND the previous one (e[i] = T1[i] = -Inf there), so their column entry is -Inf with
+// backpointer 0 (every candidate is -Inf: the first one wins) and they never beat a candidate of a live state -- the S x S
+// candidate loop shrinks to nl x nl (nl = warp-wide maximum of the live-state counts of the two bins, 5-6 of 12 on DLP data).
 template <int SMAX>
 SGB_HD void sgb_seq_step_chained(SgbSeqState<SMAX>& st, const double* e, int S, double tr_self, double tr_off,
-                                 unsigned char* bp)
+                                 unsigned char* bp, int nl = SMAX)
 {
     double Tn[SMAX];
+    const int Sl = S < nl ? S : nl;
 #pragma unroll
     for (int i = 0; i < SMAX; i++) {
         Tn[i] = -sgb_inf();
-        if (i < S) {
+        if (i < S) bp[i] = 0;
+        if (i < Sl) {
             double best = sgb_add(sgb_add(st.T1[0], (0 == i) ? tr_self : tr_off), e[i]);
             int arg = 0;
 #pragma unroll
             for (int k = 1; k < SMAX; k++) {
-                if (k < S) {
+                if (k < Sl) {
                     double val = sgb_add(sgb_add(st.T1[k], (k == i) ? tr_self : tr_off), e[i]);
                     if (val > best) { best = val; arg = k; }
                 }

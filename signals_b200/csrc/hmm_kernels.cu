@@ -609,8 +609,8 @@ __global__ void __launch_bounds__(SGB_DECODE_THREADS, SGB_DECODE_MINBLOCKS) k_de
                     if (t == 0) {
                         sgb_seq_init<SMAX>(st, e, S, sp.init);
                     } else {
-                        unsigned char bpv[SMAX];
-                        sgb_seq_step_chained<SMAX>(st, e, S, sp.tr_self, sp.tr_off, bpv);
+                        unsigned char bpv[SMAX] = {};
+                        sgb_seq_step_chained<SMAX>(st, e, S, sp.tr_self, sp.tr_off, bpv, nlive);
                         // the bin's backpointers as ONE 16-byte record (two for more than 16 states): a byte store per state
                         // and lane was 12 x 32 scattered sectors per warp and bin, and the kernel ran at 7.6 ms for 57 M bins
                         constexpr int BPW = SMAX <= 16 ? 4 : 8;

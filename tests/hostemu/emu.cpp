@@ -79,7 +79,8 @@ static void run(int S, int decode, double loherror, double eps, double rho, doub
             int back = sgb_seq_step<SMAX>(st, e, e, 1, S, sp.tr_self, sp.tr_off, sp.diag_dominant);
             out[t - 1] = (unsigned char)back;
         } else {
-            sgb_seq_step_chained<SMAX>(st, e, S, sp.tr_self, sp.tr_off, &bp[(size_t)t * S]);
+            const int nlive = (L > Lprev) ? L : Lprev;       // (the kernel: warp-wide maxima of the two counts)
+            sgb_seq_step_chained<SMAX>(st, e, S, sp.tr_self, sp.tr_off, &bp[(size_t)t * S], nlive);
         }
     }
     if (decode == SGB_DECODE_REFERENCE) {
