@@ -63,7 +63,8 @@ SEXP Rf_allocVector(int type, R_xlen_t n)
     if (!es || n < 0) Rf_error("mock: cannot allocate a vector of type %d", type);
     SEXP s = (SEXP)track(calloc(1, sizeof(struct mock_sexp)));
     s->type = type; s->len = n; s->dim = R_NilValue;
-    s->data = track(calloc((size_t)n + 1, es));
+    /* like R, numeric / integer vectors come back uninitialised (zeroing 456 MB on one thread would be the mock's cost, not R's) */
+    s->data = track((type == REALSXP || type == INTSXP) ? malloc(((size_t)n + 1) * es) : calloc((size_t)n + 1, es));
     if (type == STRSXP || type == VECSXP)
         for (R_xlen_t i = 0; i < n; i++) ((SEXP*)s->data)[i] = R_NilValue;
     return s;
